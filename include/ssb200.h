@@ -1,0 +1,100 @@
+/* libssb200 -- C ABI of the B200-native hot path of mmaciej2/speech-separation.
+ *
+ * The reference has NO C/FFI boundary: its boundary is the Python arch-module protocol
+ * (archs/uPIT.py, archs/RSH.py) plus two CLIs (steps/extract_feats.py, steps/reconstruct_sources.py), and all
+ * of its device arithmetic is implicit torch / librosa library calls.  Each entry point below therefore cites
+ * the reference call site(s) whose arithmetic it replaces.  The Python host code in
+ * speech-separation_b200/ssb200/ binds these with ctypes.
+ *
+ * Conventions: every pointer is a DEVICE pointer owned by the caller (workspaces included); `stream` is a
+ * cudaStream_t passed as void*; functions return 0 on success, <0 on error with text in ss_last_error();
+ * nothing synchronises the device.  Activations are time-major padded: row index = t*B + b.
+ *
+ * "sb16" = split-bf16 matrix: two bf16 planes (hi at base, lo at base + plane elements), x ~= hi + lo, row
+ * pitch in elements (multiple of 8).  Tensor-core products use hi*hi + hi*lo + lo*hi (fp32-class accuracy).
+ */
+#ifndef SSB200_H
+#define SSB200_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SSB200_VERSION 1
+
+/* ---- library ---- */
+const char* ss_last_error(void);
+int ss_version(void);
+int ss_device_check(void); /* >0: SM count of the current sm_100 device; <0: error */
+
+/* ---- K1: STFT features.  Replaces librosa.core.stft (+np.abs) at steps/extract_feats.py:76-89,98,105 ----
+ * Ragged corpus: utterance u owns samples [sig_off[u], sig_off[u+1]) of `sig`, frames
+ * [frame_off[u], frame_off[u+1]) with T_u = 1 + N_u/hop, and CTA tiles [tile_off[u], tile_off[u+1]) with
+ * ceil(T_u / ss_stft_tile_frames()) tiles.  Output block of utterance u starts at element frame_off[u]*F
+ * (F = n_fft/2+1; float for magnitude, float2 for complex) and is (F, T_u) row-major -- the layout of the
+ * reference's .npz arrays -- or (T_u, F) with SS_STFT_LAYOUT_TF.  N_u must exceed n_fft/2 (reflect padding). */
+#define SS_STFT_COMPLEX 1   /* keep complex64 (extract_feats.py test branch :98,105) instead of |X| (:87,89) */
+#define SS_STFT_LAYOUT_TF 2 /* (T,F) per utterance instead of the file layout (F,T) */
+#define SS_STFT_LOG 4       /* log(max(|X|,1e-8)); NOT reference behaviour, off for parity */
+int ss_stft_tile_frames(void);
+int ss_stft(const float* sig, const long long* sig_off, const long long* frame_off, const int* tile_off, int n_utts,
+            int total_tiles, int n_fft, int hop, int flags, void* out, void* stream);
+
+/* ---- K7: masked iSTFT.  Replaces steps/reconstruct_sources.py:39-42 (np.multiply, librosa.core.istft,
+ * *32767, astype('int16')) ----
+ * spec: complex64 mixture STFT blocks as written by ss_stft(COMPLEX); mask: for utterance u, n_src blocks of
+ * the same (F,T_u) shape starting at element (frame_off[u]*n_src)*F.  Output of (u, s) starts at
+ * wav_off[u] + s*L_u, L_u = hop*(T_u-1) samples (int16, or float before the *32767 with SS_ISTFT_OUT_F32).
+ * tile_off counts ceil(L_u / (ss_istft_tile_hops()*hop)) tiles per utterance. */
+#define SS_ISTFT_LAYOUT_TF 1
+#define SS_ISTFT_OUT_F32 2
+int ss_istft_tile_hops(void);
+int ss_istft_masked(const void* spec, const float* mask, const long long* frame_off, const long long* wav_off,
+                    const int* tile_off, int n_utts, int n_src, int total_tiles, int n_fft, int hop, int flags,
+                    void* out, void* stream);
+
+/* ---- tensor-core GEMM on sb16 operands.  Replaces the cuBLAS GEMMs behind nn.LSTM's input projection and
+ * nn.Linear (archs/uPIT.py:115-117,132,141; archs/RSH.py:155-157,172,181) and their autograd backward ----
+ * C[rowmap(m)][n] = alpha * sum_k A[m][k]*B[n][k] + bias[n] + beta*C[..][n];  A: M x K, B: N x K (both K-major). */
+#define SS_ROWMAP_NONE 0
+#define SS_ROWMAP_UNIT4 1 /* m = 4*u + gate  ->  output row gate*hidden + u (undo the gate interleave) */
+int ss_gemm_sb16(const void* A, long long lda, long long a_plane, const void* B, long long ldb, long long b_plane,
+                 float* C, long long ldc, int M, int N, int K, const float* bias, float alpha, float beta, int rowmap,
+                 int hidden, void* stream);
+
+/* ---- layout / precision conversion kernels (plumbing around the GEMMs) ----
+ * ss_split: fp32 in[R][C] (pitch ld_in) -> sb16 out[rp(r)][C] (pitch ld_out, plane out_plane) and/or the
+ * transposed sb16 outT[C][rp(r)] (pitch ld_outT).  rowperm = SS_ROWMAP_UNIT4 interleaves LSTM gate rows:
+ * natural row gate*hidden+u -> 4*u+gate.  Either output may be NULL.  scale[C] (optional) multiplies column c. */
+int ss_split(const float* in, long long ld_in, int R, int C, int rowperm, int hidden, const float* col_scale,
+             void* out, long long ld_out, long long out_plane, void* outT, long long ld_outT, long long outT_plane,
+             void* stream);
+/* column sums of an sb16 matrix: out[c] = sum_r (hi+lo)[r][c]; partial: >= ss_colsum_parts(R)*C floats. */
+int ss_colsum_parts(int R);
+int ss_colsum_sb16(const void* in, long long ld, long long plane, int R, int C, float* partial, float* out,
+                   int rowmap, int hidden, void* stream);
+
+/* ---- K5/K6: fused mask*mix, pairwise squared errors, permutation / greedy assignment, loss; and backward ----
+ * Replaces archs/uPIT.py:178-206 and archs/RSH.py:224-241.  z: head pre-activations [T*B][ldz] (n_out*F columns,
+ * output slot i in columns [i*F,(i+1)*F)); mix [T*B][F]; src [n_src][T*B][F]; lens[B] frames per utterance.
+ * fwd writes partial[ss_pit_chunks(T)][B][n_out*n_src] (+ optionally mask = sigmoid(z) [T*B][n_out*F]).
+ * select, mode 0 (uPIT.py:186-194): losses[P][B] in itertools.permutations order, idx[B] = argmin, assign[B][n_out]
+ * = chosen source per output slot; mode 1 (RSH.py:229-238): losses[n_src][B] with +inf for sources in the
+ * bitmask used[B], idx = argmin, used updated.  stats[4] = {sum_b min/S, sum_b len_b*F, loss = [0]/[1], 1/(S*[1])},
+ * accumulated over calls when accumulate != 0 (RSH.py:240-241).
+ * bwd: dz = (2*(m*x - src[assign])*x*stats[3]*gout[0] + dmask_extra) * m*(1-m), as sb16 [T*B][ld_dz] and
+ * transposed sb16 [n_out*F][ld_dzT]; rows with t >= len_b are zero. */
+int ss_pit_chunks(int T);
+int ss_pit_loss_fwd(const float* z, long long ldz, const float* mix, const float* src, const int* lens, int T, int B,
+                    int F, int n_out, int n_src, float* mask_out, float* partial, void* stream);
+int ss_pit_select(const float* partial, int chunks, const int* lens, int B, int F, int n_out, int n_src, int mode,
+                  int accumulate, float* losses, int* idx, int* assign, int* used, float* stats, void* stream);
+int ss_pit_loss_bwd(const float* z, long long ldz, const float* mix, const float* src, const int* lens,
+                    const int* assign, int T, int B, int F, int n_out, const float* stats, const float* gout,
+                    const float* dmask_extra, void* dz, long long ld_dz, long long dz_plane, void* dzT,
+                    long long ld_dzT, long long dzT_plane, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SSB200_H */

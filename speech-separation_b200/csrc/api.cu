@@ -1,0 +1,84 @@
+// libssb200 C-ABI plumbing: error text, version, TMA tensor-map encoding (driver entry point
+// resolved at run time so the library links without libcuda and loads on GPU-less hosts).
+#include <cudaTypedefs.h>
+#include <stdarg.h>
+#include <string.h>
+
+#include "../../include/ssb200.h"
+#include "common.cuh"
+
+namespace ssb {
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+int check_launch(const char* what) {
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    set_error("%s: %s", what, cudaGetErrorString(e));
+    return -2;
+  }
+  return 0;
+}
+
+int make_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
+                   const uint32_t* box) {
+  static PFN_cuTensorMapEncodeTiled_v12000 encode = nullptr;
+  if (!encode) {
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres);
+    if (e != cudaSuccess || qres != cudaDriverEntryPointSuccess || !fn) {
+      set_error("cuTensorMapEncodeTiled unavailable (%s)", cudaGetErrorString(e));
+      return -3;
+    }
+    encode = (PFN_cuTensorMapEncodeTiled_v12000)fn;
+  }
+  cuuint64_t gdim[5], gstr[5];
+  cuuint32_t bdim[5], estr[5];
+  for (int i = 0; i < rank; ++i) {
+    gdim[i] = dims[i];
+    bdim[i] = box[i];
+    estr[i] = 1;
+    if (i > 0) gstr[i - 1] = strides_bytes[i - 1];
+  }
+  CUresult r = encode(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, rank, const_cast<void*>(base), gdim, gstr, bdim, estr,
+                      CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                      CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("cuTensorMapEncodeTiled failed: CUresult %d (rank %d dims %llu,%llu box %u,%u)", (int)r, rank,
+              (unsigned long long)dims[0], (unsigned long long)(rank > 1 ? dims[1] : 0), box[0], rank > 1 ? box[1] : 0);
+    return -3;
+  }
+  return 0;
+}
+
+}  // namespace ssb
+
+extern "C" {
+
+const char* ss_last_error(void) { return ssb::g_err; }
+
+int ss_version(void) { return SSB200_VERSION; }
+
+int ss_device_check(void) {
+  int dev = 0;
+  cudaDeviceProp p;
+  if (cudaGetDevice(&dev) != cudaSuccess || cudaGetDeviceProperties(&p, dev) != cudaSuccess) {
+    ssb::set_error("no CUDA device: %s", cudaGetErrorString(cudaGetLastError()));
+    return -2;
+  }
+  if (p.major != 10) {
+    ssb::set_error("libssb200 is built for sm_100a only; device is sm_%d%d", p.major, p.minor);
+    return -4;
+  }
+  return p.multiProcessorCount;
+}
+
+}  // extern "C"

@@ -1,0 +1,113 @@
+// Layout / precision conversion kernels around the tensor-core GEMMs (HBM-bound plumbing).
+#include "../../include/ssb200.h"
+#include "common.cuh"
+
+namespace ssb {
+
+__device__ __forceinline__ int rowperm_fwd(int r, int mode, int hidden) {
+  // natural LSTM gate row (gate*hidden + u)  ->  interleaved (4*u + gate)
+  return mode == SS_ROWMAP_UNIT4 ? 4 * (r % hidden) + r / hidden : r;
+}
+
+__global__ void __launch_bounds__(256) split_kernel(const float* __restrict__ in, long long ld_in, int R, int C,
+                                                    int rowperm, int hidden, const float* __restrict__ col_scale,
+                                                    __nv_bfloat16* __restrict__ out, long long ld_out,
+                                                    long long out_plane, __nv_bfloat16* __restrict__ outT,
+                                                    long long ld_outT, long long outT_plane) {
+  __shared__ float tile[32][33];
+  const int c0 = blockIdx.x * 32, r0 = blockIdx.y * 32;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int r = r0 + ty + 8 * i, c = c0 + tx;
+    float v = 0.0f;
+    if (r < R && c < C) {
+      v = in[(long long)r * ld_in + c];
+      if (col_scale) v *= col_scale[c];
+      if (out) {
+        __nv_bfloat16 hi, lo;
+        split_bf16(v, hi, lo);
+        const long long o = (long long)rowperm_fwd(r, rowperm, hidden) * ld_out + c;
+        out[o] = hi;
+        out[o + out_plane] = lo;
+      }
+    }
+    tile[ty + 8 * i][tx] = v;
+  }
+  if (!outT) return;
+  __syncthreads();
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int c = c0 + ty + 8 * i, r = r0 + tx;
+    if (r < R && c < C) {
+      __nv_bfloat16 hi, lo;
+      split_bf16(tile[tx][ty + 8 * i], hi, lo);
+      const long long o = (long long)c * ld_outT + rowperm_fwd(r, rowperm, hidden);
+      outT[o] = hi;
+      outT[o + outT_plane] = lo;
+    }
+  }
+}
+
+constexpr int CS_ROWS = 256;   // rows per partial block
+
+__global__ void __launch_bounds__(256) colsum_partial_kernel(const __nv_bfloat16* __restrict__ in, long long ld,
+                                                             long long plane, int R, int C,
+                                                             float* __restrict__ partial) {
+  const int c = blockIdx.x * 256 + threadIdx.x;
+  if (c >= C) return;
+  const int r0 = blockIdx.y * CS_ROWS, r1 = min(R, r0 + CS_ROWS);
+  float acc = 0.0f;
+  for (int r = r0; r < r1; ++r) {
+    const long long o = (long long)r * ld + c;
+    acc += join_bf16(in[o], in[o + plane]);
+  }
+  partial[(long long)blockIdx.y * C + c] = acc;
+}
+
+__global__ void __launch_bounds__(256) colsum_final_kernel(const float* __restrict__ partial, int parts, int C,
+                                                           float* __restrict__ out, int rowmap, int hidden) {
+  const int c = blockIdx.x * 256 + threadIdx.x;
+  if (c >= C) return;
+  double acc = 0.0;
+  for (int p = 0; p < parts; ++p) acc += (double)partial[(long long)p * C + c];
+  int oc = c;
+  if (rowmap == SS_ROWMAP_UNIT4) {           // c = blk*4H + 4*u + gate  ->  blk*4H + gate*H + u
+    const int blk = c / (4 * hidden), w = c % (4 * hidden);
+    oc = blk * 4 * hidden + (w & 3) * hidden + (w >> 2);
+  }
+  out[oc] = (float)acc;
+}
+
+}  // namespace ssb
+
+extern "C" int ss_split(const float* in, long long ld_in, int R, int C, int rowperm, int hidden,
+                        const float* col_scale, void* out, long long ld_out, long long out_plane, void* outT,
+                        long long ld_outT, long long outT_plane, void* stream) {
+  using namespace ssb;
+  if (R == 0 || C == 0) return 0;
+  SS_REQUIRE(out || outT, "ss_split: no output");
+  SS_REQUIRE(rowperm == SS_ROWMAP_NONE || (hidden > 0 && R == 4 * hidden), "ss_split: UNIT4 needs R == 4*hidden");
+  dim3 grid(cdiv(C, 32), cdiv(R, 32));
+  split_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(in, ld_in, R, C, rowperm, hidden, col_scale,
+                                                       (__nv_bfloat16*)out, ld_out, out_plane, (__nv_bfloat16*)outT,
+                                                       ld_outT, outT_plane);
+  return check_launch("ss_split");
+}
+
+extern "C" int ss_colsum_parts(int R) { return ssb::cdiv(R, ssb::CS_ROWS); }
+
+extern "C" int ss_colsum_sb16(const void* in, long long ld, long long plane, int R, int C, float* partial, float* out,
+                              int rowmap, int hidden, void* stream) {
+  using namespace ssb;
+  if (C == 0) return 0;
+  const int parts = cdiv(R, CS_ROWS);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (parts > 0)
+    colsum_partial_kernel<<<dim3(cdiv(C, 256), parts), 256, 0, st>>>((const __nv_bfloat16*)in, ld, plane, R, C, partial);
+  colsum_final_kernel<<<cdiv(C, 256), 256, 0, st>>>(partial, parts, C, out, rowmap, hidden);
+  return check_launch("ss_colsum_sb16");
+}
+
+extern "C" int ss_stft_tile_frames(void) { return 32; }
+extern "C" int ss_istft_tile_hops(void) { return 28; }

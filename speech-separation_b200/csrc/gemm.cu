@@ -1,0 +1,171 @@
+// tcgen05 GEMM on split-bf16 operands:  C[m][n] = alpha * sum_k A[m][k] * B[n][k] (+ bias[n]) (+ beta * C[m][n])
+// A, B are "sb16" matrices (two bf16 planes hi, lo; x ~= hi + lo) and the product is evaluated as
+// hi*hi + hi*lo + lo*hi with fp32 accumulation in TMEM (error ~2^-16, i.e. fp32-class results from the bf16 pipe).
+// One 128x128 output tile per CTA; warp 0 = TMA producer, warp 1 = MMA issuer, warps 2..5 = epilogue.
+// Stands in for every cuBLAS call the reference makes through torch (nn.LSTM input projections,
+// nn.Linear: archs/uPIT.py:115-117,132,141) and for their autograd backward GEMMs.
+#include "../../include/ssb200.h"
+#include "common.cuh"
+
+namespace ssb {
+
+constexpr int GB_M = 128, GB_N = 128, GB_K = 64, G_STAGES = 3, G_THREADS = 192;
+constexpr int G_PLANE = GB_M * GB_K * 2;                 // 16 KB: one bf16 plane of one operand tile
+constexpr int G_STAGE_BYTES = 4 * G_PLANE;               // A(hi,lo) + B(hi,lo)
+constexpr int G_SMEM = G_STAGES * G_STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/;
+
+struct GemmParams {
+  float* C;
+  long long ldc;
+  const float* bias;
+  float alpha, beta;
+  int M, N, K, rowmap, hidden;
+};
+
+__global__ void __launch_bounds__(G_THREADS, 1)
+gemm_sb16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, GemmParams p) {
+  extern __shared__ unsigned char smem_raw[];
+  unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + G_STAGES * G_STAGE_BYTES);
+  uint64_t* empty = full + G_STAGES;
+  uint64_t* accum_full = empty + G_STAGES;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(accum_full + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int n0 = blockIdx.x * GB_N, m0 = blockIdx.y * GB_M;
+  const int nkb = (p.K + GB_K - 1) / GB_K;
+
+  if (threadIdx.x == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+    for (int s = 0; s < G_STAGES; ++s) {
+      mbar_init(&full[s], 1);
+      mbar_init(&empty[s], 1);
+    }
+    mbar_init(accum_full, 1);
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc<GB_N>(tmem_slot);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_d = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      for (int kb = 0; kb < nkb; ++kb) {
+        const int s = kb % G_STAGES, ph = (kb / G_STAGES) & 1;
+        mbar_wait(&empty[s], ph ^ 1);
+        unsigned char* st = smem + s * G_STAGE_BYTES;
+        mbar_arrive_expect_tx(&full[s], G_STAGE_BYTES);
+        tma_load_3d(st, &tmA, &full[s], kb * GB_K, m0, 0);               // [plane][128 rows][64 k]
+        tma_load_3d(st + 2 * G_PLANE, &tmB, &full[s], kb * GB_K, n0, 0);
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc = umma_idesc_bf16(GB_M, GB_N);
+      for (int kb = 0; kb < nkb; ++kb) {
+        const int s = kb % G_STAGES, ph = (kb / G_STAGES) & 1;
+        mbar_wait(&full[s], ph);
+        tc_fence_after();
+        const uint32_t a_hi = smem_u32(smem + s * G_STAGE_BYTES), a_lo = a_hi + G_PLANE;
+        const uint32_t b_hi = a_hi + 2 * G_PLANE, b_lo = b_hi + G_PLANE;
+#pragma unroll
+        for (int k = 0; k < GB_K / 16; ++k) {
+          const uint32_t ko = k * 32;                                      // 16 bf16 = 32 bytes inside the 128B row
+          const uint64_t dah = umma_desc_sw128(a_hi + ko), dal = umma_desc_sw128(a_lo + ko);
+          const uint64_t dbh = umma_desc_sw128(b_hi + ko), dbl = umma_desc_sw128(b_lo + ko);
+          umma_bf16(tmem_d, dal, dbh, idesc, (kb | k) ? 1u : 0u);          // small terms first
+          umma_bf16(tmem_d, dah, dbl, idesc, 1u);
+          umma_bf16(tmem_d, dah, dbh, idesc, 1u);
+        }
+        umma_commit(&empty[s]);
+      }
+      umma_commit(accum_full);
+    }
+  } else {
+    // epilogue: warp w may touch TMEM lanes [32*(w%4), +32)
+    const int q = warp & 3;
+    const int m = m0 + q * 32 + lane;
+    mbar_wait(accum_full, 0);
+    tc_fence_after();
+    long long orow = m;
+    if (p.rowmap == SS_ROWMAP_UNIT4) orow = (long long)(m & 3) * p.hidden + (m >> 2);
+    float* crow = p.C + orow * p.ldc;
+    const bool vec = ((p.ldc & 3) == 0) && ((reinterpret_cast<uintptr_t>(p.C) & 15) == 0);
+    for (int c = 0; c < GB_N; c += 16) {
+      if (n0 + c >= p.N) break;                       // warp-uniform
+      float v[16];
+      tmem_ld16(tmem_d + ((uint32_t)(q * 32) << 16) + c, v);
+      if (m < p.M) {
+        const int nb = n0 + c;
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+          float r = p.alpha * v[i];
+          if (p.bias && nb + i < p.N) r += p.bias[nb + i];
+          v[i] = r;
+        }
+        if (vec && nb + 16 <= p.N) {
+          float4* dst = reinterpret_cast<float4*>(crow + nb);
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            float4 o = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+            if (p.beta != 0.0f) {
+              const float4 old = dst[i];
+              o.x += p.beta * old.x; o.y += p.beta * old.y; o.z += p.beta * old.z; o.w += p.beta * old.w;
+            }
+            dst[i] = o;
+          }
+        } else {
+#pragma unroll
+          for (int i = 0; i < 16; ++i)
+            if (nb + i < p.N) crow[nb + i] = v[i] + (p.beta != 0.0f ? p.beta * crow[nb + i] : 0.0f);
+        }
+      }
+    }
+    tc_fence_before();
+  }
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_free<GB_N>(tmem_d);
+  }
+}
+
+// tensor map over an sb16 matrix: dims (K, rows, 2 planes), box (64, 128, 2)
+static int sb16_tmap(CUtensorMap* tm, const void* base, long long rows, long long K, long long pitch, long long plane,
+                     int box_rows) {
+  uint64_t dims[3] = {(uint64_t)K, (uint64_t)rows, 2};
+  uint64_t strides[2] = {(uint64_t)pitch * 2, (uint64_t)plane * 2};
+  uint32_t box[3] = {64, (uint32_t)box_rows, 2};
+  return make_tmap_bf16(tm, base, 3, dims, strides, box);
+}
+
+}  // namespace ssb
+
+extern "C" int ss_gemm_sb16(const void* A, long long lda, long long a_plane, const void* B, long long ldb,
+                            long long b_plane, float* C, long long ldc, int M, int N, int K, const float* bias,
+                            float alpha, float beta, int rowmap, int hidden, void* stream) {
+  using namespace ssb;
+  SS_REQUIRE(M > 0 && N > 0 && K > 0, "ss_gemm_sb16: empty problem %dx%dx%d", M, N, K);
+  SS_REQUIRE(lda % 8 == 0 && ldb % 8 == 0 && a_plane % 8 == 0 && b_plane % 8 == 0,
+             "ss_gemm_sb16: pitches/plane strides must be multiples of 8 elements (16 bytes)");
+  SS_REQUIRE(((uintptr_t)A & 15) == 0 && ((uintptr_t)B & 15) == 0, "ss_gemm_sb16: operands must be 16-byte aligned");
+  SS_REQUIRE(rowmap == SS_ROWMAP_NONE || (rowmap == SS_ROWMAP_UNIT4 && hidden > 0 && M == 4 * hidden),
+             "ss_gemm_sb16: bad rowmap");
+  CUtensorMap tmA, tmB;
+  int rc = sb16_tmap(&tmA, A, M, K, lda, a_plane, GB_M);
+  if (rc) return rc;
+  rc = sb16_tmap(&tmB, B, N, K, ldb, b_plane, GB_N);
+  if (rc) return rc;
+  GemmParams p{C, ldc, bias, alpha, beta, M, N, K, rowmap, hidden};
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaFuncSetAttribute(gemm_sb16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, G_SMEM);
+    attr_set = true;
+  }
+  dim3 grid(cdiv(N, GB_N), cdiv(M, GB_M));
+  gemm_sb16_kernel<<<grid, G_THREADS, G_SMEM, (cudaStream_t)stream>>>(tmA, tmB, p);
+  return check_launch("ss_gemm_sb16");
+}

@@ -1,0 +1,144 @@
+"""Host-side wrappers (torch tensors in, torch tensors out) over the C ABI.  No arithmetic happens here:
+torch only allocates device memory and supplies the stream."""
+import numpy as np
+import torch
+
+from ._lib import LL, call, lib, stream_ptr
+
+
+def _i64(a, device):
+    return torch.as_tensor(np.asarray(a, dtype=np.int64), device=device)
+
+
+def _i32(a, device):
+    return torch.as_tensor(np.asarray(a, dtype=np.int32), device=device)
+
+
+def up8(n):
+    return (int(n) + 7) // 8 * 8
+
+
+class Ragged:
+    """Offsets of a ragged batch of utterances (lengths in samples)."""
+
+    def __init__(self, n_samples, n_fft, hop, device):
+        n = np.asarray(n_samples, dtype=np.int64)
+        if n.size and n.min() <= n_fft // 2:
+            raise ValueError("every utterance must be longer than n_fft//2 samples (reflect padding)")
+        self.n_fft, self.hop, self.F = n_fft, hop, n_fft // 2 + 1
+        self.n_samples = n
+        self.T = 1 + n // hop
+        self.sig_off = np.concatenate([[0], np.cumsum(n)])
+        self.frame_off = np.concatenate([[0], np.cumsum(self.T)])
+        tf = lib().ss_stft_tile_frames()
+        self.stft_tiles = np.concatenate([[0], np.cumsum((self.T + tf - 1) // tf)]).astype(np.int32)
+        self.L = hop * (self.T - 1)
+        th = lib().ss_istft_tile_hops() * hop
+        self.istft_tiles = np.concatenate([[0], np.cumsum((self.L + th - 1) // th)]).astype(np.int32)
+        self.device = device
+        self.d_sig_off = _i64(self.sig_off, device)
+        self.d_frame_off = _i64(self.frame_off, device)
+        self.d_stft_tiles = _i32(self.stft_tiles, device)
+        self.d_istft_tiles = _i32(self.istft_tiles, device)
+
+    @property
+    def n_utts(self):
+        return len(self.n_samples)
+
+    @property
+    def total_frames(self):
+        return int(self.frame_off[-1])
+
+
+STFT_COMPLEX, STFT_TF, STFT_LOG = 1, 2, 4
+ISTFT_TF, ISTFT_F32 = 1, 2
+
+
+def stft(sig, rag, complex_out=False, layout_tf=False, log=False, out=None):
+    """sig: flat float32 cuda tensor holding all utterances back to back.  Returns a flat tensor whose block
+    for utterance u is [frame_off[u]*F, frame_off[u+1]*F) shaped (F,T_u) (or (T_u,F) with layout_tf)."""
+    assert sig.is_cuda and sig.dtype == torch.float32 and sig.is_contiguous()
+    assert sig.numel() == int(rag.sig_off[-1])
+    n = rag.total_frames * rag.F
+    if out is None:
+        out = torch.empty(n, dtype=torch.complex64 if complex_out else torch.float32, device=sig.device)
+    flags = (STFT_COMPLEX if complex_out else 0) | (STFT_TF if layout_tf else 0) | (STFT_LOG if log else 0)
+    call("stft", sig, rag.d_sig_off, rag.d_frame_off, rag.d_stft_tiles, rag.n_utts, int(rag.stft_tiles[-1]),
+         rag.n_fft, rag.hop, flags, out, stream_ptr())
+    return out
+
+
+def stft_views(flat, rag, layout_tf=False):
+    """Per-utterance views of a flat STFT buffer."""
+    F = rag.F
+    outs = []
+    for u in range(rag.n_utts):
+        blk = flat[int(rag.frame_off[u]) * F:int(rag.frame_off[u + 1]) * F]
+        outs.append(blk.view(int(rag.T[u]), F) if layout_tf else blk.view(F, int(rag.T[u])))
+    return outs
+
+
+def istft_masked(spec, mask, rag, n_src, layout_tf=False, out_f32=False, out=None):
+    """spec: flat complex64 (ss_stft COMPLEX output); mask: flat float32, n_src blocks per utterance.
+    Returns (flat wav tensor int16|float32, wav_off numpy[int64] of length n_utts+1)."""
+    assert spec.is_cuda and spec.dtype == torch.complex64 and mask.dtype == torch.float32
+    assert mask.numel() == rag.total_frames * rag.F * n_src
+    wav_off = np.concatenate([[0], np.cumsum(rag.L * n_src)])
+    if out is None:
+        out = torch.empty(int(wav_off[-1]), dtype=torch.float32 if out_f32 else torch.int16, device=spec.device)
+    flags = (ISTFT_TF if layout_tf else 0) | (ISTFT_F32 if out_f32 else 0)
+    call("istft_masked", spec, mask, rag.d_frame_off, _i64(wav_off, spec.device), rag.d_istft_tiles, rag.n_utts, n_src,
+         int(rag.istft_tiles[-1]), rag.n_fft, rag.hop, flags, out, stream_ptr())
+    return out, wav_off
+
+
+class SB16:
+    """Split-bf16 matrix [rows][cols] with pitch `ld` (elements): planes hi, lo in one bf16 buffer."""
+
+    def __init__(self, rows, cols, device, ld=None, buf=None):
+        self.rows, self.cols = int(rows), int(cols)
+        self.ld = up8(cols) if ld is None else int(ld)
+        self.plane = self.rows * self.ld
+        self.buf = torch.zeros(2 * self.plane, dtype=torch.bfloat16, device=device) if buf is None else buf
+        assert self.buf.numel() >= 2 * self.plane
+
+    def float(self):
+        v = self.buf[:2 * self.plane].view(2, self.rows, self.ld)[:, :, :self.cols].float()
+        return v[0] + v[1]
+
+
+def split(x, rowperm=0, hidden=0, col_scale=None, want=True, want_t=False, out=None, out_t=None):
+    """fp32 matrix (R,C) -> SB16 (R,C) and/or transposed SB16 (C,R)."""
+    assert x.is_cuda and x.dtype == torch.float32 and x.dim() == 2 and x.stride(1) == 1
+    R, C = x.shape
+    if want and out is None:
+        out = SB16(R, C, x.device)
+    if want_t and out_t is None:
+        out_t = SB16(C, R, x.device)
+    call("split", x, LL(x.stride(0)), R, C, rowperm, hidden, col_scale,
+         out.buf if out is not None else None, LL(out.ld if out is not None else 0), LL(out.plane if out is not None else 0),
+         out_t.buf if out_t is not None else None, LL(out_t.ld if out_t is not None else 0),
+         LL(out_t.plane if out_t is not None else 0), stream_ptr())
+    return out, out_t
+
+
+def gemm(a, b, out=None, bias=None, alpha=1.0, beta=0.0, rowmap=0, hidden=0, M=None, N=None, K=None):
+    """out[M,N] = alpha * a @ b^T + bias + beta*out, a: SB16 (M,K), b: SB16 (N,K)."""
+    M = a.rows if M is None else M
+    N = b.rows if N is None else N
+    K = a.cols if K is None else K
+    if out is None:
+        out = torch.empty(M, N, dtype=torch.float32, device=a.buf.device)
+    assert out.dtype == torch.float32 and out.stride(1) == 1
+    call("gemm_sb16", a.buf, LL(a.ld), LL(a.plane), b.buf, LL(b.ld), LL(b.plane), out, LL(out.stride(0)), M, N, K, bias,
+         float(alpha), float(beta), rowmap, hidden, stream_ptr())
+    return out
+
+
+def colsum(a, rowmap=0, hidden=0, R=None):
+    R = a.rows if R is None else R
+    parts = lib().ss_colsum_parts(R)
+    partial = torch.empty(max(parts, 1) * a.cols, dtype=torch.float32, device=a.buf.device)
+    out = torch.empty(a.cols, dtype=torch.float32, device=a.buf.device)
+    call("colsum_sb16", a.buf, LL(a.ld), LL(a.plane), R, a.cols, partial, out, rowmap, hidden, stream_ptr())
+    return out

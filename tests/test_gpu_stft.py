@@ -1,0 +1,112 @@
+"""Parity of the CUDA STFT / masked iSTFT (through the C ABI) against oracle/stft_oracle.py.
+Tolerances: features 1e-4 relative (north_star); wavs +-1 LSB of int16."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import stft_oracle as so
+from ssb200 import ops, synth
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+
+
+def _corpus(seed, lens, S=2):
+    sigs = []
+    for i, n in enumerate(lens):
+        mix, srcs = synth.mixture(seed * 100 + i, n, S)
+        sigs.append(mix)
+    return sigs
+
+
+def _rel(a, b):
+    a = np.asarray(a, dtype=np.complex128 if np.iscomplexobj(a) else np.float64)
+    return float(np.abs(a - b).max() / np.abs(b).max()), float(np.linalg.norm(a - b) / np.linalg.norm(b))
+
+
+@pytest.mark.parametrize("n_fft,hop", [(512, 128), (256, 64)])
+@pytest.mark.parametrize("complex_out", [False, True])
+@pytest.mark.parametrize("layout_tf", [False, True])
+def test_stft_matches_oracle(n_fft, hop, complex_out, layout_tf):
+    # ragged lengths incl. the minimum legal one (n_fft//2+1), non multiples of hop, one exact tile boundary
+    lens = [32000, n_fft // 2 + 1, 31 * hop, 32 * hop, 33 * hop + 7, 4000, 12345]
+    sigs = _corpus(3, lens)
+    rag = ops.Ragged(lens, n_fft, hop, DEV)
+    flat = torch.from_numpy(np.concatenate(sigs)).to(DEV)
+    out = ops.stft(flat, rag, complex_out=complex_out, layout_tf=layout_tf)
+    torch.cuda.synchronize()
+    for u, v in enumerate(ops.stft_views(out, rag, layout_tf)):
+        ref = so.stft(sigs[u], n_fft, hop) if complex_out else so.stft_mag(sigs[u], n_fft, hop)
+        got = v.cpu().numpy()
+        if layout_tf:
+            got = got.T
+        assert got.shape == ref.shape == (n_fft // 2 + 1, 1 + lens[u] // hop)
+        mx, l2 = _rel(got, ref)
+        assert mx <= 1e-4 and l2 <= 1e-4, (u, mx, l2)
+        assert mx <= 2e-6, (u, mx)      # what fp32 arithmetic actually achieves
+
+
+def test_stft_linearity_full_size():
+    # size-independent property at a BASELINE-sized shard: STFT(a*x + b*y) == a*STFT(x) + b*STFT(y)
+    rng = np.random.default_rng(0)
+    lens = rng.integers(16000, 80001, size=64)
+    rag = ops.Ragged(lens, 256, 64, DEV)
+    n = int(rag.sig_off[-1])
+    g = torch.Generator(device=DEV).manual_seed(1)
+    x = torch.rand(n, device=DEV, generator=g) - 0.5
+    y = torch.rand(n, device=DEV, generator=g) - 0.5
+    X = ops.stft(x, rag, complex_out=True)
+    Y = ops.stft(y, rag, complex_out=True)
+    Z = ops.stft(0.25 * x - 1.5 * y, rag, complex_out=True)
+    err = (Z - (0.25 * X - 1.5 * Y)).abs().max() / Z.abs().max()
+    assert float(err) <= 1e-5
+
+
+@pytest.mark.parametrize("n_fft,hop", [(512, 128), (256, 64)])
+@pytest.mark.parametrize("layout_tf", [False, True])
+def test_masked_istft_matches_oracle(n_fft, hop, layout_tf):
+    lens = [16000, 29 * hop, 28 * hop + 1, 5000, n_fft + 3, n_fft // 2 + hop]
+    S = 2
+    F = n_fft // 2 + 1
+    rng = np.random.default_rng(5)
+    sigs = _corpus(7, lens)
+    rag = ops.Ragged(lens, n_fft, hop, DEV)
+    specs = [so.stft(s, n_fft, hop) for s in sigs]
+    masks = [rng.uniform(0, 1, size=(S, F, sp.shape[1])).astype(np.float32) for sp in specs]
+    if layout_tf:
+        spec_flat = np.concatenate([sp.T.ravel() for sp in specs])
+        mask_flat = np.concatenate([m.transpose(0, 2, 1).ravel() for m in masks])
+    else:
+        spec_flat = np.concatenate([sp.ravel() for sp in specs])
+        mask_flat = np.concatenate([m.ravel() for m in masks])
+    d_spec, d_mask = torch.from_numpy(spec_flat).to(DEV), torch.from_numpy(mask_flat).to(DEV)
+    wav, off = ops.istft_masked(d_spec, d_mask, rag, S, layout_tf=layout_tf)
+    wavf, _ = ops.istft_masked(d_spec, d_mask, rag, S, layout_tf=layout_tf, out_f32=True)
+    wav, wavf = wav.cpu().numpy(), wavf.cpu().numpy()
+    for u in range(len(lens)):
+        L = hop * (specs[u].shape[1] - 1)
+        for s in range(S):
+            ref = so.masked_istft_int16(specs[u], masks[u][s], hop)
+            reff = so.istft(specs[u] * masks[u][s], hop)
+            got = wav[off[u] + s * L: off[u] + (s + 1) * L]
+            gotf = wavf[off[u] + s * L: off[u] + (s + 1) * L]
+            assert got.shape == ref.shape
+            assert np.abs(gotf - reff).max() <= 2e-6 * max(1e-3, np.abs(reff).max()), (u, s)
+            assert np.abs(got.astype(np.int32) - ref.astype(np.int32)).max() <= 1, (u, s)
+            assert (got == ref).mean() >= 0.99
+
+
+def test_stft_istft_roundtrip_full_size():
+    # unmasked round trip (mask == 1) reproduces the interior of the signal; cfg5-sized utterances (16 kHz, 20 s)
+    lens = [320000] * 4 + [319871, 160000]
+    rag = ops.Ragged(lens, 512, 128, DEV)
+    g = torch.Generator(device=DEV).manual_seed(2)
+    x = (torch.rand(int(rag.sig_off[-1]), device=DEV, generator=g) - 0.5)
+    X = ops.stft(x, rag, complex_out=True)
+    ones = torch.ones(rag.total_frames * rag.F, device=DEV)
+    y, off = ops.istft_masked(X, ones, rag, 1, out_f32=True)
+    for u, n in enumerate(lens):
+        L = int(rag.L[u])
+        a = x[int(rag.sig_off[u]):int(rag.sig_off[u]) + L]
+        b = y[int(off[u]):int(off[u]) + L]
+        assert float((a - b).abs().max()) <= 5e-6
