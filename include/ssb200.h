@@ -94,6 +94,48 @@ int ss_pit_loss_bwd(const float* z, long long ldz, const float* mix, const float
                     const float* dmask_extra, void* dz, long long ld_dz, long long dz_plane, void* dzT,
                     long long ld_dzT, long long dzT_plane, void* stream);
 
+/* PackedSequence data [sum_t n_t][c_src] (columns c_off..c_off+C) -> time-major padded [T][B][C], zeros where
+ * absent; toff[T+1] = prefix sums of batch_sizes.  Replaces pad_packed_sequence (archs/uPIT.py:135,165,178). */
+int ss_unpack(const float* packed, const long long* toff, int T, int B, int C, int c_src, int c_off, float* out,
+              void* stream);
+
+/* ---- K2b/K2c: persistent bidirectional LSTM recurrence.  Replaces the sequential part of the cuDNN LSTM
+ * behind nn.LSTM(..., bidirectional=True) at archs/uPIT.py:115,132 / archs/RSH.py:155,172 (PackedSequence
+ * semantics via lens[], descending) and of its backward (steps/train_qsub.py:120) ----
+ * Gate columns are interleaved: column dir*4H + 4*u + gate (gate order i,f,g,o as torch).
+ * fwd: gx [T*B][8H] = x W_ih^T + b_ih + b_hh (both directions) is overwritten with the activated gates;
+ *      whh_r sb16 [8H][H] (rows dir*4H+4u+gate); h0,c0,hn,cn [2][B][H]; out sb16 [T*B][2H] (zero at t>=len_b);
+ *      training extras (all or none): outT, hprevT sb16 [2H][ldT] (transposed outputs / pre-step states), cs.
+ *      ws: ss_lstm_ws_bytes(B,H) bytes.
+ * bwd: dout [T*B][2H] gradient wrt out; whhT sb16 [2H][4H] (row dir*H+j, column 4u+gate);
+ *      dG sb16 [T*B][8H] and dGT sb16 [8H][ldT] gate pre-activation gradients (zero at t>=len_b);
+ *      dhn,dcn (optional) gradient wrt (hn,cn); dh0,dc0 (optional) gradient wrt (h0,c0). */
+long long ss_lstm_ws_bytes(int B, int H);
+int ss_lstm_fwd(float* gx, const void* whh_r, long long whh_ld, long long whh_plane, const float* h0, const float* c0,
+                const int* lens, void* out, long long out_plane, void* outT, void* hprevT, long long ldT,
+                long long outT_plane, float* cs, float* hn, float* cn, void* ws, int T, int B, int H, void* stream);
+int ss_lstm_bwd(const float* gates, const float* cs, const float* c0, const float* dout, const float* dhn,
+                const float* dcn, const int* lens, const void* whhT, long long whhT_ld, long long whhT_plane, void* dG,
+                long long dG_plane, void* dGT, long long ldT, long long dGT_plane, float* dh0, float* dc0, void* ws,
+                int T, int B, int H, void* stream);
+
+/* ---- K3/K4 glue: BatchNorm1d(2H) over all T*B rows (padding included, archs/uPIT.py:119,138) folded into the
+ * head Linear (archs/uPIT.py:117,141), and its backward ----
+ * coef[5][C] = {s = gamma*rstd, shift = beta - mean*s, mean, rstd, biased var}; training updates the running
+ * stats (momentum 0.1, unbiased var), eval reads them.  partial: 2*ss_bn_parts(R)*C floats.
+ * ss_head_fold_bias: bout[o] = b[o] + sum_c W[o][c]*shift[c]  (the folded weight is ss_split(W, col_scale=s)).
+ * ss_bn_bwd: dy [R][C] (gradient wrt the BN output) is replaced in place by the gradient wrt x; also dgamma,
+ * dbeta; bwd: 2*C floats scratch.  ss_head_dw_fix: dW = s*(G - mean*dsum) + beta*dsum with G = dz^T x. */
+int ss_bn_parts(int R);
+int ss_bn_stats(const void* x, long long ld, long long plane, int R, int C, const float* gamma, const float* beta,
+                float eps, float momentum, int training, float* running_mean, float* running_var, float* partial,
+                float* coef, void* stream);
+int ss_head_fold_bias(const float* W, const float* b, const float* coef, int O, int C, float* bout, void* stream);
+int ss_bn_bwd(float* dy, const void* x, long long ld, long long plane, int R, int C, const float* coef, int training,
+              float* partial, float* dgamma, float* dbeta, float* bwd, void* stream);
+int ss_head_dw_fix(const float* G, const float* dsum, const float* coef, const float* beta, int O, int C, float* dW,
+                   void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,178 @@
+// K3/K4 glue: BatchNorm1d statistics over all (t,b) rows -- padding included, as the reference does
+// (archs/uPIT.py:119,138) -- folded into the head Linear (archs/uPIT.py:117,141) so that the head is one GEMM,
+// and the matching backward reductions.  x is the layer-2 BLSTM output as sb16 [R = T*B][C = 2H].
+#include "../../include/ssb200.h"
+#include "common.cuh"
+
+namespace ssb {
+
+constexpr int BN_ROWS = 256;
+
+// partial[blk][0][c] = sum_r x, partial[blk][1][c] = sum_r x^2   (if dy == null)
+// partial[blk][0][c] = sum_r dy, partial[blk][1][c] = sum_r dy*x (if dy != null)
+__global__ void __launch_bounds__(256) bn_partial_kernel(const __nv_bfloat16* __restrict__ x, long long ld,
+                                                         long long plane, const float* __restrict__ dy, int R, int C,
+                                                         float* __restrict__ partial) {
+  const int c = blockIdx.x * 256 + threadIdx.x;
+  if (c >= C) return;
+  const int r0 = blockIdx.y * BN_ROWS, r1 = min(R, r0 + BN_ROWS);
+  float a = 0.0f, b = 0.0f;
+  for (int r = r0; r < r1; ++r) {
+    const long long o = (long long)r * ld + c;
+    const float v = join_bf16(x[o], x[o + plane]);
+    if (dy) {
+      const float g = dy[(long long)r * C + c];
+      a += g;
+      b += g * v;
+    } else {
+      a += v;
+      b += v * v;
+    }
+  }
+  partial[((long long)blockIdx.y * 2 + 0) * C + c] = a;
+  partial[((long long)blockIdx.y * 2 + 1) * C + c] = b;
+}
+
+// coef layout (5 x C): [0] scale s = gamma*rstd, [1] shift = beta - mean*s, [2] mean, [3] rstd, [4] var (biased)
+__global__ void __launch_bounds__(256) bn_stats_final_kernel(const float* __restrict__ partial, int parts, int R, int C,
+                                                             const float* __restrict__ gamma,
+                                                             const float* __restrict__ beta, float eps, float momentum,
+                                                             int training, float* __restrict__ running_mean,
+                                                             float* __restrict__ running_var, float* __restrict__ coef) {
+  const int c = blockIdx.x * 256 + threadIdx.x;
+  if (c >= C) return;
+  double mean, var;
+  if (training) {
+    double s = 0.0, s2 = 0.0;
+    for (int p = 0; p < parts; ++p) {
+      s += (double)partial[((long long)p * 2 + 0) * C + c];
+      s2 += (double)partial[((long long)p * 2 + 1) * C + c];
+    }
+    mean = s / R;
+    var = s2 / R - mean * mean;
+    if (var < 0.0) var = 0.0;
+    const double unb = R > 1 ? var * ((double)R / (R - 1.0)) : var;
+    running_mean[c] = (float)((1.0 - momentum) * running_mean[c] + momentum * mean);
+    running_var[c] = (float)((1.0 - momentum) * running_var[c] + momentum * unb);
+  } else {
+    mean = running_mean[c];
+    var = running_var[c];
+  }
+  const double rstd = 1.0 / sqrt(var + (double)eps);
+  const double s = gamma[c] * rstd;
+  coef[0 * C + c] = (float)s;
+  coef[1 * C + c] = (float)(beta[c] - mean * s);
+  coef[2 * C + c] = (float)mean;
+  coef[3 * C + c] = (float)rstd;
+  coef[4 * C + c] = (float)var;
+}
+
+// b'[o] = b[o] + sum_c W[o][c] * shift[c]      (one warp per output row)
+__global__ void __launch_bounds__(256) head_fold_bias_kernel(const float* __restrict__ W, const float* __restrict__ b,
+                                                             const float* __restrict__ shift, int O, int C,
+                                                             float* __restrict__ bout) {
+  const int o = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  if (o >= O) return;
+  float acc = 0.0f;
+  for (int c = lane; c < C; c += 32) acc += W[(long long)o * C + c] * shift[c];
+  acc = warp_sum(acc);
+  if (lane == 0) bout[o] = b[o] + acc;
+}
+
+// from partial sums of dy and dy*x: dgamma, dbeta and the coefficients of dx = s*dy + bc*(x - mean) + cc
+// bwd layout (2 x C): [0] bc, [1] cc
+__global__ void __launch_bounds__(256) bn_bwd_final_kernel(const float* __restrict__ partial, int parts, int R, int C,
+                                                           const float* __restrict__ coef, int training,
+                                                           float* __restrict__ dgamma, float* __restrict__ dbeta,
+                                                           float* __restrict__ bwd) {
+  const int c = blockIdx.x * 256 + threadIdx.x;
+  if (c >= C) return;
+  double a = 0.0, bx = 0.0;
+  for (int p = 0; p < parts; ++p) {
+    a += (double)partial[((long long)p * 2 + 0) * C + c];
+    bx += (double)partial[((long long)p * 2 + 1) * C + c];
+  }
+  const double s = coef[0 * C + c], mean = coef[2 * C + c], rstd = coef[3 * C + c];
+  const double dg = (bx - mean * a) * rstd;      // sum dy * xhat
+  dgamma[c] = (float)dg;
+  dbeta[c] = (float)a;
+  if (training) {
+    bwd[0 * C + c] = (float)(-s * rstd * dg / R);
+    bwd[1 * C + c] = (float)(-s * a / R);
+  } else {
+    bwd[0 * C + c] = 0.0f;
+    bwd[1 * C + c] = 0.0f;
+  }
+}
+
+// in place: dy[r][c] <- s*dy + bc*(x - mean) + cc
+__global__ void __launch_bounds__(256) bn_bwd_apply_kernel(float* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
+                                                           long long ld, long long plane, long long n, int C,
+                                                           const float* __restrict__ coef,
+                                                           const float* __restrict__ bwd) {
+  for (long long e = (long long)blockIdx.x * 256 + threadIdx.x; e < n; e += (long long)gridDim.x * 256) {
+    const long long r = e / C;
+    const int c = (int)(e - r * C);
+    const long long o = r * ld + c;
+    const float v = join_bf16(x[o], x[o + plane]);
+    dy[e] = coef[c] * dy[e] + bwd[c] * (v - coef[2 * C + c]) + bwd[C + c];
+  }
+}
+
+// dW[o][c] = s_c * (G[o][c] - mean_c * dsum[o]) + beta_c * dsum[o]   with G = dz^T x
+__global__ void __launch_bounds__(256) head_dw_fix_kernel(const float* __restrict__ G, const float* __restrict__ dsum,
+                                                          const float* __restrict__ coef,
+                                                          const float* __restrict__ beta, int O, int C,
+                                                          float* __restrict__ dW) {
+  const long long n = (long long)O * C;
+  for (long long e = (long long)blockIdx.x * 256 + threadIdx.x; e < n; e += (long long)gridDim.x * 256) {
+    const int o = (int)(e / C), c = (int)(e - (long long)o * C);
+    dW[e] = coef[c] * (G[e] - coef[2 * C + c] * dsum[o]) + beta[c] * dsum[o];
+  }
+}
+
+}  // namespace ssb
+
+extern "C" int ss_bn_parts(int R) { return ssb::cdiv(R, ssb::BN_ROWS); }
+
+extern "C" int ss_bn_stats(const void* x, long long ld, long long plane, int R, int C, const float* gamma,
+                           const float* beta, float eps, float momentum, int training, float* running_mean,
+                           float* running_var, float* partial, float* coef, void* stream) {
+  using namespace ssb;
+  cudaStream_t st = (cudaStream_t)stream;
+  const int parts = cdiv(R, BN_ROWS);
+  if (training)
+    bn_partial_kernel<<<dim3(cdiv(C, 256), parts), 256, 0, st>>>((const __nv_bfloat16*)x, ld, plane, nullptr, R, C, partial);
+  bn_stats_final_kernel<<<cdiv(C, 256), 256, 0, st>>>(partial, parts, R, C, gamma, beta, eps, momentum, training,
+                                                      running_mean, running_var, coef);
+  return check_launch("ss_bn_stats");
+}
+
+extern "C" int ss_head_fold_bias(const float* W, const float* b, const float* coef, int O, int C, float* bout,
+                                 void* stream) {
+  using namespace ssb;
+  head_fold_bias_kernel<<<cdiv(O, 8), 256, 0, (cudaStream_t)stream>>>(W, b, coef + C, O, C, bout);
+  return check_launch("ss_head_fold_bias");
+}
+
+extern "C" int ss_bn_bwd(float* dy, const void* x, long long ld, long long plane, int R, int C, const float* coef,
+                         int training, float* partial, float* dgamma, float* dbeta, float* bwd, void* stream) {
+  using namespace ssb;
+  cudaStream_t st = (cudaStream_t)stream;
+  const int parts = cdiv(R, BN_ROWS);
+  bn_partial_kernel<<<dim3(cdiv(C, 256), parts), 256, 0, st>>>((const __nv_bfloat16*)x, ld, plane, dy, R, C, partial);
+  bn_bwd_final_kernel<<<cdiv(C, 256), 256, 0, st>>>(partial, parts, R, C, coef, training, dgamma, dbeta, bwd);
+  const long long n = (long long)R * C;
+  bn_bwd_apply_kernel<<<(int)min((long long)148 * 8, (n + 255) / 256), 256, 0, st>>>(dy, (const __nv_bfloat16*)x, ld, plane,
+                                                                                    n, C, coef, bwd);
+  return check_launch("ss_bn_bwd");
+}
+
+extern "C" int ss_head_dw_fix(const float* G, const float* dsum, const float* coef, const float* beta, int O, int C,
+                              float* dW, void* stream) {
+  using namespace ssb;
+  const long long n = (long long)O * C;
+  head_dw_fix_kernel<<<(int)min((long long)148 * 8, (n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(G, dsum, coef, beta,
+                                                                                                   O, C, dW);
+  return check_launch("ss_head_dw_fix");
+}

@@ -79,7 +79,32 @@ __global__ void __launch_bounds__(256) colsum_final_kernel(const float* __restri
   out[oc] = (float)acc;
 }
 
+// PackedSequence data [sum_t n_t][C] (row of (t,b) = toff[t] + b, present iff b < n_t = toff[t+1]-toff[t])
+// -> time-major padded [T][B][C], zero where absent.  Replaces pad_packed_sequence (archs/uPIT.py:135,165,178).
+__global__ void __launch_bounds__(256) unpack_kernel(const float* __restrict__ packed, const long long* __restrict__ toff,
+                                                     int T, int B, int C, int c_src, int c_off,
+                                                     float* __restrict__ out) {
+  const long long n = (long long)T * B * C;
+  for (long long e = (long long)blockIdx.x * 256 + threadIdx.x; e < n; e += (long long)gridDim.x * 256) {
+    const long long r = e / C;
+    const int c = (int)(e - r * C);
+    const int t = (int)(r / B), b = (int)(r - (long long)t * B);
+    const long long o = toff[t];
+    out[e] = (b < (int)(toff[t + 1] - o)) ? packed[(o + b) * c_src + c_off + c] : 0.0f;
+  }
+}
+
 }  // namespace ssb
+
+extern "C" int ss_unpack(const float* packed, const long long* toff, int T, int B, int C, int c_src, int c_off,
+                         float* out, void* stream) {
+  using namespace ssb;
+  const long long n = (long long)T * B * C;
+  if (n == 0) return 0;
+  unpack_kernel<<<(int)min((long long)148 * 8, (n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(packed, toff, T, B, C, c_src,
+                                                                                              c_off, out);
+  return check_launch("ss_unpack");
+}
 
 extern "C" int ss_split(const float* in, long long ld_in, int R, int C, int rowperm, int hidden,
                         const float* col_scale, void* out, long long ld_out, long long out_plane, void* outT,
