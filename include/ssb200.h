@@ -94,6 +94,15 @@ int ss_pit_loss_bwd(const float* z, long long ldz, const float* mix, const float
                     const float* dmask_extra, void* dz, long long ld_dz, long long dz_plane, void* dzT,
                     long long ld_dzT, long long dzT_plane, void* stream);
 
+/* out[R][C] = sigmoid(z[R][ldz]) -- F.sigmoid of the head output (archs/uPIT.py:144) */
+int ss_sigmoid(const float* z, long long ldz, int R, int C, float* out, void* stream);
+
+/* y = a*x + b*y (b == 0: y need not be initialised) */
+int ss_axpby(const float* x, float* y, long long n, float a, float b, void* stream);
+
+/* out[blk*4H + 4u+gate] = b_ih[blk*4H + gate*H+u] + b_hh[same]: interleaved bias of the x-projection GEMM. */
+int ss_bias_prep(const float* b_ih, const float* b_hh, int n, int hidden, float* out, void* stream);
+
 /* PackedSequence data [sum_t n_t][c_src] (columns c_off..c_off+C) -> time-major padded [T][B][C], zeros where
  * absent; toff[T+1] = prefix sums of batch_sizes.  Replaces pad_packed_sequence (archs/uPIT.py:135,165,178). */
 int ss_unpack(const float* packed, const long long* toff, int T, int B, int C, int c_src, int c_off, float* out,

@@ -94,7 +94,55 @@ __global__ void __launch_bounds__(256) unpack_kernel(const float* __restrict__ p
   }
 }
 
+// out[blk*4H + 4u+g] = b_ih[blk*4H + g*H+u] + b_hh[...]   (interleaved LSTM bias for the x-projection GEMM)
+__global__ void __launch_bounds__(256) bias_prep_kernel(const float* __restrict__ b_ih, const float* __restrict__ b_hh,
+                                                        int n, int hidden, float* __restrict__ out) {
+  const int i = blockIdx.x * 256 + threadIdx.x;
+  if (i >= n) return;
+  const int blk = i / (4 * hidden), w = i % (4 * hidden);
+  out[blk * 4 * hidden + 4 * (w % hidden) + w / hidden] = b_ih[i] + b_hh[i];
+}
+
+__global__ void __launch_bounds__(256) axpy_kernel(const float* __restrict__ x, float* __restrict__ y, long long n,
+                                                   float a, float b) {
+  for (long long e = (long long)blockIdx.x * 256 + threadIdx.x; e < n; e += (long long)gridDim.x * 256)
+    y[e] = a * x[e] + (b != 0.0f ? b * y[e] : 0.0f);
+}
+
+__global__ void __launch_bounds__(256) sigmoid_kernel(const float* __restrict__ z, long long ldz, long long R, int C,
+                                                      float* __restrict__ out) {
+  const long long n = R * C;
+  for (long long e = (long long)blockIdx.x * 256 + threadIdx.x; e < n; e += (long long)gridDim.x * 256) {
+    const long long r = e / C;
+    out[e] = sigmoidf_(z[r * ldz + (e - r * C)]);
+  }
+}
+
 }  // namespace ssb
+
+// out[R][C] (dense) = sigmoid(z[R][ldz])   -- F.sigmoid of the head output (archs/uPIT.py:144)
+extern "C" int ss_sigmoid(const float* z, long long ldz, int R, int C, float* out, void* stream) {
+  using namespace ssb;
+  const long long n = (long long)R * C;
+  if (n == 0) return 0;
+  sigmoid_kernel<<<(int)min((long long)148 * 8, (n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(z, ldz, R, C, out);
+  return check_launch("ss_sigmoid");
+}
+
+// y = a*x + b*y  (b == 0: plain scaled copy, y may be uninitialised)
+extern "C" int ss_axpby(const float* x, float* y, long long n, float a, float b, void* stream) {
+  using namespace ssb;
+  if (n == 0) return 0;
+  axpy_kernel<<<(int)min((long long)148 * 8, (n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(x, y, n, a, b);
+  return check_launch("ss_axpby");
+}
+
+extern "C" int ss_bias_prep(const float* b_ih, const float* b_hh, int n, int hidden, float* out, void* stream) {
+  using namespace ssb;
+  SS_REQUIRE(hidden > 0 && n % (4 * hidden) == 0, "ss_bias_prep: n must be a multiple of 4*hidden");
+  bias_prep_kernel<<<cdiv(n, 256), 256, 0, (cudaStream_t)stream>>>(b_ih, b_hh, n, hidden, out);
+  return check_launch("ss_bias_prep");
+}
 
 extern "C" int ss_unpack(const float* packed, const long long* toff, int T, int B, int C, int c_src, int c_off,
                          float* out, void* stream) {
