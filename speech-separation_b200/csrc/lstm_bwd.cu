@@ -199,10 +199,12 @@ lstm_bwd_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
         l4[0] = reinterpret_cast<uint4*>(lo)[0];
         l4[1] = reinterpret_cast<uint4*>(lo)[1];
       }
-      fence_proxy_async();
-      __threadfence();
       asm volatile("bar.sync 1, %0;" ::"n"(32 * LB_EPI_WARPS) : "memory");
-      if (threadIdx.x == 64) red_release_add(counter, 1u);
+      if (threadIdx.x == 64) {
+        __threadfence();
+        fence_proxy_async();
+        red_release_add(counter, 1u);
+      }
       if (row_ok && in_range) {
 #pragma unroll
         for (int i = 0; i < 16; ++i) {

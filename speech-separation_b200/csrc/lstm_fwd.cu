@@ -4,21 +4,30 @@
 //   * the reverse direction starts at each utterance's own last frame, from (h0, c0);
 //   * outputs at t >= len_b are zero, (h_n, c_n) are the states after each utterance's last processed frame.
 // Each CTA owns LF_U hidden units of one direction with their 4 gates interleaved (column 4*u+gate), keeps its
-// slice of W_hh (split-bf16) resident in shared memory, and per step computes
-//   D[b][4u+g] = sum_k h_{prev}[b][k] * W_hh[g*H+u][k]      (tcgen05, fp32 accumulate in TMEM)
-// from h_prev streamed by TMA out of a small ping-pong buffer that all CTAs of the direction publish into;
-// a gpu-scope release/acquire counter per direction is the per-step grid barrier.
+// slice of W_hh (split-bf16, hi rows then lo rows) resident in shared memory, and per step computes
+//   D[b][4u+g] = sum_k h_prev[b][k] * W_hh[g*H+u][k]      (tcgen05, fp32 accumulate in TMEM)
+// from h_prev (split-bf16) streamed by bulk async copies out of a small ping-pong buffer that all CTAs of the
+// direction publish into; a gpu-scope release/acquire counter per direction is the per-step grid barrier.
+//
+// tcgen05.mma costs >= ~53 cycles per instruction whatever its shape (tools/microbench/mma_rate.cu), so the
+// three split-bf16 products are folded into ONE instruction per 16-wide k-step: for B <= 64 the A operand is the
+// 128-row stack [h_hi; h_lo] and the B operand the 96-row stack [W_hi; W_lo]; the four 64x48 quadrants of D
+// (hi*hi, hi*lo, lo*hi, lo*lo) are summed in the epilogue.
+#include <stdlib.h>
+
 #include "../../include/ssb200.h"
 #include "common.cuh"
 
 namespace ssb {
 
 constexpr int LF_U = 12;                    // hidden units per CTA
-constexpr int LF_N = 4 * LF_U;              // gate columns per CTA (MMA N)
+constexpr int LF_N = 4 * LF_U;              // gate columns per CTA
 constexpr int LF_EPI_WARPS = 12;            // 4 TMEM lane quadrants x 3 column groups of 4 units
-constexpr int LF_THREADS = 64 + 32 * LF_EPI_WARPS;
-constexpr int LF_WCHUNK = 2 * LF_N * 128;   // one 64-wide K chunk of the W slice, both planes
+constexpr int LF_THREADS = 32 * LF_EPI_WARPS + 64;
+constexpr int LF_WCHUNK = 2 * LF_N * 128;   // one 64-wide K chunk of the W slice: [hi 48 rows][lo 48 rows] x 128 B
 constexpr int LF_MAXKC = 10;                // H <= 640
+constexpr int LF_XPITCH = 52;               // floats per row of the lo-row exchange buffer
+constexpr int LF_TMEM = 128;
 
 struct LstmFwdParams {
   float* gx;                 // [T*B][8H] in: x-projection + biases (interleaved gate columns); out: activated gates
@@ -33,21 +42,30 @@ struct LstmFwdParams {
   float* cs;                 // [T*B][2H] or null
   float* hn;                 // [2][B][H]
   float* cn;
-  __nv_bfloat16* hbuf;       // [slot 2][dir 2][plane 2][R][H]
+  __nv_bfloat16* hbuf;       // [rep][slot 2][dir 2][kc][plane 2][R][64], rows pre-swizzled (SWIZZLE_128B)
+  int REP, EXP;
   unsigned int* sync;        // [2]
   int T, B, H, R, NC, KC, NS;
+  long long* dbg;            // optional clock64 trace of CTA 0: [step][32]
 };
 
+#define LF_STAMP(slot)                                               \
+  do {                                                               \
+    if (p.dbg && blockIdx.x == 0) p.dbg[s * 32 + (slot)] = clock64(); \
+  } while (0)
+
 __global__ void __launch_bounds__(LF_THREADS, 1)
-lstm_fwd_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUtensorMap tmH, LstmFwdParams p) {
+lstm_fwd_kernel(const __grid_constant__ CUtensorMap tmW, LstmFwdParams p) {
   extern __shared__ unsigned char smem_raw[];
   unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   const int stage_bytes = 2 * p.R * 128;
+  const bool stacked = p.R == 64;                              // A operand = [h_hi; h_lo] as one 128-row tile
   unsigned char* ring = smem;                                  // NS stages of h_prev chunks
-  unsigned char* wsm = smem + p.NS * stage_bytes;              // KC chunks of the W slice (also absorbs M=128 over-read)
-  uint64_t* full = reinterpret_cast<uint64_t*>(wsm + p.KC * LF_WCHUNK);
-  uint64_t* empty = full + 4;
-  uint64_t* accum_full = empty + 4;
+  unsigned char* wsm = smem + p.NS * stage_bytes;              // KC chunks of the W slice
+  float* xbuf = reinterpret_cast<float*>(wsm + p.KC * LF_WCHUNK);          // [64][LF_XPITCH] lo-row partial sums
+  uint64_t* full = reinterpret_cast<uint64_t*>(xbuf + 64 * LF_XPITCH);
+  uint64_t* empty = full + 8;
+  uint64_t* accum_full = empty + 8;
   uint64_t* wfull = accum_full + 1;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(wfull + 1);
 
@@ -59,7 +77,6 @@ lstm_fwd_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
 
   if (threadIdx.x == 0) {
     tma_prefetch_desc(&tmW);
-    tma_prefetch_desc(&tmH);
     for (int s = 0; s < p.NS; ++s) {
       mbar_init(&full[s], 1);
       mbar_init(&empty[s], 1);
@@ -68,67 +85,73 @@ lstm_fwd_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
     mbar_init(wfull, 1);
     fence_barrier_init();
   }
-  if (warp == 1) tmem_alloc<64>(tmem_slot);
+  // roles: warps 0..11 epilogue, warp 12 producer, warp 13 MMA issuer
+  constexpr int W_PROD = LF_EPI_WARPS, W_MMA = LF_EPI_WARPS + 1;
+  if (warp == W_MMA) tmem_alloc<LF_TMEM>(tmem_slot);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_d = *tmem_slot;
 
-  if (warp == 0) {
+  if (warp == W_PROD) {
     if (lane == 0) {
       mbar_arrive_expect_tx(wfull, p.KC * LF_WCHUNK);
       for (int kc = 0; kc < p.KC; ++kc) tma_load_3d(wsm + kc * LF_WCHUNK, &tmW, wfull, kc * 64, dir * 4 * H + 4 * u0, 0);
+      const long long blk = 2LL * p.R * 64;                    // elements per (slot,dir,kc) block
       int it = 0;
       for (int s = 0; s < T; ++s) {
         const unsigned int need = (unsigned int)p.NC * (unsigned int)(s + 1);
+        LF_STAMP(0);
         while (ld_acquire(counter) < need) {
         }
+        LF_STAMP(1);
         fence_proxy_async();
+        const __nv_bfloat16* src = p.hbuf + (((long long)(cta % p.REP) * 2 + (s & 1)) * 2 + dir) * p.KC * blk;
         for (int kc = 0; kc < p.KC; ++kc, ++it) {
           const int st = it % p.NS, ph = (it / p.NS) & 1;
           mbar_wait(&empty[st], ph ^ 1);
           mbar_arrive_expect_tx(&full[st], stage_bytes);
-          asm volatile(
-              "cp.async.bulk.tensor.4d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];" ::
-                  "r"(smem_u32(ring + st * stage_bytes)), "l"((uint64_t)&tmH), "r"(smem_u32(&full[st])), "r"(kc * 64), "r"(0),
-              "r"(0), "r"((s & 1) * 2 + dir)
-              : "memory");
+          bulk_load(ring + st * stage_bytes, src + kc * blk, stage_bytes, &full[st]);
         }
+        LF_STAMP(2);
       }
     }
-  } else if (warp == 1) {
+  } else if (warp == W_MMA) {
     if (lane == 0) {
-      constexpr uint32_t idesc = umma_idesc_bf16(128, LF_N);
+      const uint32_t idesc96 = umma_idesc_bf16(128, 2 * LF_N), idesc48 = umma_idesc_bf16(128, LF_N);
+      const uint64_t a_base = umma_desc_sw128(smem_u32(ring)), b_base = umma_desc_sw128(smem_u32(wsm));
+      const uint32_t a_stage = stage_bytes >> 4, a_lo_off = (p.R * 128) >> 4;
       mbar_wait(wfull, 0);
       int it = 0;
       for (int s = 0; s < T; ++s) {
         for (int kc = 0; kc < p.KC; ++kc, ++it) {
           const int st = it % p.NS, ph = (it / p.NS) & 1;
           mbar_wait(&full[st], ph);
+          LF_STAMP(kc == 0 ? 3 : 10 + kc);
           tc_fence_after();
-          const uint32_t a_hi = smem_u32(ring + st * stage_bytes), a_lo = a_hi + p.R * 128;
-          const uint32_t b_hi = smem_u32(wsm + kc * LF_WCHUNK), b_lo = b_hi + LF_N * 128;
+          const uint64_t da = a_base + (uint32_t)st * a_stage;
+          const uint64_t db = b_base + (uint32_t)kc * (LF_WCHUNK >> 4);
           const int ksteps = min(4, (H - kc * 64 + 15) / 16);
-          for (int k = 0; k < ksteps; ++k) {
-            const uint32_t ko = k * 32;
-            const uint64_t dah = umma_desc_sw128(a_hi + ko), dal = umma_desc_sw128(a_lo + ko);
-            const uint64_t dbh = umma_desc_sw128(b_hi + ko), dbl = umma_desc_sw128(b_lo + ko);
-            umma_bf16(tmem_d, dal, dbh, idesc, (kc | k) ? 1u : 0u);
-            umma_bf16(tmem_d, dah, dbl, idesc, 1u);
-            umma_bf16(tmem_d, dah, dbh, idesc, 1u);
+          if (stacked) {
+            for (int k = 0; k < ksteps; ++k) umma_bf16(tmem_d, da + 2 * k, db + 2 * k, idesc96, (kc | k) ? 1u : 0u);
+          } else {
+            for (int k = 0; k < ksteps; ++k) {
+              umma_bf16(tmem_d, da + 2 * k, db + 2 * k, idesc96, (kc | k) ? 1u : 0u);          // h_hi x [W_hi; W_lo]
+              umma_bf16(tmem_d, da + a_lo_off + 2 * k, db + 2 * k, idesc48, 1u);               // h_lo x W_hi
+            }
           }
           umma_commit(&empty[st]);
         }
         umma_commit(accum_full);
+        LF_STAMP(4);
       }
     }
   } else {
-    const int ew = warp - 2;
-    const int q = warp & 3, cg = ew >> 2;
-    const int b = q * 32 + lane;
-    const int ul = cg * 4;                                     // first of this thread's 4 units within the CTA
-    const int ug = u0 + ul;                                    // ... within the direction
-    const bool row_ok = b < B;
+    const int q = warp & 3, cg = warp >> 2;
+    const bool helper = stacked && q >= 2;                     // these warps own the h_lo rows of D
+    const int b = (stacked ? (q & 1) : q) * 32 + lane;
+    const int ug = u0 + cg * 4;                                // this thread's 4 units within the direction
+    const bool row_ok = !helper && b < B;
     const int len = row_ok ? p.lens[b] : 0;
     float h[4], c[4];
 #pragma unroll
@@ -136,22 +159,36 @@ lstm_fwd_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
       h[j] = row_ok ? p.h0[((long long)dir * B + b) * H + ug + j] : 0.0f;
       c[j] = row_ok ? p.c0[((long long)dir * B + b) * H + ug + j] : 0.0f;
     }
-    const long long hb_plane = (long long)p.R * H;
+    // byte offset of this thread's 4 units inside the pre-swizzled 128-byte row of K-chunk kc_w
+    const int kc_w = ug >> 6;
+    const int o = (ug & 63) * 2;
+    const long long row_off = (long long)b * 64 + ((((o >> 4) ^ (b & 7)) << 4) + (o & 15)) / 2;   // elements
+    const long long blk = 2LL * p.R * 64;
+    int dbg_s = 0;
     auto publish = [&](int slot) {
       if (row_ok) {
         __nv_bfloat16 hi[4], lo[4];
 #pragma unroll
         for (int j = 0; j < 4; ++j) split_bf16(h[j], hi[j], lo[j]);
-        __nv_bfloat16* dst = p.hbuf + ((long long)(slot * 2 + dir) * 2) * hb_plane + (long long)b * H + ug;
-        *reinterpret_cast<uint2*>(dst) = *reinterpret_cast<uint2*>(hi);
-        *reinterpret_cast<uint2*>(dst + hb_plane) = *reinterpret_cast<uint2*>(lo);
+        for (int r = 0; r < p.REP; ++r) {
+          __nv_bfloat16* dst = p.hbuf + ((((long long)r * 2 + slot) * 2 + dir) * p.KC + kc_w) * blk + row_off;
+          *reinterpret_cast<uint2*>(dst) = *reinterpret_cast<uint2*>(hi);
+          *reinterpret_cast<uint2*>(dst + p.R * 64) = *reinterpret_cast<uint2*>(lo);
+        }
       }
-      fence_proxy_async();
-      __threadfence();
+      // CTA barrier, then ONE thread releases at gpu scope (cumulative over the other threads' stores, the
+      // cooperative-groups grid.sync pattern) and orders them against the consumers' async-proxy reads.
+      if (threadIdx.x == 0 && p.dbg && blockIdx.x == 0) p.dbg[dbg_s * 32 + 20] = clock64();
       asm volatile("bar.sync 1, %0;" ::"n"(32 * LF_EPI_WARPS) : "memory");
-      if (threadIdx.x == 64) red_release_add(counter, 1u);
+      if (threadIdx.x == 0) {
+        if (p.dbg && blockIdx.x == 0) p.dbg[dbg_s * 32 + 21] = clock64();
+        if (p.dbg && blockIdx.x == 0) p.dbg[dbg_s * 32 + 22] = clock64();
+        red_release_add(counter, 1u);
+        if (p.dbg && blockIdx.x == 0) p.dbg[dbg_s * 32 + 23] = clock64();
+      }
     };
     publish(0);
+    const uint32_t trow = tmem_d + ((uint32_t)(q * 32) << 16);
     for (int s = 0; s < T; ++s) {
       const int t = dir ? (T - 1 - s) : s;
       const bool active = row_ok && t < len;
@@ -162,38 +199,63 @@ lstm_fwd_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
 #pragma unroll
         for (int j = 0; j < 4; ++j) g4[j] = gptr[j];
       }
-      mbar_wait(accum_full, s & 1);
+      // one warp polls the mbarrier; the others sleep on a hardware barrier
+      if (warp == 0) mbar_wait(accum_full, s & 1);
+      asm volatile("bar.sync 2, %0;" ::"n"(32 * LF_EPI_WARPS) : "memory");
+      if (threadIdx.x == 0) LF_STAMP(5);
       tc_fence_after();
-      float d[16];
-      tmem_ld16(tmem_d + ((uint32_t)(q * 32) << 16) + 16 * cg, d);
+      float d[16], e[16];
+      tmem_ld16(trow + 16 * cg, d);
+      tmem_ld16(trow + LF_N + 16 * cg, e);
       tc_fence_before();
+#pragma unroll
+      for (int i = 0; i < 16; ++i) d[i] += e[i];
+      if (stacked) {
+        float* xr = xbuf + (long long)b * LF_XPITCH + 16 * cg;
+        if (helper) {
+#pragma unroll
+          for (int i = 0; i < 4; ++i) reinterpret_cast<float4*>(xr)[i] = make_float4(d[4 * i], d[4 * i + 1], d[4 * i + 2], d[4 * i + 3]);
+        }
+        asm volatile("bar.sync 3, %0;" ::"n"(32 * LF_EPI_WARPS) : "memory");
+        if (!helper) {
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const float4 v = reinterpret_cast<const float4*>(xr)[i];
+            d[4 * i] += v.x; d[4 * i + 1] += v.y; d[4 * i + 2] += v.z; d[4 * i + 3] += v.w;
+          }
+        }
+      }
+      if (threadIdx.x == 0) LF_STAMP(8);
       float hout[4] = {0.0f, 0.0f, 0.0f, 0.0f};
       const float hp[4] = {h[0], h[1], h[2], h[3]};
       if (active) {
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
-          const float gi = sigmoidf_(d[4 * j + 0] + g4[j].x), gf = sigmoidf_(d[4 * j + 1] + g4[j].y);
-          const float gg = tanhf_(d[4 * j + 2] + g4[j].z), go = sigmoidf_(d[4 * j + 3] + g4[j].w);
+          const float gi = fsigmoid(d[4 * j + 0] + g4[j].x), gf = fsigmoid(d[4 * j + 1] + g4[j].y);
+          const float gg = ftanh(d[4 * j + 2] + g4[j].z), go = fsigmoid(d[4 * j + 3] + g4[j].w);
           c[j] = gf * c[j] + gi * gg;
-          h[j] = go * tanhf_(c[j]);
+          h[j] = go * ftanh(c[j]);
           hout[j] = h[j];
           g4[j] = make_float4(gi, gf, gg, go);
         }
       }
+      if (threadIdx.x == 0) LF_STAMP(6);
+      dbg_s = s;
       publish((s + 1) & 1);                                    // carried state for the next step (critical path first)
-      if (row_ok) {
+      if (threadIdx.x == 0) LF_STAMP(7);
+      if (row_ok && !(p.EXP & 4)) {
         if (active) {
 #pragma unroll
-          for (int j = 0; j < 4; ++j) gptr[j] = g4[j];
-          if (p.cs) *reinterpret_cast<float4*>(p.cs + row * (2LL * H) + dir * H + ug) = make_float4(c[0], c[1], c[2], c[3]);
+          for (int j = 0; j < 4; ++j) __stcs(gptr + j, g4[j]);
+          if (p.cs) __stcs(reinterpret_cast<float4*>(p.cs + row * (2LL * H) + dir * H + ug), make_float4(c[0], c[1], c[2], c[3]));
         }
         __nv_bfloat16 hi[4], lo[4];
 #pragma unroll
         for (int j = 0; j < 4; ++j) split_bf16(hout[j], hi[j], lo[j]);
-        __nv_bfloat16* o = p.out + row * (2LL * H) + dir * H + ug;
-        *reinterpret_cast<uint2*>(o) = *reinterpret_cast<uint2*>(hi);
-        *reinterpret_cast<uint2*>(o + p.out_plane) = *reinterpret_cast<uint2*>(lo);
-        if (p.outT) {
+        __nv_bfloat16* op = p.out + row * (2LL * H) + dir * H + ug;
+        __stcs(reinterpret_cast<uint2*>(op), *reinterpret_cast<uint2*>(hi));
+        __stcs(reinterpret_cast<uint2*>(op + p.out_plane), *reinterpret_cast<uint2*>(lo));
+        if (p.outT && !(p.EXP & 8)) {
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
             const long long oT = (long long)(dir * H + ug + j) * p.ldT + row;
@@ -216,23 +278,35 @@ lstm_fwd_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
     }
   }
   __syncthreads();
-  if (warp == 1) {
+  if (warp == W_MMA) {
     tc_fence_after();
-    tmem_free<64>(tmem_d);
+    tmem_free<LF_TMEM>(tmem_d);
   }
 }
 
 }  // namespace ssb
 
+static long long* g_lstm_dbg = nullptr;
+extern "C" int ss_lstm_debug(long long* buf) {   // development aid: clock64 trace [T][32] of CTA 0 of the next launches
+  g_lstm_dbg = buf;
+  return 0;
+}
+
+static int lstm_rep() {
+  const char* e = getenv("SSB_HREP");
+  int r = e ? atoi(e) : 1;
+  return r < 1 ? 1 : (r > 8 ? 8 : r);
+}
+
 extern "C" long long ss_lstm_ws_bytes(int B, int H) {
   const long long R = B <= 64 ? 64 : 128;
-  return 2LL * 2 * 2 * R * H * 2 + 256;       // hbuf + sync counters
+  return 8LL * 2 * 2 * ssb::cdiv(H, 64) * 2 * R * 64 * 2 + 256;       // hbuf (up to 8 replicas) + sync counters
 }
 
 extern "C" int ss_lstm_fwd(float* gx, const void* whh_r, long long whh_ld, long long whh_plane, const float* h0,
                            const float* c0, const int* lens, void* out, long long out_plane, void* outT, void* hprevT,
-                           long long ldT, long long outT_plane, float* cs, float* hn, float* cn, void* ws, int T, int B, int H,
-                           void* stream) {
+                           long long ldT, long long outT_plane, float* cs, float* hn, float* cn, void* ws, int T, int B,
+                           int H, void* stream) {
   using namespace ssb;
   SS_REQUIRE(T > 0 && B > 0 && B <= 128, "ss_lstm_fwd: need 1 <= B <= 128 (got %d) and T > 0", B);
   SS_REQUIRE((outT == nullptr) == (hprevT == nullptr), "ss_lstm_fwd: outT and hprevT go together");
@@ -244,16 +318,19 @@ extern "C" int ss_lstm_fwd(float* gx, const void* whh_r, long long whh_ld, long 
   p.outT = (__nv_bfloat16*)outT; p.hprevT = (__nv_bfloat16*)hprevT; p.ldT = ldT; p.outT_plane = outT_plane;
   p.cs = cs; p.hn = hn; p.cn = cn;
   p.T = T; p.B = B; p.H = H;
+  p.dbg = g_lstm_dbg;
   p.R = B <= 64 ? 64 : 128;
   p.NC = H / LF_U;
   p.KC = cdiv(H, 64);
-  p.NS = p.R == 64 ? 4 : 3;
-  const long long hbuf_bytes = 2LL * 2 * 2 * p.R * H * 2;
+  p.NS = p.R == 64 ? 5 : 2;
+  p.REP = lstm_rep();
+  p.EXP = getenv("SSB_EXP") ? atoi(getenv("SSB_EXP")) : 0;
+  const long long hbuf_bytes = (long long)p.REP * 2 * 2 * p.KC * 2 * p.R * 64 * 2;
   p.hbuf = (__nv_bfloat16*)ws;
   p.sync = (unsigned int*)((char*)ws + hbuf_bytes);
   cudaMemsetAsync(ws, 0, hbuf_bytes + 256, st);
 
-  CUtensorMap tmW, tmH;
+  CUtensorMap tmW;
   {
     uint64_t dims[3] = {(uint64_t)H, (uint64_t)8 * H, 2};
     uint64_t str[2] = {(uint64_t)whh_ld * 2, (uint64_t)whh_plane * 2};
@@ -261,16 +338,9 @@ extern "C" int ss_lstm_fwd(float* gx, const void* whh_r, long long whh_ld, long 
     int rc = make_tmap_bf16(&tmW, whh_r, 3, dims, str, box);
     if (rc) return rc;
   }
-  {
-    uint64_t dims[4] = {(uint64_t)H, (uint64_t)p.R, 2, 4};
-    uint64_t str[3] = {(uint64_t)H * 2, (uint64_t)p.R * H * 2, (uint64_t)2 * p.R * H * 2};
-    uint32_t box[4] = {64, (uint32_t)p.R, 2, 1};
-    int rc = make_tmap_bf16(&tmH, p.hbuf, 4, dims, str, box);
-    if (rc) return rc;
-  }
-  const int smem = p.NS * 2 * p.R * 128 + p.KC * LF_WCHUNK + 1024 + 256;
+  const int smem = p.NS * 2 * p.R * 128 + p.KC * LF_WCHUNK + 64 * LF_XPITCH * 4 + 1024 + 256;
   cudaFuncSetAttribute(lstm_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-  void* args[] = {(void*)&tmW, (void*)&tmH, (void*)&p};
+  void* args[] = {(void*)&tmW, (void*)&p};
   cudaError_t e = cudaLaunchCooperativeKernel((void*)lstm_fwd_kernel, dim3(2 * p.NC), dim3(LF_THREADS), args, smem, st);
   if (e != cudaSuccess) {
     set_error("ss_lstm_fwd: cooperative launch failed: %s", cudaGetErrorString(e));
