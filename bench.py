@@ -1,0 +1,536 @@
+#!/usr/bin/env python3
+"""Benchmark of the hot path (contract: see DESIGN.md "Measurement").
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload train|stft|istft] [--impl reference]
+
+Default workload `train` = BASELINE.json configs[2]: uPIT 2-speaker BLSTM training, WSJ0-2mix shape (8 kHz, 4-8 s
+utterances, STFT 512/128 -> F=257), batch 64 per GPU, one full train step per "step" (forward, uPIT loss, backward,
+gradient allreduce when N>1, global-norm clip 0.25, Adam) -- metric "uPIT train audio-sec/sec".  The same JSON line
+carries the second half of BASELINE.json's metric, "STFT frames/sec vs HBM roofline" (configs[1], 256/64), under
+"stft", and the masked iSTFT under "istft".
+
+Everything timed on the GPU is a libssb200 kernel (hand-written sm_100a CUDA, C ABI in include/ssb200.h); torch
+allocates memory, supplies the stream and NCCL.  oracle/ is executed only by the cpu_baseline leg and by
+`--impl reference`.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for _p in (ROOT, os.path.join(ROOT, "speech-separation_b200")):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+SR, N_FFT, HOP, S, B_PER_GPU = 8000, 512, 128, 2, 64
+F = N_FFT // 2 + 1
+H = 600
+N_BATCHES = 4            # distinct synthetic batches rotated through the timed steps
+
+
+def peaks():
+    """(hbm GB/s, bf16 TF/s burst, bf16 TF/s sustained, source)"""
+    try:
+        p = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        return float(p["hbm_gbs"]), float(p["bf16_tflops"]), float(p.get("bf16_tflops_sustained", p["bf16_tflops"])), \
+            "measured (MEASURED_PEAKS.json)"
+    except Exception:
+        return 6650.0, 1590.0, 1400.0, "fallback (B200_PROFILING.md)"
+
+
+def train_lengths(seed, B):
+    """cfg3 utterance lengths in samples: U{32000..64000} at 8 kHz, sorted descending."""
+    rng = np.random.default_rng(seed)
+    return sorted((int(v) for v in rng.integers(32000, 64001, size=B)), reverse=True)
+
+
+def synth_features(seed, lens_samples, num_spk=S):
+    """Magnitude-like synthetic features (T_b, F) per utterance: non-negative, sources sum >= mixture like |STFT|.
+    (Feature VALUES do not change the work done; tests/ use real STFT features for parity.)"""
+    rng = np.random.default_rng(seed)
+    samples = []
+    for n in lens_samples:
+        T = 1 + n // HOP
+        srcs = [rng.random((T, F), dtype=np.float32) * 0.5 for _ in range(num_spk)]
+        d = {"mix": np.sum(srcs, axis=0, dtype=np.float32) * rng.random((T, F), dtype=np.float32)}
+        for i, s in enumerate(srcs):
+            d["source%d" % (i + 1)] = s
+        samples.append(d)
+    return samples
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs."""
+
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "200"], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            self.thr = threading.Thread(target=self._read, daemon=True)
+            self.thr.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.25)
+        self.proc.terminate()
+        self.thr.join(timeout=2)
+        sm = [float(r[0]) for r in self.rows if len(r) >= 6 and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) >= 6 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(len(r) >= 6 and r[2 + i].lower().startswith("active")
+                                                          for r in self.rows)]
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+# kernels launched per C-ABI call (memsets not counted); default 1
+KERNELS_PER_CALL = {"colsum_sb16": 2, "bn_stats": 2, "bn_bwd": 3, "grad_norm": 2}
+
+
+class CallMeter:
+    """Wraps ssb200._lib.call: counts kernel launches and (when `timing`) brackets every call with CUDA events on
+    the launching stream."""
+
+    def __init__(self):
+        from ssb200 import _lib
+        self._lib = _lib
+        self.orig = _lib.call
+        self.launches = 0
+        self.timing = False
+        self.records = {}
+        mods = [m for n, m in sys.modules.items() if n.startswith("ssb200") and hasattr(m, "call")]
+        for m in mods:
+            if getattr(m, "call") is self.orig:
+                m.call = self
+        self.mods = mods
+
+    def __call__(self, name, *a):
+        import torch
+        self.launches += KERNELS_PER_CALL.get(name, 1)
+        if not self.timing:
+            return self.orig(name, *a)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        r = self.orig(name, *a)
+        e1.record()
+        self.records.setdefault(name, []).append((e0, e1))
+        return r
+
+    def summary(self, steps):
+        out = {}
+        for k, v in self.records.items():
+            ms = [a.elapsed_time(b) for a, b in v]
+            out[k] = {"calls_per_step": len(ms) / steps, "ms_per_step": sum(ms) / steps, "ms_per_call": sum(ms) / len(ms)}
+        return out
+
+
+def dist_setup(n_gpus):
+    import torch
+    import torch.distributed as dist
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    torch.cuda.set_device(local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    return rank, local, world
+
+
+def timed_region(fn, steps, warmup, world, sampler=None):
+    """W untimed + K timed calls of fn(i), barrier + synchronize on both sides, CUDA events, max over ranks (ms)."""
+    import torch
+    import torch.distributed as dist
+    for i in range(warmup):
+        fn(i)
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    if sampler:
+        sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(steps):
+        fn(warmup + i)
+    e1.record()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1)
+    clocks = sampler.stop() if sampler else None
+    if world > 1:
+        t = torch.tensor([ms], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t)
+    return ms, clocks
+
+
+def train_flops_per_frame(feat=F, num_spk=S):
+    """Algorithmic flops per frame per sequence of one train step, split into the GEMM part (input projections,
+    head, and their backward GEMMs) and the recurrence part (h W_hh^T and its backward)  (DESIGN.md)."""
+    inproj = 2 * 4 * H * feat * 2 + 2 * 4 * H * 2 * H * 2           # both directions, layers 0 and 1
+    head = 2 * 2 * H * feat * num_spk
+    rec = 2 * 4 * H * H * 2 * 2                                     # both directions, two layers
+    gemm = (inproj + head) + (inproj + head) + (2 * 4 * H * 2 * H * 2 + head) + rec   # fwd, dW, dX(l1)+dY, dW_hh
+    return gemm, 2 * rec
+
+
+def pad_batch(samples, keys):
+    """list of per-utterance dicts (T_b,F) sorted by descending length -> {key: (T,B,F) tensor}, lens (CPU arm)."""
+    import torch
+    lens = [s["mix"].shape[0] for s in samples]
+    T, B = max(lens), len(samples)
+    out = {}
+    for k in keys:
+        x = torch.zeros(T, B, samples[0][k].shape[1])
+        for b, s in enumerate(samples):
+            x[:lens[b], b] = torch.from_numpy(s[k])
+        out[k] = x
+    return out, lens
+
+
+def cpu_train_sample(n_utts, steps, warmup, seed=0):
+    """Times oracle/cpu_step.py (the reference's torch CPU calls) on the first n_utts utterances of batch `seed`.
+    Returns (audio-sec/sec, sec/step, cores)."""
+    import torch
+    from oracle import cpu_step
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    lens_s = train_lengths(seed, B_PER_GPU)[:n_utts]
+    samples = synth_features(seed, lens_s)
+    keys = ["mix"] + ["source%d" % (i + 1) for i in range(S)]
+    pb, lens = pad_batch(samples, keys)
+    torch.manual_seed(0)
+    tr = cpu_step.CpuTrainer(F, S)
+    times = []
+    for i in range(warmup + steps):
+        h0, c0 = torch.randn(4, n_utts, H), torch.randn(4, n_utts, H)
+        t0 = time.perf_counter()
+        tr.step(pb["mix"], [pb[k] for k in keys[1:]], lens, h0, c0)
+        if i >= warmup:
+            times.append(time.perf_counter() - t0)
+    sec = sum(times) / len(times)
+    return sum(lens_s) / SR / sec, sec, cores
+
+
+def run_train(args, rank, local, world):
+    import torch
+    from torch.nn.utils.rnn import PackedSequence
+    from ssb200 import train, uPIT
+    hbm, tf_burst, tf_sus, peak_src = peaks()
+    torch.manual_seed(0)
+    model = uPIT.SepDNN(local, feat_dim=str(F), num_spk=str(S)).cuda()
+    model.max_workspaces = N_BATCHES
+    trainer = train.Trainer(model, uPIT)
+    meter = CallMeter()
+    coll = uPIT.Collator("mix")
+    host, dev, audio_s, frames = [], [], [], []
+    for i in range(N_BATCHES):
+        # every rank knows every rank's lengths (seeded), so the job totals need no collective
+        audio_s.append(sum(sum(train_lengths(1000 * r + i, B_PER_GPU)) for r in range(world)) / SR)
+        lens_s = train_lengths(1000 * rank + i, B_PER_GPU)
+        frames.append(sum(1 + n // HOP for n in lens_s))
+        b = coll(synth_features(1000 * rank + i, lens_s))
+        host.append({k: PackedSequence(v.data.pin_memory(), v.batch_sizes) for k, v in b.items()})
+        dev.append({k: PackedSequence(v.data.cuda(), v.batch_sizes) for k, v in b.items()})
+    h2d = int(np.mean([sum(v.data.numel() * 4 for v in b.values()) for b in host]))
+    sink = {}
+
+    def step_dev(i):
+        sink["loss"], _ = trainer.step(dev[i % N_BATCHES])
+
+    def step_e2e(i):
+        loss, norm = trainer.step(host[i % N_BATCHES])
+        sink["host_loss"] = (float(loss), float(norm))          # D2H read of the step's result, every step
+
+    K, W = args.steps, args.warmup
+    sampler = ClockSampler(local) if rank == 0 else None
+    meter.launches = 0
+    ms, clocks = timed_region(step_dev, K, W, world, sampler)
+    launches = meter.launches // (K + W) * K
+    tot_audio = sum(audio_s[(W + i) % N_BATCHES] for i in range(K))
+    value = tot_audio / (ms / 1e3)
+    ms_e2e, _ = timed_region(step_e2e, K, W, world)
+    e2e = tot_audio / (ms_e2e / 1e3)
+    # per-kernel device times (CUDA events around every C-ABI call, same stream), separate untimed pass
+    meter.timing = True
+    PROF = 2
+    for i in range(PROF):
+        step_dev(i)
+    torch.cuda.synchronize()
+    meter.timing = False
+    prof = meter.summary(PROF)
+    fr = float(np.mean(frames[:PROF]))
+    gemm_fl, rec_fl = train_flops_per_frame()
+    rl = {}
+    for name, fl in (("gemm_sb16", gemm_fl), ("lstm_fwd", rec_fl / 3), ("lstm_bwd", rec_fl / 3)):
+        if name in prof:
+            a = fl * fr / (prof[name]["ms_per_step"] * 1e-3) / 1e12
+            rl[name] = {"bound": "tensor", "achieved": round(a, 2), "peak": tf_sus, "unit": "TFLOP/s",
+                        "frac": round(a / tf_sus, 4), "ms_per_step": round(prof[name]["ms_per_step"], 3)}
+    for name, byts in (("pit_loss_fwd", (2 * S + 1) * 4.0 * F), ("pit_loss_bwd", (2 * S + 1) * 4.0 * F + S * F * 8.0)):
+        if name in prof:
+            a = byts * B_PER_GPU * (fr / B_PER_GPU) / (prof[name]["ms_per_step"] * 1e-3) / 1e9
+            rl[name] = {"bound": "hbm", "achieved": round(a, 1), "peak": hbm, "unit": "GB/s", "frac": round(a / hbm, 4),
+                        "ms_per_step": round(prof[name]["ms_per_step"], 3)}
+    dom = max(prof, key=lambda k: prof[k]["ms_per_step"])
+    roofline = dict(rl.get(dom, {"bound": "tensor", "achieved": None, "peak": tf_sus, "unit": "TFLOP/s", "frac": None}))
+    roofline.update({"kernel": dom, "traffic": None, "peak_source": peak_src,
+                     "share_of_step": round(prof[dom]["ms_per_step"] / sum(v["ms_per_step"] for v in prof.values()), 3)})
+    line = {
+        "metric": "uPIT train audio-sec/sec", "value": round(value, 1), "unit": "audio-sec/sec", "n_gpus": world,
+        "steps": K, "warmup": W, "ms_per_step": round(ms / K, 3), "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "split-bf16 operands (hi+lo), fp32 accumulate/state", "data": "synthetic",
+        "config": {"workload": "configs[2]: uPIT 2-spk BLSTM(2x600 bidir)+BN+Linear train step, WSJ0-2mix shape, 8 kHz, "
+                               "STFT 512/128 (F=257), utterances U[4,8] s, batch 64/GPU",
+                   "global_batch": B_PER_GPU * world, "frames_per_step_per_gpu": int(fr), "parallelism": "dp%d" % world,
+                   "dp_semantics": "mode A: per-rank loss/BN, gradients averaged (bucketed NCCL allreduce overlapped "
+                                   "with backward)",
+                   "l2": "4 distinct batches rotated; per-step working set ~3 GB >> 126 MB L2"},
+        "e2e": {"value": round(e2e, 1), "unit": "audio-sec/sec", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 8,
+                "ms_per_step": round(ms_e2e / K, 3)},
+        "gpu_launches": launches, "clocks": clocks, "roofline": roofline, "rooflines": rl,
+        "kernel_ms_per_step": {k: round(v["ms_per_step"], 3) for k, v in sorted(prof.items(), key=lambda kv: -kv[1]["ms_per_step"])},
+    }
+    return line
+
+
+# ---------------------------------------------------------------- STFT (configs[1]) and masked iSTFT legs
+STFT_NFFT, STFT_HOP = 256, 64
+STFT_F = STFT_NFFT // 2 + 1
+
+
+def stft_corpus_lengths(n_signals, seed=0):
+    """configs[1]: wsj_tr-sized corpus = 20 000 mixtures x 3 signals, N ~ U{16000..80000} samples (2-10 s @ 8 kHz)."""
+    rng = np.random.default_rng(seed)
+    return rng.integers(16000, 80001, size=n_signals).astype(np.int64)
+
+
+def cpu_stft_sample(budget_s=8.0):
+    """oracle STFT (numpy restatement of the librosa call at extract_feats.py:87,89), one utterance at a time,
+    single process, for ~budget_s seconds.  Returns (frames/sec, n_utts, cores=1)."""
+    from oracle import stft_oracle
+    lens = stft_corpus_lengths(4096, seed=1)
+    rng = np.random.default_rng(1)
+    sigs = [rng.standard_normal(int(n)).astype(np.float32) * 0.1 for n in lens[:64]]
+    stft_oracle.stft_mag(sigs[0], STFT_NFFT, STFT_HOP)
+    t0 = time.perf_counter()
+    frames = n = 0
+    while time.perf_counter() - t0 < budget_s:
+        y = sigs[n % len(sigs)]
+        frames += stft_oracle.stft_mag(y, STFT_NFFT, STFT_HOP).shape[1]
+        n += 1
+    return frames / (time.perf_counter() - t0), n, 1
+
+
+def run_stft(args, rank, local, world, n_mix=20000, e2e_mix=2000):
+    """value: the WHOLE corpus (n_mix x 3 signals / world per rank) resident in HBM, one launch per step.
+    e2e: a shard of e2e_mix mixtures through pinned host buffers (H2D of the audio + D2H of the features inside
+    the timed region), because pinning the whole 34 GB corpus would dominate the bench's wall time."""
+    import torch
+    from ssb200 import ops
+    hbm, _, _, peak_src = peaks()
+    K, W = args.steps, args.warmup
+    per_rank = n_mix * 3 // world
+    lens = stft_corpus_lengths(n_mix * 3)[rank * per_rank:(rank + 1) * per_rank]
+    rag = ops.Ragged(lens, STFT_NFFT, STFT_HOP, "cuda")
+    n = int(rag.sig_off[-1])
+    sig = torch.empty(n, dtype=torch.float32, device="cuda").uniform_(-0.5, 0.5)
+    out = torch.empty(rag.total_frames * STFT_F, dtype=torch.float32, device="cuda")
+    tot_frames = sum(int((1 + stft_corpus_lengths(n_mix * 3)[r * per_rank:(r + 1) * per_rank] // STFT_HOP).sum())
+                     for r in range(world))
+    meter = CallMeter()
+    ev = []
+
+    def step(i):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        ops.stft(sig, rag, out=out)
+        e1.record()
+        ev.append((e0, e1))
+
+    sampler = ClockSampler(local) if rank == 0 else None
+    ms, clocks = timed_region(step, K, W, world, sampler)
+    launches = meter.launches // (K + W) * K
+    kms = float(np.mean([a.elapsed_time(b) for a, b in ev[W:]]))
+    value = tot_frames * K / (ms / 1e3)
+    bytes_per_frame = STFT_HOP * 4 + STFT_F * 4
+    ach = bytes_per_frame * rag.total_frames / (kms * 1e-3) / 1e9
+    # e2e shard
+    ne = e2e_mix * 3 // world
+    rag_e = ops.Ragged(lens[:ne], STFT_NFFT, STFT_HOP, "cuda")
+    n_e = int(rag_e.sig_off[-1])
+    h_sig = torch.empty(n_e, dtype=torch.float32).uniform_(-0.5, 0.5).pin_memory()
+    h_out = torch.empty(rag_e.total_frames * STFT_F, dtype=torch.float32).pin_memory()
+    d_sig = torch.empty(n_e, dtype=torch.float32, device="cuda")
+    d_out = torch.empty(rag_e.total_frames * STFT_F, dtype=torch.float32, device="cuda")
+
+    def step_e2e(i):
+        d_sig.copy_(h_sig, non_blocking=True)
+        ops.stft(d_sig, rag_e, out=d_out)
+        h_out.copy_(d_out, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+
+    ms_e, _ = timed_region(step_e2e, K, W, world)
+    e2e = rag_e.total_frames * world * K / (ms_e / 1e3)
+    del sig, out
+    return {
+        "metric": "STFT frames/sec", "value": round(value, 0), "unit": "frames/sec", "n_gpus": world, "steps": K,
+        "warmup": W, "ms_per_step": round(ms / K, 3), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "configs[1]: STFT magnitude features, 8 kHz, 256-pt periodic Hann / hop 64 (F=129), "
+                               "wsj_tr-sized corpus: %d mixtures x 3 signals, 2-10 s" % n_mix,
+                   "signals_per_gpu": int(per_rank), "frames_per_gpu": int(rag.total_frames),
+                   "mode": "magnitude, (F,T) file layout; log/CMVN off (reference has none, SURVEY D2)",
+                   "l2": "input %.1f GB + output %.1f GB per step >> 126 MB L2" % (n * 4 / 1e9, rag.total_frames * STFT_F * 4 / 1e9)},
+        "e2e": {"value": round(e2e, 0), "unit": "frames/sec", "h2d_bytes_per_step": n_e * 4,
+                "d2h_bytes_per_step": rag_e.total_frames * STFT_F * 4, "sample": "%d-mixture shard via pinned host memory" % e2e_mix},
+        "gpu_launches": launches, "clocks": clocks,
+        "roofline": {"bound": "hbm", "kernel": "stft_kernel<256>", "achieved": round(ach, 1), "peak": hbm, "unit": "GB/s",
+                     "frac": round(ach / hbm, 4), "traffic": None, "peak_source": peak_src,
+                     "algorithmic_bytes_per_frame": bytes_per_frame, "kernel_ms": round(kms, 3)},
+    }
+
+
+def run_istft(args, rank, local, world, n_utts=3000, n_src=2):
+    """Masked iSTFT (reconstruct_sources.py:39-42): wsj_tt-sized set, 512/128, int16 out, HBM-resident."""
+    import torch
+    from ssb200 import ops
+    hbm, _, _, peak_src = peaks()
+    K, W = args.steps, args.warmup
+    rng = np.random.default_rng(5)
+    lens = rng.integers(32000, 64001, size=n_utts).astype(np.int64)
+    rag = ops.Ragged(lens, N_FFT, HOP, "cuda")
+    sig = torch.empty(int(rag.sig_off[-1]), dtype=torch.float32, device="cuda").uniform_(-0.3, 0.3)
+    spec = ops.stft(sig, rag, complex_out=True)
+    mask = torch.rand(rag.total_frames * F * n_src, device="cuda")
+    out, _ = ops.istft_masked(spec, mask, rag, n_src)
+    ev = []
+
+    def step(i):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        ops.istft_masked(spec, mask, rag, n_src, out=out)
+        e1.record()
+        ev.append((e0, e1))
+
+    ms, _ = timed_region(step, K, W, world)
+    kms = float(np.mean([a.elapsed_time(b) for a, b in ev[W:]]))
+    fs = rag.total_frames * n_src
+    byts = F * 8 + F * 4 + HOP * 2
+    ach = byts * fs / (kms * 1e-3) / 1e9
+    return {"metric": "masked iSTFT frames/sec (per source)", "value": round(fs * world * K / (ms / 1e3), 0),
+            "unit": "frame-sources/sec", "n_gpus": world,
+            "config": {"workload": "mask x mixture-phase iSTFT, 512/128, %d utts x %d sources, int16 out" % (n_utts, n_src)},
+            "roofline": {"bound": "hbm", "kernel": "istft_kernel<512>", "achieved": round(ach, 1), "peak": hbm,
+                         "unit": "GB/s", "frac": round(ach / hbm, 4), "traffic": None, "peak_source": peak_src,
+                         "algorithmic_bytes_per_frame_source": byts, "kernel_ms": round(kms, 3)}}
+
+
+# ---------------------------------------------------------------- reference arm (CPU, rank 0 only)
+def run_reference(args, rank, world):
+    """`--impl reference`: the reference's CPU implementation of the path, on the host cores.  /root/reference is
+    Python that cannot be installed (no setup.py) nor copied, and is absent on the GPU box, so this times
+    oracle/cpu_step.py -- the same torch.nn CPU library calls the reference's step makes -- kind "port"."""
+    if rank != 0:
+        return None
+    K, W = args.steps, args.warmup
+    if args.workload == "stft":
+        fps, n, cores = cpu_stft_sample(budget_s=min(60.0, 4.0 * (K + W)))
+        return {"impl": "reference", "metric": "STFT frames/sec", "value": round(fps, 0), "unit": "frames/sec",
+                "n_gpus": world, "steps": K, "warmup": W, "higher_is_better": True, "data": "synthetic", "dtype": "f64->c64",
+                "config": {"workload": "configs[1] STFT 256/64, one utterance at a time (extract_feats.py:62-90), numpy"},
+                "cpu_baseline": {"value": round(fps, 0), "unit": "frames/sec", "cores": cores, "kind": "port",
+                                 "sample": "%d utterances of 2-10 s" % n},
+                "e2e": {"value": round(fps, 0), "unit": "frames/sec", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    # per-step sample: 4 utterances (~3 s of CPU work per step here), 2 when many steps are asked for, so that the
+    # whole run ends within a few minutes whatever K and W are
+    n_utts = 4 if K + W <= 30 else 2
+    aps, sec, cores = cpu_train_sample(n_utts, K, W)
+    return {"impl": "reference", "metric": "uPIT train audio-sec/sec", "value": round(aps, 2), "unit": "audio-sec/sec",
+            "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": round(sec * 1e3, 1), "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "configs[2] uPIT train step (same shapes as the GPU arm), CPU, torch %d threads" % cores,
+                       "batch": n_utts},
+            "cpu_baseline": {"value": round(aps, 2), "unit": "audio-sec/sec", "cores": cores, "kind": "port",
+                             "sample": "%d of the 64 utterances of one batch per step" % n_utts},
+            "e2e": {"value": round(aps, 2), "unit": "audio-sec/sec", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--workload", default="train", choices=["train", "stft", "istft"])
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--no-extras", action="store_true", help="skip the stft/istft/cpu_baseline legs of the train line")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.impl == "reference":
+        line = run_reference(args, rank, world)
+        if line is not None:
+            print(json.dumps(line), flush=True)
+        return
+    import torch
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (the product path has no CPU fallback)")
+    rank, local, world = dist_setup(args.gpus)
+    if args.workload == "stft":
+        line = run_stft(args, rank, local, world)
+    elif args.workload == "istft":
+        line = run_istft(args, rank, local, world)
+    else:
+        line = run_train(args, rank, local, world)
+        if not args.no_extras:
+            sub = argparse.Namespace(steps=max(3, min(args.steps, 5)), warmup=3)
+            torch.cuda.empty_cache()
+            line["stft"] = run_stft(sub, rank, local, world)
+            torch.cuda.empty_cache()
+            line["istft"] = run_istft(sub, rank, local, world)
+    if rank == 0 and world == 1 and not args.no_extras:
+        if args.workload == "train":
+            aps, sec, cores = cpu_train_sample(4, 1, 1)
+            line["cpu_baseline"] = {"value": round(aps, 2), "unit": "audio-sec/sec", "cores": cores, "kind": "port",
+                                    "sample": "1 train step on 4 of the 64 utterances (%.1f s)" % sec}
+            fps, n, c1 = cpu_stft_sample(5.0)
+            line["stft"]["cpu_baseline"] = {"value": round(fps, 0), "unit": "frames/sec", "cores": c1, "kind": "port",
+                                            "sample": "%d utterances, single process" % n}
+        elif args.workload == "stft":
+            fps, n, c1 = cpu_stft_sample(10.0)
+            line["cpu_baseline"] = {"value": round(fps, 0), "unit": "frames/sec", "cores": c1, "kind": "port",
+                                    "sample": "%d utterances, single process" % n}
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        import torch.distributed as dist
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -82,7 +82,7 @@ int ss_colsum_sb16(const void* in, long long ld, long long plane, int R, int C, 
  * = chosen source per output slot; mode 1 (RSH.py:229-238): losses[n_src][B] with +inf for sources in the
  * bitmask used[B], idx = argmin, used updated.  stats[4] = {sum_b min/S, sum_b len_b*F, loss = [0]/[1], 1/(S*[1])},
  * accumulated over calls when accumulate != 0 (RSH.py:240-241).
- * bwd: dz = (2*(m*x - src[assign])*x*stats[3]*gout[0] + dmask_extra) * m*(1-m), as sb16 [T*B][ld_dz] and
+ * bwd (gout NULL = 1): dz = (2*(m*x - src[assign])*x*stats[3]*gout[0] + dmask_extra) * m*(1-m), as sb16 [T*B][ld_dz] and
  * transposed sb16 [n_out*F][ld_dzT]; rows with t >= len_b are zero. */
 int ss_pit_chunks(int T);
 int ss_pit_loss_fwd(const float* z, long long ldz, const float* mix, const float* src, const int* lens, int T, int B,
@@ -144,6 +144,18 @@ int ss_bn_bwd(float* dy, const void* x, long long ld, long long plane, int R, in
               float* partial, float* dgamma, float* dbeta, float* bwd, void* stream);
 int ss_head_dw_fix(const float* G, const float* dsum, const float* coef, const float* beta, int O, int C, float* dW,
                    void* stream);
+
+/* ---- f1: global-norm clip + Adam over one flat fp32 bucket.  Replaces torch.nn.utils.clip_grad_norm_(params,
+ * 0.25) and torch.optim.Adam(lr=1e-3).step() at steps/train_qsub.py:95,121-122 ----
+ * ss_grad_norm: norm_out[0] = gscale * ||g||_2 (partial: ss_optim_parts(n) floats).  gscale = 1/world turns an
+ * allreduce-summed gradient into the data-parallel mean.
+ * ss_clip_adam: g' = g * gscale * min(1, max_norm/(norm[0]+1e-6)) (max_norm <= 0: no clipping, norm unused), then
+ * Adam with bias correction (step counts from 1): m += (g'-m)(1-b1); v = b2 v + (1-b2) g'^2;
+ * p -= lr/(1-b1^step) * m / (sqrt(v)/sqrt(1-b2^step) + eps). */
+int ss_optim_parts(long long n);
+int ss_grad_norm(const float* g, long long n, float gscale, float* partial, float* norm_out, void* stream);
+int ss_clip_adam(float* p, const float* g, float* m, float* v, long long n, const float* norm, float gscale,
+                 float max_norm, float lr, float beta1, float beta2, float eps, int step, void* stream);
 
 #ifdef __cplusplus
 }

@@ -143,7 +143,7 @@ pit_bwd_kernel(const float* __restrict__ z, long long ldz, const float* __restri
   const int c0 = blockIdx.x * 32, r0 = blockIdx.y * 32;
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
   const int R = T * B, C = n_out * F;
-  const float g = 2.0f * stats[3] * gout[0];
+  const float g = 2.0f * stats[3] * (gout ? gout[0] : 1.0f);
   const long long plane = (long long)T * B * F;
 #pragma unroll
   for (int i = 0; i < 4; ++i) {

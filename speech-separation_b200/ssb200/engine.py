@@ -151,7 +151,7 @@ def pit_loss(ws, mix, src, lens_dev, F, n_out, n_src, mode=0, accumulate=False, 
 
 
 def backward(ws, wt, p, grads, mix, src, lens_dev, c0, F, n_out, gout, dmask_extra=None, dhn=None, dcn=None,
-             want_dx=False, want_d0=False, training=True, accumulate=False):
+             want_dx=False, want_d0=False, training=True, accumulate=False, hook=None):
     """Backward of loss -> every parameter gradient in `grads` (dict name -> fp32 tensor, natural layouts).
     Returns (dx or None, dh0 or None, dc0 or None)."""
     T, B, TB = ws.T, ws.B, ws.TB
@@ -179,6 +179,8 @@ def backward(ws, wt, p, grads, mix, src, lens_dev, c0, F, n_out, gout, dmask_ext
     _acc(grads, "lin.bias", dsum, accumulate)
     _acc(grads, "bn.weight", ws.dgamma, accumulate)
     _acc(grads, "bn.bias", ws.dbeta, accumulate)
+    if hook is not None:
+        hook("head")
     dout = ws.dy
     dx = dh0 = dc0 = None
     if want_d0:
@@ -200,6 +202,8 @@ def backward(ws, wt, p, grads, mix, src, lens_dev, c0, F, n_out, gout, dmask_ext
         for d, suf in enumerate(("", "_reverse")):
             _acc(grads, "blstm.bias_ih_l%d%s" % (l, suf), ws.db[d * 4 * H:(d + 1) * 4 * H], accumulate)
             _acc(grads, "blstm.bias_hh_l%d%s" % (l, suf), ws.db[d * 4 * H:(d + 1) * 4 * H], accumulate)
+        if hook is not None:
+            hook("l%d" % l)
         if l > 0:
             _gemm(ws.dG, wt.wihT[l], ws.dout, K=8 * H)
             dout = ws.dout

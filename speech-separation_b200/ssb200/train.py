@@ -1,0 +1,140 @@
+"""Train step around the hot path: what steps/train_qsub.py:116-122 does per batch --
+
+    loss, norm = m.compute_loss(model, epoch, batch); loss.backward()
+    torch.nn.utils.clip_grad_norm_(model.parameters(), 0.25); optimizer.step()        (Adam, lr 1e-3)
+
+-- as one call, with (new) the data-parallel gradient exchange between the backward pass and the clip.
+Parameters, gradients and Adam moments live in flat fp32 buckets ordered by when the backward pass finishes them
+(layer 0 | layer 1 | head), so each bucket is allreduced over NCCL on a side stream while the next layer's backward
+recurrence still runs, and clip + Adam are two kernels over the whole flat buffer (libssb200 ss_grad_norm /
+ss_clip_adam) instead of ~120 per-tensor launches.
+
+DP semantics (mode A of SURVEY.md 8e): every rank computes the reference loss on its own shard of utterances with
+its own BatchNorm batch statistics; gradients are averaged over ranks before the clip; parameters stay identical on
+all ranks because they start identical (broadcast from rank 0) and see identical averaged gradients.
+"""
+import torch
+
+from ._lib import LL, call, lib, stream_ptr
+
+
+def bucket_of(name):
+    """Gradient bucket a parameter belongs to, by the reference's state_dict names."""
+    if name.startswith("blstm.") and "_l0" in name:
+        return "l0"
+    if name.startswith("blstm.") and "_l1" in name:
+        return "l1"
+    return "head"
+
+
+BUCKET_ORDER = ("l0", "l1", "head")
+
+
+def flat_layout(named_shapes, align=64):
+    """named_shapes: [(name, numel)] -> ({name: (offset, numel)}, {bucket: (offset, numel)}, total).
+    Buckets are contiguous; every tensor starts on an `align`-float boundary."""
+    offs, buckets, pos = {}, {}, 0
+    for bk in BUCKET_ORDER:
+        start = pos
+        for name, n in named_shapes:
+            if bucket_of(name) != bk:
+                continue
+            offs[name] = (pos, n)
+            pos += (n + align - 1) // align * align
+        buckets[bk] = (start, pos - start)
+    return offs, buckets, pos
+
+
+def shard_utterances(lengths, world, rank):
+    """Length-bucketed sharding of a global batch: utterances sorted by descending length are dealt
+    in snake order (0..w-1, w-1..0, ...), so every rank sees a similar T_max and total frame count.  Returns the
+    indices for `rank`, longest first."""
+    order = sorted(range(len(lengths)), key=lambda i: (-lengths[i], i))
+    out = []
+    for g in range(0, len(order), world):
+        grp = order[g:g + world]
+        k = rank if (g // world) % 2 == 0 else world - 1 - rank
+        if k < len(grp):
+            out.append(grp[k])
+    return out
+
+
+def allreduce_buckets(flat, buckets, group=None, tags=BUCKET_ORDER):
+    """Sum-allreduce the listed buckets of a flat tensor (host-side logic shared by the NCCL path and the CPU/gloo
+    tests).  Returns the async work handles."""
+    import torch.distributed as dist
+    works = []
+    for tag in tags:
+        o, n = buckets[tag]
+        if n:
+            works.append(dist.all_reduce(flat[o:o + n], op=dist.ReduceOp.SUM, group=group, async_op=True))
+    return works
+
+
+class Trainer:
+    """Owns the flat parameter / gradient / Adam buckets of one SepDNN and runs whole train steps."""
+
+    def __init__(self, model, arch, lr=1e-3, clip=0.25, betas=(0.9, 0.999), eps=1e-8, group=None):
+        import torch.distributed as dist
+        self.model, self.arch = model, arch
+        self.lr, self.clip, self.betas, self.eps = float(lr), float(clip), betas, float(eps)
+        self.world = dist.get_world_size(group) if dist.is_available() and dist.is_initialized() else 1
+        self.group = group
+        named = [(k, p) for k, p in model.named_parameters()]
+        dev = named[0][1].device
+        if dev.type != "cuda":
+            raise RuntimeError("ssb200.train.Trainer needs the model on a CUDA device (no CPU fallback)")
+        self.offs, self.buckets, total = flat_layout([(k, p.numel()) for k, p in named])
+        self.n = total
+        self.flat_p = torch.zeros(total, dtype=torch.float32, device=dev)
+        self.flat_g = torch.zeros(total, dtype=torch.float32, device=dev)
+        self.flat_m = torch.zeros(total, dtype=torch.float32, device=dev)
+        self.flat_v = torch.zeros(total, dtype=torch.float32, device=dev)
+        self.grads = {}
+        for k, p in named:
+            o, n = self.offs[k]
+            self.flat_p[o:o + n].copy_(p.detach().reshape(-1))
+            p.data = self.flat_p[o:o + n].view_as(p)          # the module's parameters now alias the flat bucket
+            self.grads[k] = self.flat_g[o:o + n].view_as(p)
+        if self.world > 1:
+            dist.broadcast(self.flat_p, src=0, group=group)
+            for buf in (model.bn.running_mean, model.bn.running_var):
+                dist.broadcast(buf, src=0, group=group)
+        import ctypes
+        self.partial = torch.empty(max(1, lib().ss_optim_parts(ctypes.c_longlong(total))), dtype=torch.float32,
+                                   device=dev)
+        self.norm = torch.zeros(1, dtype=torch.float32, device=dev)
+        self.steps = 0
+        self.comm = torch.cuda.Stream(device=dev) if self.world > 1 else None
+        self._works = []
+
+    # -- gradient exchange: called by the engine as each bucket's last kernel has been enqueued --
+    def _bucket_ready(self, tag):
+        if self.world == 1:
+            return
+        import torch.distributed as dist
+        ev = torch.cuda.Event()
+        ev.record()
+        self.comm.wait_event(ev)
+        o, n = self.buckets[tag]
+        with torch.cuda.stream(self.comm):
+            dist.all_reduce(self.flat_g[o:o + n], op=dist.ReduceOp.SUM, group=self.group)
+
+    def step(self, batch_sample):
+        """One optimisation step on a collated batch.  Returns device scalars (loss, norm) of this rank's shard."""
+        loss, norm = self.arch.loss_and_grads(self.model, batch_sample, self.grads, hook=self._bucket_ready)
+        loss, norm = loss.clone(), norm.clone()
+        if self.world > 1:
+            torch.cuda.current_stream().wait_stream(self.comm)
+        self.apply_update()
+        return loss, norm
+
+    def apply_update(self):
+        """clip_grad_norm_(clip) + Adam.step() on the flat buckets (steps/train_qsub.py:121-122)."""
+        st = stream_ptr()
+        gscale = 1.0 / self.world
+        self.steps += 1
+        call("grad_norm", self.flat_g, LL(self.n), gscale, self.partial, self.norm, st)
+        call("clip_adam", self.flat_p, self.flat_g, self.flat_m, self.flat_v, LL(self.n), self.norm, gscale,
+             self.clip, self.lr, float(self.betas[0]), float(self.betas[1]), self.eps, self.steps, st)
+        self.model._wt_versions = None     # parameters changed behind autograd's back: refresh the operand copies

@@ -132,7 +132,7 @@ class SepDNN(nn.Module):
         key = (T, B, training)
         ws = self._ws.get(key)
         if ws is None:
-            if len(self._ws) >= 2:
+            if len(self._ws) >= getattr(self, "max_workspaces", 2):
                 self._ws.clear()
             ws = engine.Workspace(T, B, self.in_dim, self.out_dim, self.num_spk, self.num_layers,
                                   self.lin.weight.device, training)
@@ -223,6 +223,27 @@ def compute_loss(model, epoch, batch_sample, plotdir=""):
     P = {1: 1, 2: 2, 3: 6, 4: 24}[model.num_spk]
     model.last = {"losses": ws.losses[:P], "indices": ws.idx, "stats": ws.stats, "batch": batch}
     return loss, norm.detach()
+
+
+def loss_and_grads(model, batch_sample, grads, hook=None):
+    """compute_loss + loss.backward() without the autograd tape: every parameter gradient is written (not
+    accumulated) straight into grads[name] -- e.g. views of the trainer's flat bucket (ssb200/train.py).  `hook(tag)`
+    is called when a gradient bucket ('head', 'l1', 'l0') has been enqueued.  Returns device scalars (loss, norm)."""
+    dev = model.lin.weight.device
+    keys = ["mix"] + ["source%d" % (i + 1) for i in range(model.num_spk)]
+    batch = unpack_batch(batch_sample, keys, dev)
+    batch["src"] = torch.stack([batch[k] for k in keys[1:]]) if model.num_spk > 1 else batch[keys[1]][None]
+    model.hidden = model.init_hidden(batch["B"])
+    with torch.no_grad():
+        run_forward(model, batch, model.hidden, save=True)
+        ws, wt = batch["ws"], batch["wt"]
+        S, F = model.num_spk, model.feat_dim
+        engine.pit_loss(ws, batch["mix"], batch["src"], batch["lens_dev"], F, S, S, mode=0)
+        p = {k: v.detach() for k, v in model.param_dict().items()}
+        engine.backward(ws, wt, p, grads, batch["mix"], batch["src"], batch["lens_dev"], model.hidden[1].contiguous(),
+                        F, S, None, training=model.training, hook=hook)
+    model.last = {"losses": ws.losses, "indices": ws.idx, "stats": ws.stats, "batch": batch}
+    return ws.stats[2], ws.stats[1]
 
 
 def compute_cv_loss(model, epoch, batch_sample, plotdir=""):

@@ -1,0 +1,64 @@
+"""Trainer.step (tape-free backward into flat buckets + fused clip/Adam kernels) vs the reference's sequence
+compute_loss -> backward -> torch clip_grad_norm_(0.25) -> torch Adam(lr=1e-3).step() (steps/train_qsub.py:117-122)
+run through the drop-in module's autograd path, whose gradients test_gpu_upit.py pins to the reference goldens.
+Tolerance: parameters after 3 steps within 1e-5 absolute of the torch optimiser's (fp32 arithmetic, different
+summation order in the norm)."""
+import copy
+
+import numpy as np
+import pytest
+import torch
+
+import common
+from ssb200 import train, uPIT
+from test_gpu_upit import _batch, _model
+
+pytestmark = pytest.mark.gpu
+
+
+def test_trainer_matches_torch_clip_adam():
+    z, case = common.load_golden("upit_s2_f129")
+    batch, _, _ = _batch(case)
+    model_a = _model(case)
+    model_b = copy.deepcopy(model_a)
+    opt = torch.optim.Adam(model_a.parameters(), lr=1e-3)
+    tr = train.Trainer(model_b, uPIT)
+    for it in range(3):
+        torch.manual_seed(40 + it)
+        loss_a, norm_a = uPIT.compute_loss(model_a, 0, batch)
+        loss_a.backward()
+        gn = torch.nn.utils.clip_grad_norm_(model_a.parameters(), 0.25)
+        opt.step()
+        torch.manual_seed(40 + it)
+        loss_b, norm_b = tr.step(batch)
+        torch.cuda.synchronize()
+        assert abs(float(loss_a) - float(loss_b)) <= 1e-5 * abs(float(loss_a)), it
+        assert float(norm_a) == float(norm_b)
+        assert abs(float(gn) - float(tr.norm)) <= 1e-5 * float(gn)
+        for (k, pa), (_, pb) in zip(model_a.named_parameters(), model_b.named_parameters()):
+            d = float((pa.detach() - pb.detach()).abs().max())
+            assert d <= 1e-5, (it, k, d)
+    for k in ("running_mean", "running_var"):
+        assert torch.allclose(getattr(model_a.bn, k), getattr(model_b.bn, k), atol=1e-6)
+
+
+def test_clip_adam_kernels_unaligned_sizes():
+    from ssb200._lib import LL, call, lib, stream_ptr
+    import ctypes
+    for n in (1, 7, 8192, 8193, 100003):
+        g = torch.randn(n, device="cuda") * 3
+        p = torch.randn(n, device="cuda")
+        ref_p = p.clone().requires_grad_(True)
+        ref_p.grad = g.clone()
+        opt = torch.optim.Adam([ref_p], lr=1e-3)
+        m, v = torch.zeros_like(p), torch.zeros_like(p)
+        partial = torch.empty(max(1, lib().ss_optim_parts(ctypes.c_longlong(n))), device="cuda")
+        norm = torch.zeros(1, device="cuda")
+        for step in (1, 2):
+            torch.nn.utils.clip_grad_norm_([ref_p], 0.25)
+            opt.step()
+            ref_p.grad = g.clone()
+            call("grad_norm", g, LL(n), 1.0, partial, norm, stream_ptr())
+            call("clip_adam", p, g, m, v, LL(n), norm, 1.0, 0.25, 1e-3, 0.9, 0.999, 1e-8, step, stream_ptr())
+        assert abs(float(norm) - float(g.norm())) <= 1e-5 * float(g.norm())
+        assert float((p - ref_p.detach()).abs().max()) <= 2e-6, n
