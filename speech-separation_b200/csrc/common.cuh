@@ -155,6 +155,23 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, float* v) {
   for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
 }
 
+// Two 32-lane x 4-column TMEM loads (4 registers each) followed by one wait.
+__device__ __forceinline__ void tmem_ld4x2(uint32_t taddr0, uint32_t taddr1, float* v0, float* v1) {
+  uint32_t r[8];
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0,%1,%2,%3}, [%8];\n\t"
+      "tcgen05.ld.sync.aligned.32x32b.x4.b32 {%4,%5,%6,%7}, [%9];\n\t"
+      "tcgen05.wait::ld.sync.aligned;"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+      : "r"(taddr0), "r"(taddr1)
+      : "memory");
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    v0[i] = __uint_as_float(r[i]);
+    v1[i] = __uint_as_float(r[4 + i]);
+  }
+}
+
 // gpu-scope release/acquire on a global counter (grid-wide step barrier of the recurrence)
 __device__ __forceinline__ void red_release_add(unsigned int* p, unsigned int v) {
   asm volatile("red.release.gpu.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");

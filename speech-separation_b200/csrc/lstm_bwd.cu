@@ -6,6 +6,8 @@
 // with dG_prev (the gate pre-activation gradients of the previously processed frame) streamed by TMA straight
 // from the dG matrix all CTAs of the direction write; then the cell backward for its units, producing dG[t].
 // dG is written as sb16 [T*B][8H] (operand of the dX GEMM) and transposed [8H][T*B] (operand of the dW GEMMs).
+#include <stdlib.h>
+
 #include "../../include/ssb200.h"
 #include "common.cuh"
 
@@ -16,6 +18,7 @@ constexpr int LB_EPI_WARPS = 16;            // 4 TMEM lane quadrants x 4 column 
 constexpr int LB_THREADS = 64 + 32 * LB_EPI_WARPS;
 constexpr int LB_WCHUNK = 2 * LB_U * 128;   // 4 KB
 constexpr int LB_MAXKC = 38;                // 4H <= 2432
+constexpr int LB_XPITCH = 20;               // floats per row of the lo-row exchange buffer
 
 struct LstmBwdParams {
   const float* gates;        // [T*B][8H] activated gates saved by the forward kernel
@@ -32,7 +35,7 @@ struct LstmBwdParams {
   float* dh0;                // [2][B][H] or null
   float* dc0;
   unsigned int* sync;
-  int T, B, H, R, NC, KC, NS, want_d0;
+  int T, B, H, R, NC, KC, NS, want_d0, ROT;
 };
 
 __global__ void __launch_bounds__(LB_THREADS, 1)
@@ -42,7 +45,8 @@ lstm_bwd_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
   const int stage_bytes = 2 * p.R * 128;
   unsigned char* ring = smem;
   unsigned char* wsm = smem + p.NS * stage_bytes;
-  uint64_t* full = reinterpret_cast<uint64_t*>(wsm + p.KC * LB_WCHUNK);
+  float* xbuf = reinterpret_cast<float*>(wsm + p.KC * LB_WCHUNK);         // [64][LB_XPITCH] dG_lo-row partial sums
+  uint64_t* full = reinterpret_cast<uint64_t*>(xbuf + 64 * LB_XPITCH);
   uint64_t* empty = full + 4;
   uint64_t* accum_full = empty + 4;
   uint64_t* wfull = accum_full + 1;
@@ -54,6 +58,7 @@ lstm_bwd_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
   const int T = p.T, B = p.B, H = p.H;
   const int nsteps = T + (p.want_d0 ? 1 : 0);
   unsigned int* counter = p.sync + dir;
+  const int kc0 = p.ROT ? (cta * p.ROT) % p.KC : 0;
 
   if (threadIdx.x == 0) {
     tma_prefetch_desc(&tmW);
@@ -84,7 +89,8 @@ lstm_bwd_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
         while (ld_acquire(counter) < need) {
         }
         fence_proxy_async();
-        for (int kc = 0; kc < p.KC; ++kc, ++it) {
+        for (int i = 0; i < p.KC; ++i, ++it) {
+          const int kc = (kc0 + i) % p.KC;               // every CTA starts on a different chunk: spreads the L2 slices
           const int st = it % p.NS, ph = (it / p.NS) & 1;
           mbar_wait(&empty[st], ph ^ 1);
           mbar_arrive_expect_tx(&full[st], stage_bytes);
@@ -94,24 +100,31 @@ lstm_bwd_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
     }
   } else if (warp == 1) {
     if (lane == 0) {
-      constexpr uint32_t idesc = umma_idesc_bf16(128, LB_U);
+      // B <= 64: ONE instruction per 16-wide k-step on the stacks A = [dG_hi; dG_lo] (128 rows) and
+      // B = [W_hi; W_lo] (32 rows); the four 64x16 quadrants of D are summed in the epilogue.  (tcgen05.mma costs
+      // >= ~53 cycles per instruction whatever its shape, tools/microbench/mma_rate.cu.)
+      constexpr uint32_t idesc32 = umma_idesc_bf16(128, 2 * LB_U), idesc16 = umma_idesc_bf16(128, LB_U);
+      const bool stacked = p.R == 64;
+      const uint64_t a_base = umma_desc_sw128(smem_u32(ring)), b_base = umma_desc_sw128(smem_u32(wsm));
+      const uint32_t a_stage = stage_bytes >> 4, a_lo_off = (p.R * 128) >> 4;
       mbar_wait(wfull, 0);
       int it = 0;
       for (int s = 1; s < nsteps; ++s) {
-        for (int kc = 0; kc < p.KC; ++kc, ++it) {
+        for (int i = 0; i < p.KC; ++i, ++it) {
+          const int kc = (kc0 + i) % p.KC;
           const int st = it % p.NS, ph = (it / p.NS) & 1;
           mbar_wait(&full[st], ph);
           tc_fence_after();
-          const uint32_t a_hi = smem_u32(ring + st * stage_bytes), a_lo = a_hi + p.R * 128;
-          const uint32_t b_hi = smem_u32(wsm + kc * LB_WCHUNK), b_lo = b_hi + LB_U * 128;
+          const uint64_t da = a_base + (uint32_t)st * a_stage;
+          const uint64_t db = b_base + (uint32_t)kc * (LB_WCHUNK >> 4);
           const int ksteps = min(4, (4 * H - kc * 64 + 15) / 16);
-          for (int k = 0; k < ksteps; ++k) {
-            const uint32_t ko = k * 32;
-            const uint64_t dah = umma_desc_sw128(a_hi + ko), dal = umma_desc_sw128(a_lo + ko);
-            const uint64_t dbh = umma_desc_sw128(b_hi + ko), dbl = umma_desc_sw128(b_lo + ko);
-            umma_bf16(tmem_d, dal, dbh, idesc, (kc | k) ? 1u : 0u);
-            umma_bf16(tmem_d, dah, dbl, idesc, 1u);
-            umma_bf16(tmem_d, dah, dbh, idesc, 1u);
+          if (stacked) {
+            for (int k = 0; k < ksteps; ++k) umma_bf16(tmem_d, da + 2 * k, db + 2 * k, idesc32, (i | k) ? 1u : 0u);
+          } else {
+            for (int k = 0; k < ksteps; ++k) {
+              umma_bf16(tmem_d, da + 2 * k, db + 2 * k, idesc32, (i | k) ? 1u : 0u);          // dG_hi x [W_hi; W_lo]
+              umma_bf16(tmem_d, da + a_lo_off + 2 * k, db + 2 * k, idesc16, 1u);               // dG_lo x W_hi
+            }
           }
           umma_commit(&empty[st]);
         }
@@ -121,10 +134,14 @@ lstm_bwd_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
   } else {
     const int ew = warp - 2;
     const int q = warp & 3, cg = ew >> 2;
-    const int b = q * 32 + lane;
+    const bool stacked = p.R == 64;
+    const bool helper = stacked && q >= 2;                     // these warps own the dG_lo rows of D
+    const int b = (stacked ? (q & 1) : q) * 32 + lane;
     const int ug = j0 + cg * 4;
-    const bool row_ok = b < B && ug < H;
+    const bool row_ok = !helper && b < B && ug < H;
     const int len = row_ok ? p.lens[b] : 0;
+    float* xr = xbuf + b * LB_XPITCH + 4 * cg;
+    const uint32_t trow = tmem_d + ((uint32_t)(q * 32) << 16) + 4 * cg;
     float dc[4] = {0.0f, 0.0f, 0.0f, 0.0f};
     float dh0[4] = {0.0f, 0.0f, 0.0f, 0.0f};
     for (int s = 0; s < nsteps; ++s) {
@@ -146,17 +163,25 @@ lstm_bwd_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
           cp = *reinterpret_cast<const float4*>(p.c0 + ((long long)dir * B + b) * H + ug);
         dov = *reinterpret_cast<const float4*>(p.dout + row * (2LL * H) + dir * H + ug);
       }
-      float d[16];
-#pragma unroll
-      for (int i = 0; i < 16; ++i) d[i] = 0.0f;
+      float dhr[4] = {0.0f, 0.0f, 0.0f, 0.0f};
       if (s > 0) {
-        mbar_wait(accum_full, (s - 1) & 1);
+        if (warp == 2) mbar_wait(accum_full, (s - 1) & 1);     // one warp polls, the others sleep on a hardware barrier
+        asm volatile("bar.sync 2, %0;" ::"n"(32 * LB_EPI_WARPS) : "memory");
         tc_fence_after();
-        tmem_ld16(tmem_d + ((uint32_t)(q * 32) << 16), d);
+        float e[4];
+        tmem_ld4x2(trow, trow + LB_U, dhr, e);                 // x W_hi and x W_lo columns of this thread's 4 units
         tc_fence_before();
+#pragma unroll
+        for (int j = 0; j < 4; ++j) dhr[j] += e[j];
+        if (stacked) {
+          if (helper) *reinterpret_cast<float4*>(xr) = make_float4(dhr[0], dhr[1], dhr[2], dhr[3]);
+          asm volatile("bar.sync 3, %0;" ::"n"(32 * LB_EPI_WARPS) : "memory");
+          if (!helper) {
+            const float4 v = *reinterpret_cast<const float4*>(xr);
+            dhr[0] += v.x; dhr[1] += v.y; dhr[2] += v.z; dhr[3] += v.w;
+          }
+        }
       }
-      const float* dr = d + 4 * cg;                         // this thread's 4 units (all 16 columns were loaded)
-      float dhr[4] = {dr[0], dr[1], dr[2], dr[3]};
       // the row's forward pass started at frame 0 (dir 0) / len-1 (dir 1): one step later dh_rec is d(h0)
       if (row_ok && p.want_d0 && ((dir == 0 && s == T) || (dir == 1 && t == len))) {
 #pragma unroll
@@ -250,6 +275,7 @@ extern "C" int ss_lstm_bwd(const float* gates, const float* cs, const float* c0,
   p.KC = cdiv(4 * H, 64);
   p.NS = p.R == 64 ? 4 : 2;
   p.want_d0 = dh0 != nullptr;
+  p.ROT = getenv("SSB_ROT") ? atoi(getenv("SSB_ROT")) : 1;
   p.sync = (unsigned int*)ws;
   cudaMemsetAsync(ws, 0, 256, st);
 
@@ -268,7 +294,7 @@ extern "C" int ss_lstm_bwd(const float* gates, const float* cs, const float* c0,
     int rc = make_tmap_bf16(&tmG, dG, 3, dims, str, box);
     if (rc) return rc;
   }
-  const int smem = p.NS * 2 * p.R * 128 + p.KC * LB_WCHUNK + 1024 + 256;
+  const int smem = p.NS * 2 * p.R * 128 + p.KC * LB_WCHUNK + 64 * LB_XPITCH * 4 + 1024 + 256;
   cudaFuncSetAttribute(lstm_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
   void* args[] = {(void*)&tmW, (void*)&tmG, (void*)&p};
   cudaError_t e = cudaLaunchCooperativeKernel((void*)lstm_bwd_kernel, dim3(2 * p.NC), dim3(LB_THREADS), args, smem, st);

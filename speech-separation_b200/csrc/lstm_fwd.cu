@@ -43,7 +43,7 @@ struct LstmFwdParams {
   float* hn;                 // [2][B][H]
   float* cn;
   __nv_bfloat16* hbuf;       // [rep][slot 2][dir 2][kc][plane 2][R][64], rows pre-swizzled (SWIZZLE_128B)
-  int REP, EXP;
+  int REP, EXP, ROT;
   unsigned int* sync;        // [2]
   int T, B, H, R, NC, KC, NS;
   long long* dbg;            // optional clock64 trace of CTA 0: [step][32]
@@ -74,6 +74,7 @@ lstm_fwd_kernel(const __grid_constant__ CUtensorMap tmW, LstmFwdParams p) {
   const int u0 = cta * LF_U;
   const int T = p.T, B = p.B, H = p.H;
   unsigned int* counter = p.sync + dir;
+  const int kc0 = p.ROT ? (cta * p.ROT) % p.KC : 0;
 
   if (threadIdx.x == 0) {
     tma_prefetch_desc(&tmW);
@@ -107,7 +108,8 @@ lstm_fwd_kernel(const __grid_constant__ CUtensorMap tmW, LstmFwdParams p) {
         LF_STAMP(1);
         fence_proxy_async();
         const __nv_bfloat16* src = p.hbuf + (((long long)(cta % p.REP) * 2 + (s & 1)) * 2 + dir) * p.KC * blk;
-        for (int kc = 0; kc < p.KC; ++kc, ++it) {
+        for (int i = 0; i < p.KC; ++i, ++it) {
+          const int kc = (kc0 + i) % p.KC;               // every CTA starts on a different chunk: spreads the L2 slices
           const int st = it % p.NS, ph = (it / p.NS) & 1;
           mbar_wait(&empty[st], ph ^ 1);
           mbar_arrive_expect_tx(&full[st], stage_bytes);
@@ -124,19 +126,20 @@ lstm_fwd_kernel(const __grid_constant__ CUtensorMap tmW, LstmFwdParams p) {
       mbar_wait(wfull, 0);
       int it = 0;
       for (int s = 0; s < T; ++s) {
-        for (int kc = 0; kc < p.KC; ++kc, ++it) {
+        for (int i = 0; i < p.KC; ++i, ++it) {
+          const int kc = (kc0 + i) % p.KC;
           const int st = it % p.NS, ph = (it / p.NS) & 1;
           mbar_wait(&full[st], ph);
-          LF_STAMP(kc == 0 ? 3 : 10 + kc);
+          LF_STAMP(i == 0 ? 3 : 10 + i);
           tc_fence_after();
           const uint64_t da = a_base + (uint32_t)st * a_stage;
           const uint64_t db = b_base + (uint32_t)kc * (LF_WCHUNK >> 4);
           const int ksteps = min(4, (H - kc * 64 + 15) / 16);
           if (stacked) {
-            for (int k = 0; k < ksteps; ++k) umma_bf16(tmem_d, da + 2 * k, db + 2 * k, idesc96, (kc | k) ? 1u : 0u);
+            for (int k = 0; k < ksteps; ++k) umma_bf16(tmem_d, da + 2 * k, db + 2 * k, idesc96, (i | k) ? 1u : 0u);
           } else {
             for (int k = 0; k < ksteps; ++k) {
-              umma_bf16(tmem_d, da + 2 * k, db + 2 * k, idesc96, (kc | k) ? 1u : 0u);          // h_hi x [W_hi; W_lo]
+              umma_bf16(tmem_d, da + 2 * k, db + 2 * k, idesc96, (i | k) ? 1u : 0u);           // h_hi x [W_hi; W_lo]
               umma_bf16(tmem_d, da + a_lo_off + 2 * k, db + 2 * k, idesc48, 1u);               // h_lo x W_hi
             }
           }
@@ -325,6 +328,7 @@ extern "C" int ss_lstm_fwd(float* gx, const void* whh_r, long long whh_ld, long 
   p.NS = p.R == 64 ? 5 : 2;
   p.REP = lstm_rep();
   p.EXP = getenv("SSB_EXP") ? atoi(getenv("SSB_EXP")) : 0;
+  p.ROT = getenv("SSB_ROT") ? atoi(getenv("SSB_ROT")) : 1;
   const long long hbuf_bytes = (long long)p.REP * 2 * 2 * p.KC * 2 * p.R * 64 * 2;
   p.hbuf = (__nv_bfloat16*)ws;
   p.sync = (unsigned int*)((char*)ws + hbuf_bytes);
