@@ -10,6 +10,7 @@
 
 #include "../../include/ssb200.h"
 #include "common.cuh"
+#include "lstm_bwd.cuh"
 
 namespace ssb {
 
@@ -20,23 +21,6 @@ constexpr int LB_WCHUNK = 2 * LB_U * 128;   // 4 KB
 constexpr int LB_MAXKC = 38;                // 4H <= 2432
 constexpr int LB_XPITCH = 20;               // floats per row of the lo-row exchange buffer
 
-struct LstmBwdParams {
-  const float* gates;        // [T*B][8H] activated gates saved by the forward kernel
-  const float* cs;           // [T*B][2H] cell states
-  const float* c0;           // [2][B][H]
-  const float* dout;         // [T*B][2H] gradient wrt the layer output
-  const float* dhn;          // [2][B][H] or null: gradient wrt (h_n, c_n)
-  const float* dcn;
-  const int* lens;
-  __nv_bfloat16* dG;         // sb16 [T*B][8H]
-  long long dG_plane;
-  __nv_bfloat16* dGT;        // sb16 [8H][ldT]
-  long long ldT, dGT_plane;
-  float* dh0;                // [2][B][H] or null
-  float* dc0;
-  unsigned int* sync;
-  int T, B, H, R, NC, KC, NS, want_d0, ROT;
-};
 
 __global__ void __launch_bounds__(LB_THREADS, 1)
 lstm_bwd_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUtensorMap tmG, LstmBwdParams p) {
@@ -278,6 +262,7 @@ extern "C" int ss_lstm_bwd(const float* gates, const float* cs, const float* c0,
   p.ROT = getenv("SSB_ROT") ? atoi(getenv("SSB_ROT")) : 1;
   p.sync = (unsigned int*)ws;
   cudaMemsetAsync(ws, 0, 256, st);
+  if (H == 600 && B <= 64 && !getenv("SSB_BWD_V1")) return launch_lstm_bwd_ks(p, whhT, whhT_ld, whhT_plane, st);
 
   CUtensorMap tmW, tmG;
   {

@@ -1,0 +1,338 @@
+// K2c (fast path): backward LSTM recurrence with the K dimension split over 4-CTA clusters.
+// Same contract as lstm_bwd.cu (which stays as the generic path); used for the reference's shape H = 600, B <= 64.
+//
+//   dh_rec[b][j] = sum_{n < 4H} dG_prev[b][n] * W_hh[n][j]            (n = 4u+gate, interleaved)
+//
+// has K = 4H = 2400: an output-stationary CTA must stream all of dG_prev (614 KB split-bf16) through shared memory
+// every step, and TMA delivers ~58 B/clk per SM (tools/microbench/bulk_rate.cu) -> >= 10.6k cycles per step.  Here a
+// cluster of 4 CTAs owns 64 hidden units; CTA r streams only K-quarter r of dG_prev (154 KB), multiplies it with
+// its resident [K-quarter x 64 units] slice of W_hh^T (one stacked tcgen05.mma per 16-wide k-step: A = dG rows with
+// hi/lo planes interleaved, B = [W_hi; W_lo], D = 128 x 128 in TMEM), and the four partial products are reduced over
+// distributed shared memory: every CTA adds the hi/lo row pairs with a warp shuffle and sends each peer the
+// 64 x 16 block of the 16 units that peer finalises (st.async, completion counted on the peer's mbarrier).
+// Each CTA then runs the cell backward for its 16 units, writes dG[t] and publishes it (gpu-scope release counter).
+#include <stdlib.h>
+
+#include "../../include/ssb200.h"
+#include "common.cuh"
+#include "lstm_bwd.cuh"
+
+namespace ssb {
+
+constexpr int KS_CL = 4;                       // CTAs per cluster
+constexpr int KS_UC = 64;                      // hidden units per cluster
+constexpr int KS_U = KS_UC / KS_CL;            // units finalised per CTA
+constexpr int KS_H = 600;
+constexpr int KS_NCL = (KS_H + KS_UC - 1) / KS_UC;      // clusters per direction (10)
+constexpr int KS_NCTA = KS_NCL * KS_CL;                 // CTAs per direction (40)
+constexpr int KS_KCH = (4 * KS_H + 63) / 64;            // 64-wide K chunks in total (38; the last holds 32 columns)
+constexpr int KS_MAXCH = 10;                            // chunks per CTA: 10, 10, 9, 9
+constexpr int KS_NS = 3;                                // dG ring stages
+constexpr int KS_CHUNK = 16384;                         // one chunk of either operand: 128 rows x 128 B
+constexpr int KS_EPI_WARPS = 16;
+constexpr int KS_THREADS = 64 + 32 * KS_EPI_WARPS;
+constexpr int KS_RBUF = KS_CL * 64 * KS_U * 4;          // [src][b][16 floats]
+constexpr int KS_SMEM = KS_MAXCH * KS_CHUNK + KS_NS * KS_CHUNK + KS_RBUF + 1024 + 256;
+
+__device__ __forceinline__ int ks_chunk_begin(int r) { return r < 2 ? 10 * r : 20 + 9 * (r - 2); }
+
+__device__ __forceinline__ uint32_t cluster_rank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ uint32_t map_to_rank(uint32_t saddr, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(saddr), "r"(rank));
+  return r;
+}
+// 16-byte store into a peer CTA's shared memory; the bytes are counted on that CTA's mbarrier when they land.
+__device__ __forceinline__ void st_async_v4(uint32_t raddr, float a, float b, float c, float d, uint32_t rbar) {
+  asm volatile("st.async.weak.shared::cluster.mbarrier::complete_tx::bytes.v4.f32 [%0], {%1, %2, %3, %4}, [%5];" ::"r"(raddr),
+               "f"(a), "f"(b), "f"(c), "f"(d), "r"(rbar)
+               : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait_cluster(uint64_t* bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+
+__global__ void __launch_bounds__(KS_THREADS, 1)
+lstm_bwd_ks_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUtensorMap tmG, LstmBwdParams p) {
+  extern __shared__ unsigned char smem_raw[];
+  unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  unsigned char* wsm = smem;                                   // KS_MAXCH chunks of [W_hi 64 units; W_lo 64 units]
+  unsigned char* ring = smem + KS_MAXCH * KS_CHUNK;            // KS_NS chunks of dG_prev, rows = 2*b + plane
+  float* rbuf = reinterpret_cast<float*>(ring + KS_NS * KS_CHUNK);   // [src][b][16], 16-byte pieces XOR-swizzled
+  uint64_t* full = reinterpret_cast<uint64_t*>(reinterpret_cast<unsigned char*>(rbuf) + KS_RBUF);
+  uint64_t* empty = full + KS_NS;
+  uint64_t* accum_full = empty + KS_NS;
+  uint64_t* wfull = accum_full + 1;
+  uint64_t* rfull = wfull + 1;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(rfull + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int rank = (int)cluster_rank();
+  const int cl = blockIdx.x / KS_CL;
+  const int dir = cl / KS_NCL, c = cl % KS_NCL;
+  const int T = p.T, B = p.B;
+  constexpr int H = KS_H;
+  const int nsteps = T + (p.want_d0 ? 1 : 0);
+  const int ch0 = ks_chunk_begin(rank), nch = rank < 2 ? 10 : 9;
+  unsigned int* counter = p.sync + dir;
+
+  if (threadIdx.x == 0) {
+    tma_prefetch_desc(&tmW);
+    tma_prefetch_desc(&tmG);
+    for (int s = 0; s < KS_NS; ++s) {
+      mbar_init(&full[s], 1);
+      mbar_init(&empty[s], 1);
+    }
+    mbar_init(accum_full, 1);
+    mbar_init(wfull, 1);
+    mbar_init(rfull, 1);
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc<128>(tmem_slot);
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();                                          // peers' mbarriers exist before anyone sends
+  tc_fence_after();
+  const uint32_t tmem_d = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      mbar_arrive_expect_tx(wfull, nch * KS_CHUNK);
+      for (int i = 0; i < nch; ++i) tma_load_3d(wsm + i * KS_CHUNK, &tmW, wfull, (ch0 + i) * 64, dir * H + c * KS_UC, 0);
+      uint32_t phase = 0;                                      // bit st = parity of the next wait on empty[st]
+      for (int s = 1; s < nsteps; ++s) {
+        const int tp = dir ? (s - 1) : (T - s);                // frame whose dG this step consumes
+        const unsigned int need = (unsigned int)KS_NCTA * (unsigned int)s;
+        while (ld_acquire(counter) < need) {
+        }
+        fence_proxy_async();
+#pragma unroll
+        for (int i = 0; i < KS_MAXCH; ++i) {
+          if (i < nch) {
+            constexpr int dummy = 0;
+            (void)dummy;
+            const int st = i % KS_NS;
+            mbar_wait(&empty[st], ((phase >> st) & 1) ^ 1);
+            phase ^= 1u << st;
+            mbar_arrive_expect_tx(&full[st], KS_CHUNK);
+            tma_load_3d(ring + st * KS_CHUNK, &tmG, &full[st], dir * 4 * H + (ch0 + i) * 64, 0, tp * B);
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc = umma_idesc_bf16(128, 128);
+      const uint64_t a_base = umma_desc_sw128(smem_u32(ring)), b_base = umma_desc_sw128(smem_u32(wsm));
+      mbar_wait(wfull, 0);
+      uint32_t phase = 0;
+      for (int s = 1; s < nsteps; ++s) {
+#pragma unroll
+        for (int i = 0; i < KS_MAXCH; ++i) {
+          if (i < nch) {
+            const int st = i % KS_NS;
+            mbar_wait(&full[st], (phase >> st) & 1);
+            phase ^= 1u << st;
+            tc_fence_after();
+            const uint64_t da = a_base + (uint32_t)(st * (KS_CHUNK >> 4));
+            const uint64_t db = b_base + (uint32_t)(i * (KS_CHUNK >> 4));
+            const bool last = ch0 + i == KS_KCH - 1;           // 32 valid columns: 2 k-steps
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+              if (k < 2 || !last) umma_bf16(tmem_d, da + 2 * k, db + 2 * k, idesc, (i | k) ? 1u : 0u);
+            umma_commit(&empty[st]);
+          }
+        }
+        umma_commit(accum_full);
+      }
+    }
+  } else {
+    const int ew = warp - 2;
+    const int q = warp & 3, dst = ew >> 2;                     // TMEM lane quadrant; peer this warp's columns go to
+    const int sb = 16 * q + (lane >> 1), half = lane & 1;      // sender role: batch row, which 8 of the 16 floats
+    const int fb = (ew & 1) * 32 + lane, u2 = ew >> 1;         // final role: batch row, unit pair
+    const int ul = 2 * u2;                                     // unit within this CTA's 16
+    const int ug = c * KS_UC + rank * KS_U + ul;               // unit within the direction
+    const bool row_ok = fb < B && ug < H;
+    const int len = row_ok ? p.lens[fb] : 0;
+    const uint32_t trow = tmem_d + ((uint32_t)(q * 32) << 16);
+    const uint32_t rbar = map_to_rank(smem_u32(rfull), (uint32_t)dst);
+    const uint32_t rdst = map_to_rank(smem_u32(rbuf), (uint32_t)dst) + (uint32_t)((rank * 64 + sb) * 64);
+    const int ssw = (sb >> 1) & 3, fsw = (fb >> 1) & 3;
+    float dc[2] = {0.0f, 0.0f};
+    float dh0[2] = {0.0f, 0.0f};
+    for (int s = 0; s < nsteps; ++s) {
+      const int t = dir ? s : (T - 1 - s);                     // t == -1 / T on the extra step
+      const bool in_range = s < T;
+      const bool active = row_ok && in_range && t < len;
+      const long long row = (long long)(in_range ? t : 0) * B + (row_ok ? fb : 0);
+      float4 g4[2];
+      float2 ct = make_float2(0.f, 0.f), cp = ct, dov = ct;
+      if (s > 0 && ew == 0 && lane == 0) mbar_arrive_expect_tx(rfull, KS_RBUF);
+      if (active) {
+        const float4* gp = reinterpret_cast<const float4*>(p.gates + row * (8LL * H) + (long long)dir * 4 * H + 4 * ug);
+        g4[0] = gp[0];
+        g4[1] = gp[1];
+        ct = *reinterpret_cast<const float2*>(p.cs + row * (2LL * H) + dir * H + ug);
+        const int tprev = dir ? t + 1 : t - 1;                 // frame the forward pass processed before t
+        if (tprev >= 0 && tprev < len)
+          cp = *reinterpret_cast<const float2*>(p.cs + ((long long)tprev * B + fb) * (2LL * H) + dir * H + ug);
+        else
+          cp = *reinterpret_cast<const float2*>(p.c0 + ((long long)dir * B + fb) * H + ug);
+        dov = *reinterpret_cast<const float2*>(p.dout + row * (2LL * H) + dir * H + ug);
+      }
+      float dhr[2] = {0.0f, 0.0f};
+      if (s > 0) {
+        if (warp == 2) mbar_wait(accum_full, (s - 1) & 1);     // one warp polls, the others sleep on a hardware barrier
+        asm volatile("bar.sync 2, %0;" ::"n"(32 * KS_EPI_WARPS) : "memory");
+        tc_fence_after();
+        float v[16], e[16];
+        tmem_ld16(trow + 16 * dst, v);                         // x W_hi columns of the 16 units peer `dst` finalises
+        tmem_ld16(trow + 64 + 16 * dst, e);                    // x W_lo columns
+        tc_fence_before();
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+          v[i] += e[i];
+          v[i] += __shfl_xor_sync(0xffffffffu, v[i], 1);       // lanes 2b, 2b+1 hold the hi / lo plane rows of b
+        }
+        {
+          const float* w = v + 8 * half;
+          const uint32_t a0 = rdst + (uint32_t)(((2 * half) ^ ssw) * 16), a1 = rdst + (uint32_t)(((2 * half + 1) ^ ssw) * 16);
+          st_async_v4(a0, half ? v[8] : v[0], half ? v[9] : v[1], half ? v[10] : v[2], half ? v[11] : v[3], rbar);
+          st_async_v4(a1, half ? v[12] : v[4], half ? v[13] : v[5], half ? v[14] : v[6], half ? v[15] : v[7], rbar);
+          (void)w;
+        }
+        while (!mbar_try_wait_cluster(rfull, (s - 1) & 1)) {
+        }
+        const float* rb = rbuf + fb * 16 + (((u2 >> 1) ^ fsw) * 4) + (u2 & 1) * 2;
+#pragma unroll
+        for (int r = 0; r < KS_CL; ++r) {
+          const float2 x = *reinterpret_cast<const float2*>(rb + r * 64 * 16);
+          dhr[0] += x.x;
+          dhr[1] += x.y;
+        }
+      }
+      // the row's forward pass started at frame 0 (dir 0) / len-1 (dir 1): one step later dh_rec is d(h0)
+      if (row_ok && p.want_d0 && ((dir == 0 && s == T) || (dir == 1 && t == len))) {
+        dh0[0] = dhr[0];
+        dh0[1] = dhr[1];
+      }
+      float dgv[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) dgv[i] = 0.0f;
+      if (active) {
+        const bool first = dir ? (t == 0) : (t == len - 1);    // first frame of this row in backward order
+        const float cta_[2] = {ct.x, ct.y}, cpa[2] = {cp.x, cp.y}, doa[2] = {dov.x, dov.y};
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+          float dh = doa[j] + dhr[j];
+          float dct = dc[j];
+          if (first && p.dhn) {
+            dh += p.dhn[((long long)dir * B + fb) * H + ug + j];
+            dct += p.dcn[((long long)dir * B + fb) * H + ug + j];
+          }
+          const float gi = g4[j].x, gf = g4[j].y, gg = g4[j].z, go = g4[j].w;
+          const float tc = tanhf_(cta_[j]);
+          dct += dh * go * (1.0f - tc * tc);
+          dgv[4 * j + 0] = dct * gg * gi * (1.0f - gi);
+          dgv[4 * j + 1] = dct * cpa[j] * gf * (1.0f - gf);
+          dgv[4 * j + 2] = dct * gi * (1.0f - gg * gg);
+          dgv[4 * j + 3] = dh * tc * go * (1.0f - go);
+          dc[j] = dct * gf;
+        }
+      }
+      __nv_bfloat16 hi[8], lo[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) split_bf16(dgv[i], hi[i], lo[i]);
+      if (row_ok && in_range) {
+        __nv_bfloat16* o = p.dG + row * (8LL * H) + (long long)dir * 4 * H + 4 * ug;
+        *reinterpret_cast<uint4*>(o) = *reinterpret_cast<uint4*>(hi);
+        *reinterpret_cast<uint4*>(o + p.dG_plane) = *reinterpret_cast<uint4*>(lo);
+      }
+      asm volatile("bar.sync 1, %0;" ::"n"(32 * KS_EPI_WARPS) : "memory");
+      if (threadIdx.x == 64) {
+        __threadfence();
+        fence_proxy_async();
+        red_release_add(counter, 1u);
+      }
+      if (row_ok && in_range) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const long long oT = ((long long)dir * 4 * H + 4 * ug + i) * p.ldT + row;
+          p.dGT[oT] = hi[i];
+          p.dGT[oT + p.dGT_plane] = lo[i];
+        }
+      }
+    }
+    if (row_ok && p.want_d0) {
+#pragma unroll
+      for (int j = 0; j < 2; ++j) {
+        p.dh0[((long long)dir * B + fb) * H + ug + j] = dh0[j];
+        p.dc0[((long long)dir * B + fb) * H + ug + j] = dc[j];
+      }
+    }
+  }
+  __syncthreads();
+  cluster_sync_all();                                          // nobody leaves while a peer may still address it
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_free<128>(tmem_d);
+  }
+}
+
+int launch_lstm_bwd_ks(const LstmBwdParams& p, const void* whhT, long long whhT_ld, long long whhT_plane, cudaStream_t st) {
+  const int H = KS_H;
+  CUtensorMap tmW, tmG;
+  {
+    uint64_t dims[3] = {(uint64_t)4 * H, (uint64_t)2 * H, 2};
+    uint64_t str[2] = {(uint64_t)whhT_ld * 2, (uint64_t)whhT_plane * 2};
+    uint32_t box[3] = {64, KS_UC, 2};
+    int rc = make_tmap_bf16(&tmW, whhT, 3, dims, str, box);
+    if (rc) return rc;
+  }
+  {  // (columns, plane, row): a box lands in shared memory as rows 2*b + plane
+    uint64_t dims[3] = {(uint64_t)8 * H, 2, (uint64_t)p.T * p.B};
+    uint64_t str[2] = {(uint64_t)p.dG_plane * 2, (uint64_t)8 * H * 2};
+    uint32_t box[3] = {64, 2, 64};
+    int rc = make_tmap_bf16(&tmG, p.dG, 3, dims, str, box);
+    if (rc) return rc;
+  }
+  cudaFuncSetAttribute(lstm_bwd_ks_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, KS_SMEM);
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(2 * KS_NCTA);
+  cfg.blockDim = dim3(KS_THREADS);
+  cfg.dynamicSmemBytes = KS_SMEM;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[2];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = KS_CL;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  attr[1].id = cudaLaunchAttributeCooperative;
+  attr[1].val.cooperative = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 2;
+  cudaError_t e = cudaLaunchKernelEx(&cfg, lstm_bwd_ks_kernel, tmW, tmG, p);
+  if (e != cudaSuccess) {
+    set_error("ss_lstm_bwd (K-split clusters): launch failed: %s", cudaGetErrorString(e));
+    return -2;
+  }
+  return 0;
+}
+
+}  // namespace ssb

@@ -49,20 +49,25 @@ struct LstmFwdParams {
   long long* dbg;            // optional clock64 trace of CTA 0: [step][32]
 };
 
-#define LF_STAMP(slot)                                               \
-  do {                                                               \
-    if (p.dbg && blockIdx.x == 0) p.dbg[s * 32 + (slot)] = clock64(); \
+#define LF_STAMP(slot)                                                        \
+  do {                                                                        \
+    if (!FAST && p.dbg && blockIdx.x == 0) p.dbg[s * 32 + (slot)] = clock64(); \
   } while (0)
 
+// FAST: H = 600, B <= 64 (R = 64), no rotation, no trace -- the reference's shape; every loop bound is a constant so
+// the single MMA-issuing thread runs a fully unrolled instruction stream (its scalar overhead, not the tensor
+// pipe, paced the generic loop: tools/microbench/bulk_rate.cu).
+template <bool FAST>
 __global__ void __launch_bounds__(LF_THREADS, 1)
 lstm_fwd_kernel(const __grid_constant__ CUtensorMap tmW, LstmFwdParams p) {
   extern __shared__ unsigned char smem_raw[];
   unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-  const int stage_bytes = 2 * p.R * 128;
-  const bool stacked = p.R == 64;                              // A operand = [h_hi; h_lo] as one 128-row tile
+  const int PR = FAST ? 64 : p.R, PKC = FAST ? 10 : p.KC, PNS = FAST ? 5 : p.NS;
+  const int stage_bytes = 2 * PR * 128;
+  const bool stacked = PR == 64;                               // A operand = [h_hi; h_lo] as one 128-row tile
   unsigned char* ring = smem;                                  // NS stages of h_prev chunks
-  unsigned char* wsm = smem + p.NS * stage_bytes;              // KC chunks of the W slice
-  float* xbuf = reinterpret_cast<float*>(wsm + p.KC * LF_WCHUNK);          // [64][LF_XPITCH] lo-row partial sums
+  unsigned char* wsm = smem + PNS * stage_bytes;               // KC chunks of the W slice
+  float* xbuf = reinterpret_cast<float*>(wsm + PKC * LF_WCHUNK);           // [64][LF_XPITCH] lo-row partial sums
   uint64_t* full = reinterpret_cast<uint64_t*>(xbuf + 64 * LF_XPITCH);
   uint64_t* empty = full + 8;
   uint64_t* accum_full = empty + 8;
@@ -72,13 +77,13 @@ lstm_fwd_kernel(const __grid_constant__ CUtensorMap tmW, LstmFwdParams p) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int dir = blockIdx.x / p.NC, cta = blockIdx.x % p.NC;
   const int u0 = cta * LF_U;
-  const int T = p.T, B = p.B, H = p.H;
+  const int T = p.T, B = p.B, H = FAST ? 600 : p.H;
   unsigned int* counter = p.sync + dir;
-  const int kc0 = p.ROT ? (cta * p.ROT) % p.KC : 0;
+  const int kc0 = (!FAST && p.ROT) ? (cta * p.ROT) % p.KC : 0;
 
   if (threadIdx.x == 0) {
     tma_prefetch_desc(&tmW);
-    for (int s = 0; s < p.NS; ++s) {
+    for (int s = 0; s < PNS; ++s) {
       mbar_init(&full[s], 1);
       mbar_init(&empty[s], 1);
     }
@@ -96,9 +101,9 @@ lstm_fwd_kernel(const __grid_constant__ CUtensorMap tmW, LstmFwdParams p) {
 
   if (warp == W_PROD) {
     if (lane == 0) {
-      mbar_arrive_expect_tx(wfull, p.KC * LF_WCHUNK);
-      for (int kc = 0; kc < p.KC; ++kc) tma_load_3d(wsm + kc * LF_WCHUNK, &tmW, wfull, kc * 64, dir * 4 * H + 4 * u0, 0);
-      const long long blk = 2LL * p.R * 64;                    // elements per (slot,dir,kc) block
+      mbar_arrive_expect_tx(wfull, PKC * LF_WCHUNK);
+      for (int kc = 0; kc < PKC; ++kc) tma_load_3d(wsm + kc * LF_WCHUNK, &tmW, wfull, kc * 64, dir * 4 * H + 4 * u0, 0);
+      const long long blk = 2LL * PR * 64;                     // elements per (slot,dir,kc) block
       int it = 0;
       for (int s = 0; s < T; ++s) {
         const unsigned int need = (unsigned int)p.NC * (unsigned int)(s + 1);
@@ -107,10 +112,11 @@ lstm_fwd_kernel(const __grid_constant__ CUtensorMap tmW, LstmFwdParams p) {
         }
         LF_STAMP(1);
         fence_proxy_async();
-        const __nv_bfloat16* src = p.hbuf + (((long long)(cta % p.REP) * 2 + (s & 1)) * 2 + dir) * p.KC * blk;
-        for (int i = 0; i < p.KC; ++i, ++it) {
-          const int kc = (kc0 + i) % p.KC;               // every CTA starts on a different chunk: spreads the L2 slices
-          const int st = it % p.NS, ph = (it / p.NS) & 1;
+        const __nv_bfloat16* src = p.hbuf + (((long long)(cta % p.REP) * 2 + (s & 1)) * 2 + dir) * PKC * blk;
+#pragma unroll
+        for (int i = 0; i < PKC; ++i, ++it) {
+          const int kc = FAST ? i : (kc0 + i) % PKC;     // (generic path: optional per-CTA chunk rotation)
+          const int st = FAST ? i % 5 : it % PNS, ph = FAST ? (i / 5) & 1 : (it / PNS) & 1;
           mbar_wait(&empty[st], ph ^ 1);
           mbar_arrive_expect_tx(&full[st], stage_bytes);
           bulk_load(ring + st * stage_bytes, src + kc * blk, stage_bytes, &full[st]);
@@ -122,13 +128,14 @@ lstm_fwd_kernel(const __grid_constant__ CUtensorMap tmW, LstmFwdParams p) {
     if (lane == 0) {
       const uint32_t idesc96 = umma_idesc_bf16(128, 2 * LF_N), idesc48 = umma_idesc_bf16(128, LF_N);
       const uint64_t a_base = umma_desc_sw128(smem_u32(ring)), b_base = umma_desc_sw128(smem_u32(wsm));
-      const uint32_t a_stage = stage_bytes >> 4, a_lo_off = (p.R * 128) >> 4;
+      const uint32_t a_stage = stage_bytes >> 4, a_lo_off = (PR * 128) >> 4;
       mbar_wait(wfull, 0);
       int it = 0;
       for (int s = 0; s < T; ++s) {
-        for (int i = 0; i < p.KC; ++i, ++it) {
-          const int kc = (kc0 + i) % p.KC;
-          const int st = it % p.NS, ph = (it / p.NS) & 1;
+#pragma unroll
+        for (int i = 0; i < PKC; ++i, ++it) {
+          const int kc = FAST ? i : (kc0 + i) % PKC;
+          const int st = FAST ? i % 5 : it % PNS, ph = FAST ? (i / 5) & 1 : (it / PNS) & 1;
           mbar_wait(&full[st], ph);
           LF_STAMP(i == 0 ? 3 : 10 + i);
           tc_fence_after();
@@ -136,7 +143,9 @@ lstm_fwd_kernel(const __grid_constant__ CUtensorMap tmW, LstmFwdParams p) {
           const uint64_t db = b_base + (uint32_t)kc * (LF_WCHUNK >> 4);
           const int ksteps = min(4, (H - kc * 64 + 15) / 16);
           if (stacked) {
-            for (int k = 0; k < ksteps; ++k) umma_bf16(tmem_d, da + 2 * k, db + 2 * k, idesc96, (i | k) ? 1u : 0u);
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+              if (k < ksteps) umma_bf16(tmem_d, da + 2 * k, db + 2 * k, idesc96, (i | k) ? 1u : 0u);
           } else {
             for (int k = 0; k < ksteps; ++k) {
               umma_bf16(tmem_d, da + 2 * k, db + 2 * k, idesc96, (i | k) ? 1u : 0u);           // h_hi x [W_hi; W_lo]
@@ -166,7 +175,7 @@ lstm_fwd_kernel(const __grid_constant__ CUtensorMap tmW, LstmFwdParams p) {
     const int kc_w = ug >> 6;
     const int o = (ug & 63) * 2;
     const long long row_off = (long long)b * 64 + ((((o >> 4) ^ (b & 7)) << 4) + (o & 15)) / 2;   // elements
-    const long long blk = 2LL * p.R * 64;
+    const long long blk = 2LL * PR * 64;
     int dbg_s = 0;
     auto publish = [&](int slot) {
       if (row_ok) {
@@ -174,20 +183,19 @@ lstm_fwd_kernel(const __grid_constant__ CUtensorMap tmW, LstmFwdParams p) {
 #pragma unroll
         for (int j = 0; j < 4; ++j) split_bf16(h[j], hi[j], lo[j]);
         for (int r = 0; r < p.REP; ++r) {
-          __nv_bfloat16* dst = p.hbuf + ((((long long)r * 2 + slot) * 2 + dir) * p.KC + kc_w) * blk + row_off;
+          __nv_bfloat16* dst = p.hbuf + ((((long long)r * 2 + slot) * 2 + dir) * PKC + kc_w) * blk + row_off;
           *reinterpret_cast<uint2*>(dst) = *reinterpret_cast<uint2*>(hi);
-          *reinterpret_cast<uint2*>(dst + p.R * 64) = *reinterpret_cast<uint2*>(lo);
+          *reinterpret_cast<uint2*>(dst + PR * 64) = *reinterpret_cast<uint2*>(lo);
         }
       }
       // CTA barrier, then ONE thread releases at gpu scope (cumulative over the other threads' stores, the
       // cooperative-groups grid.sync pattern) and orders them against the consumers' async-proxy reads.
-      if (threadIdx.x == 0 && p.dbg && blockIdx.x == 0) p.dbg[dbg_s * 32 + 20] = clock64();
+      if (!FAST && threadIdx.x == 0 && p.dbg && blockIdx.x == 0) p.dbg[dbg_s * 32 + 20] = clock64();
       asm volatile("bar.sync 1, %0;" ::"n"(32 * LF_EPI_WARPS) : "memory");
       if (threadIdx.x == 0) {
-        if (p.dbg && blockIdx.x == 0) p.dbg[dbg_s * 32 + 21] = clock64();
-        if (p.dbg && blockIdx.x == 0) p.dbg[dbg_s * 32 + 22] = clock64();
+        if (!FAST && p.dbg && blockIdx.x == 0) p.dbg[dbg_s * 32 + 21] = clock64();
         red_release_add(counter, 1u);
-        if (p.dbg && blockIdx.x == 0) p.dbg[dbg_s * 32 + 23] = clock64();
+        if (!FAST && p.dbg && blockIdx.x == 0) p.dbg[dbg_s * 32 + 23] = clock64();
       }
     };
     publish(0);
@@ -328,7 +336,7 @@ extern "C" int ss_lstm_fwd(float* gx, const void* whh_r, long long whh_ld, long 
   p.NS = p.R == 64 ? 5 : 2;
   p.REP = lstm_rep();
   p.EXP = getenv("SSB_EXP") ? atoi(getenv("SSB_EXP")) : 0;
-  p.ROT = getenv("SSB_ROT") ? atoi(getenv("SSB_ROT")) : 1;
+  p.ROT = getenv("SSB_ROT") ? atoi(getenv("SSB_ROT")) : 0;
   const long long hbuf_bytes = (long long)p.REP * 2 * 2 * p.KC * 2 * p.R * 64 * 2;
   p.hbuf = (__nv_bfloat16*)ws;
   p.sync = (unsigned int*)((char*)ws + hbuf_bytes);
@@ -343,9 +351,11 @@ extern "C" int ss_lstm_fwd(float* gx, const void* whh_r, long long whh_ld, long 
     if (rc) return rc;
   }
   const int smem = p.NS * 2 * p.R * 128 + p.KC * LF_WCHUNK + 64 * LF_XPITCH * 4 + 1024 + 256;
-  cudaFuncSetAttribute(lstm_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+  const bool fast = H == 600 && p.R == 64 && p.ROT == 0 && p.dbg == nullptr && !getenv("SSB_GENERIC");
+  void* kern = fast ? (void*)lstm_fwd_kernel<true> : (void*)lstm_fwd_kernel<false>;
+  cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
   void* args[] = {(void*)&tmW, (void*)&p};
-  cudaError_t e = cudaLaunchCooperativeKernel((void*)lstm_fwd_kernel, dim3(2 * p.NC), dim3(LF_THREADS), args, smem, st);
+  cudaError_t e = cudaLaunchCooperativeKernel(kern, dim3(2 * p.NC), dim3(LF_THREADS), args, smem, st);
   if (e != cudaSuccess) {
     set_error("ss_lstm_fwd: cooperative launch failed: %s", cudaGetErrorString(e));
     return -2;
