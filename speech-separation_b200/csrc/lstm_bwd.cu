@@ -214,14 +214,6 @@ lstm_bwd_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
         fence_proxy_async();
         red_release_add(counter, 1u);
       }
-      if (row_ok && in_range) {
-#pragma unroll
-        for (int i = 0; i < 16; ++i) {
-          const long long oT = ((long long)dir * 4 * H + 4 * ug + i) * p.ldT + row;
-          p.dGT[oT] = hi[i];
-          p.dGT[oT + p.dGT_plane] = lo[i];
-        }
-      }
     }
     if (row_ok && p.want_d0) {
 #pragma unroll
@@ -259,10 +251,15 @@ extern "C" int ss_lstm_bwd(const float* gates, const float* cs, const float* c0,
   p.KC = cdiv(4 * H, 64);
   p.NS = p.R == 64 ? 4 : 2;
   p.want_d0 = dh0 != nullptr;
+  p.dbg = g_lstm_dbg;
   p.ROT = getenv("SSB_ROT") ? atoi(getenv("SSB_ROT")) : 1;
   p.sync = (unsigned int*)ws;
   cudaMemsetAsync(ws, 0, 256, st);
-  if (H == 600 && B <= 64 && !getenv("SSB_BWD_V1")) return launch_lstm_bwd_ks(p, whhT, whhT_ld, whhT_plane, st);
+  if (H == 600 && B <= 64 && !getenv("SSB_BWD_V1")) {
+    int rc = launch_lstm_bwd_ks(p, whhT, whhT_ld, whhT_plane, st);
+    if (rc) return rc;
+    return launch_transpose_sb16(dG, 8LL * H, dG_plane, T * B, 8 * H, dGT, ldT, dGT_plane, st);
+  }
 
   CUtensorMap tmW, tmG;
   {
@@ -287,5 +284,5 @@ extern "C" int ss_lstm_bwd(const float* gates, const float* cs, const float* c0,
     set_error("ss_lstm_bwd: cooperative launch failed: %s", cudaGetErrorString(e));
     return -2;
   }
-  return 0;
+  return launch_transpose_sb16(dG, 8LL * H, dG_plane, T * B, 8 * H, dGT, ldT, dGT_plane, st);
 }

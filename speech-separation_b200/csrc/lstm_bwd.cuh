@@ -20,7 +20,10 @@ struct LstmBwdParams {
   float* dc0;
   unsigned int* sync;
   int T, B, H, R, NC, KC, NS, want_d0, ROT;
+  long long* dbg;            // optional clock64 trace of CTA 0: [step][32]
 };
+
+extern long long* g_lstm_dbg;   // set by ss_lstm_debug (lstm_fwd.cu)
 
 // K-split cluster variant (H = 600, B <= 64); returns 0 / negative error like the C ABI.
 int launch_lstm_bwd_ks(const LstmBwdParams& p, const void* whhT, long long whhT_ld, long long whhT_plane, cudaStream_t st);

@@ -67,6 +67,12 @@ __device__ __forceinline__ bool mbar_try_wait_cluster(uint64_t* bar, uint32_t pa
   return ok != 0;
 }
 
+#define KS_STAMP(slot)                                                 \
+  do {                                                                 \
+    if (DBG && blockIdx.x == 0) p.dbg[s * 32 + (slot)] = clock64();    \
+  } while (0)
+
+template <bool DBG>
 __global__ void __launch_bounds__(KS_THREADS, 1)
 lstm_bwd_ks_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUtensorMap tmG, LstmBwdParams p) {
   extern __shared__ unsigned char smem_raw[];
@@ -118,14 +124,14 @@ lstm_bwd_ks_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
       for (int s = 1; s < nsteps; ++s) {
         const int tp = dir ? (s - 1) : (T - s);                // frame whose dG this step consumes
         const unsigned int need = (unsigned int)KS_NCTA * (unsigned int)s;
+        KS_STAMP(0);
         while (ld_acquire(counter) < need) {
         }
+        KS_STAMP(1);
         fence_proxy_async();
 #pragma unroll
         for (int i = 0; i < KS_MAXCH; ++i) {
           if (i < nch) {
-            constexpr int dummy = 0;
-            (void)dummy;
             const int st = i % KS_NS;
             mbar_wait(&empty[st], ((phase >> st) & 1) ^ 1);
             phase ^= 1u << st;
@@ -133,6 +139,7 @@ lstm_bwd_ks_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
             tma_load_3d(ring + st * KS_CHUNK, &tmG, &full[st], dir * 4 * H + (ch0 + i) * 64, 0, tp * B);
           }
         }
+        KS_STAMP(2);
       }
     }
   } else if (warp == 1) {
@@ -148,6 +155,7 @@ lstm_bwd_ks_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
             const int st = i % KS_NS;
             mbar_wait(&full[st], (phase >> st) & 1);
             phase ^= 1u << st;
+            KS_STAMP(10 + i);
             tc_fence_after();
             const uint64_t da = a_base + (uint32_t)(st * (KS_CHUNK >> 4));
             const uint64_t db = b_base + (uint32_t)(i * (KS_CHUNK >> 4));
@@ -159,6 +167,7 @@ lstm_bwd_ks_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
           }
         }
         umma_commit(accum_full);
+        KS_STAMP(3);
       }
     }
   } else {
@@ -176,30 +185,38 @@ lstm_bwd_ks_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
     const int ssw = (sb >> 1) & 3, fsw = (fb >> 1) & 3;
     float dc[2] = {0.0f, 0.0f};
     float dh0[2] = {0.0f, 0.0f};
+    // running pointers of this thread's (row, unit pair): one add per step instead of 64-bit multiplies
+    const long long rstep = dir ? (long long)B : -(long long)B;           // rows per step in processing order
+    const long long row0 = (long long)(dir ? 0 : T - 1) * B + (row_ok ? fb : 0);
+    const float* gptr = p.gates + row0 * (8LL * H) + (long long)dir * 4 * H + 4 * ug;
+    const float* cptr = p.cs + row0 * (2LL * H) + dir * H + ug;
+    const float* dptr = p.dout + row0 * (2LL * H) + dir * H + ug;
+    __nv_bfloat16* optr = p.dG + row0 * (8LL * H) + (long long)dir * 4 * H + 4 * ug;
+    const float* c0ptr = p.c0 + ((long long)dir * B + (row_ok ? fb : 0)) * H + ug;
     for (int s = 0; s < nsteps; ++s) {
       const int t = dir ? s : (T - 1 - s);                     // t == -1 / T on the extra step
       const bool in_range = s < T;
       const bool active = row_ok && in_range && t < len;
-      const long long row = (long long)(in_range ? t : 0) * B + (row_ok ? fb : 0);
       float4 g4[2];
       float2 ct = make_float2(0.f, 0.f), cp = ct, dov = ct;
       if (s > 0 && ew == 0 && lane == 0) mbar_arrive_expect_tx(rfull, KS_RBUF);
       if (active) {
-        const float4* gp = reinterpret_cast<const float4*>(p.gates + row * (8LL * H) + (long long)dir * 4 * H + 4 * ug);
+        const float4* gp = reinterpret_cast<const float4*>(gptr);
         g4[0] = gp[0];
         g4[1] = gp[1];
-        ct = *reinterpret_cast<const float2*>(p.cs + row * (2LL * H) + dir * H + ug);
+        ct = *reinterpret_cast<const float2*>(cptr);
         const int tprev = dir ? t + 1 : t - 1;                 // frame the forward pass processed before t
         if (tprev >= 0 && tprev < len)
-          cp = *reinterpret_cast<const float2*>(p.cs + ((long long)tprev * B + fb) * (2LL * H) + dir * H + ug);
+          cp = *reinterpret_cast<const float2*>(cptr + rstep * (2LL * H));   // tprev = t + (dir ? 1 : -1)
         else
-          cp = *reinterpret_cast<const float2*>(p.c0 + ((long long)dir * B + fb) * H + ug);
-        dov = *reinterpret_cast<const float2*>(p.dout + row * (2LL * H) + dir * H + ug);
+          cp = *reinterpret_cast<const float2*>(c0ptr);
+        dov = *reinterpret_cast<const float2*>(dptr);
       }
       float dhr[2] = {0.0f, 0.0f};
       if (s > 0) {
         if (warp == 2) mbar_wait(accum_full, (s - 1) & 1);     // one warp polls, the others sleep on a hardware barrier
         asm volatile("bar.sync 2, %0;" ::"n"(32 * KS_EPI_WARPS) : "memory");
+        if (threadIdx.x == 64) KS_STAMP(4);
         tc_fence_after();
         float v[16], e[16];
         tmem_ld16(trow + 16 * dst, v);                         // x W_hi columns of the 16 units peer `dst` finalises
@@ -217,8 +234,10 @@ lstm_bwd_ks_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
           st_async_v4(a1, half ? v[12] : v[4], half ? v[13] : v[5], half ? v[14] : v[6], half ? v[15] : v[7], rbar);
           (void)w;
         }
+        if (threadIdx.x == 64) KS_STAMP(5);
         while (!mbar_try_wait_cluster(rfull, (s - 1) & 1)) {
         }
+        if (threadIdx.x == 64) KS_STAMP(6);
         const float* rb = rbuf + fb * 16 + (((u2 >> 1) ^ fsw) * 4) + (u2 & 1) * 2;
 #pragma unroll
         for (int r = 0; r < KS_CL; ++r) {
@@ -260,23 +279,19 @@ lstm_bwd_ks_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
 #pragma unroll
       for (int i = 0; i < 8; ++i) split_bf16(dgv[i], hi[i], lo[i]);
       if (row_ok && in_range) {
-        __nv_bfloat16* o = p.dG + row * (8LL * H) + (long long)dir * 4 * H + 4 * ug;
-        *reinterpret_cast<uint4*>(o) = *reinterpret_cast<uint4*>(hi);
-        *reinterpret_cast<uint4*>(o + p.dG_plane) = *reinterpret_cast<uint4*>(lo);
+        *reinterpret_cast<uint4*>(optr) = *reinterpret_cast<uint4*>(hi);
+        *reinterpret_cast<uint4*>(optr + p.dG_plane) = *reinterpret_cast<uint4*>(lo);
       }
+      gptr += rstep * (8LL * H);
+      cptr += rstep * (2LL * H);
+      dptr += rstep * (2LL * H);
+      optr += rstep * (8LL * H);
+      if (threadIdx.x == 64) KS_STAMP(7);
       asm volatile("bar.sync 1, %0;" ::"n"(32 * KS_EPI_WARPS) : "memory");
       if (threadIdx.x == 64) {
-        __threadfence();
-        fence_proxy_async();
-        red_release_add(counter, 1u);
-      }
-      if (row_ok && in_range) {
-#pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          const long long oT = ((long long)dir * 4 * H + 4 * ug + i) * p.ldT + row;
-          p.dGT[oT] = hi[i];
-          p.dGT[oT + p.dGT_plane] = lo[i];
-        }
+        KS_STAMP(8);
+        red_release_add(counter, 1u);     // cumulative over the CTA's stores ordered before the bar.sync
+        KS_STAMP(9);
       }
     }
     if (row_ok && p.want_d0) {
@@ -312,7 +327,8 @@ int launch_lstm_bwd_ks(const LstmBwdParams& p, const void* whhT, long long whhT_
     int rc = make_tmap_bf16(&tmG, p.dG, 3, dims, str, box);
     if (rc) return rc;
   }
-  cudaFuncSetAttribute(lstm_bwd_ks_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, KS_SMEM);
+  auto kern = p.dbg ? lstm_bwd_ks_kernel<true> : lstm_bwd_ks_kernel<false>;
+  cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, KS_SMEM);
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(2 * KS_NCTA);
   cfg.blockDim = dim3(KS_THREADS);
@@ -327,7 +343,7 @@ int launch_lstm_bwd_ks(const LstmBwdParams& p, const void* whhT, long long whhT_
   attr[1].val.cooperative = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 2;
-  cudaError_t e = cudaLaunchKernelEx(&cfg, lstm_bwd_ks_kernel, tmW, tmG, p);
+  cudaError_t e = cudaLaunchKernelEx(&cfg, kern, tmW, tmG, p);
   if (e != cudaSuccess) {
     set_error("ss_lstm_bwd (K-split clusters): launch failed: %s", cudaGetErrorString(e));
     return -2;

@@ -238,7 +238,6 @@ lstm_fwd_kernel(const __grid_constant__ CUtensorMap tmW, LstmFwdParams p) {
       }
       if (threadIdx.x == 0) LF_STAMP(8);
       float hout[4] = {0.0f, 0.0f, 0.0f, 0.0f};
-      const float hp[4] = {h[0], h[1], h[2], h[3]};
       if (active) {
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
@@ -266,18 +265,6 @@ lstm_fwd_kernel(const __grid_constant__ CUtensorMap tmW, LstmFwdParams p) {
         __nv_bfloat16* op = p.out + row * (2LL * H) + dir * H + ug;
         __stcs(reinterpret_cast<uint2*>(op), *reinterpret_cast<uint2*>(hi));
         __stcs(reinterpret_cast<uint2*>(op + p.out_plane), *reinterpret_cast<uint2*>(lo));
-        if (p.outT && !(p.EXP & 8)) {
-#pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            const long long oT = (long long)(dir * H + ug + j) * p.ldT + row;
-            p.outT[oT] = hi[j];
-            p.outT[oT + p.outT_plane] = lo[j];
-            __nv_bfloat16 phi, plo;
-            split_bf16(hp[j], phi, plo);
-            p.hprevT[oT] = phi;
-            p.hprevT[oT + p.outT_plane] = plo;
-          }
-        }
       }
     }
     if (row_ok) {
@@ -297,7 +284,10 @@ lstm_fwd_kernel(const __grid_constant__ CUtensorMap tmW, LstmFwdParams p) {
 
 }  // namespace ssb
 
-static long long* g_lstm_dbg = nullptr;
+namespace ssb {
+long long* g_lstm_dbg = nullptr;
+}
+using ssb::g_lstm_dbg;
 extern "C" int ss_lstm_debug(long long* buf) {   // development aid: clock64 trace [T][32] of CTA 0 of the next launches
   g_lstm_dbg = buf;
   return 0;
@@ -359,6 +349,12 @@ extern "C" int ss_lstm_fwd(float* gx, const void* whh_r, long long whh_ld, long 
   if (e != cudaSuccess) {
     set_error("ss_lstm_fwd: cooperative launch failed: %s", cudaGetErrorString(e));
     return -2;
+  }
+  if (outT) {   // transposed copies for the dW GEMMs, one HBM-bound pass each instead of scattered stores per step
+    int rc = launch_transpose_sb16(out, 2LL * H, out_plane, T * B, 2 * H, outT, ldT, outT_plane, st);
+    if (rc) return rc;
+    rc = launch_hprev_transpose(out, 2LL * H, out_plane, T, B, H, lens, h0, hprevT, ldT, outT_plane, st);
+    if (rc) return rc;
   }
   return 0;
 }
