@@ -145,6 +145,18 @@ int ss_bn_bwd(float* dy, const void* x, long long ld, long long plane, int R, in
 int ss_head_dw_fix(const float* G, const float* dsum, const float* coef, const float* beta, int O, int C, float* dW,
                    void* stream);
 
+/* ---- RSH residual attention.  Replaces archs/RSH.py:254-257 (compute_loss: combos = relu_(combos - [0 || mask]),
+ * repack) and :277-281 (compute_masks: no relu) and the autograd backward of that path ----
+ * cur,next: pass inputs [T*B][2F] = [mix || attention]; z: head pre-activations of the pass (mask = sigmoid(z)).
+ * Rows with t >= len_b of `next` are zero.  bwd: dx = gradient wrt the NEXT pass's input [R][2F], next_in = that
+ * input; carry_out[R][F] = (dx[:,F:] + carry_in) * [next_in[:,F:] > 0] is the total gradient reaching this pass's
+ * attention half through the residual, dmask = -carry_out is the extra gradient wrt this pass's mask
+ * (ss_pit_loss_bwd's dmask_extra).  carry_in may be NULL. */
+int ss_rsh_residual(const float* cur, const float* z, long long ldz, const int* lens, int T, int B, int F, int relu,
+                    float* next, void* stream);
+int ss_rsh_residual_bwd(const float* dx, const float* carry_in, const float* next_in, long long R, int F,
+                        float* carry_out, float* dmask, void* stream);
+
 /* ---- f1: global-norm clip + Adam over one flat fp32 bucket.  Replaces torch.nn.utils.clip_grad_norm_(params,
  * 0.25) and torch.optim.Adam(lr=1e-3).step() at steps/train_qsub.py:95,121-122 ----
  * ss_grad_norm: norm_out[0] = gscale * ||g||_2 (partial: ss_optim_parts(n) floats).  gscale = 1/world turns an

@@ -184,3 +184,68 @@ extern "C" int ss_colsum_sb16(const void* in, long long ld, long long plane, int
 
 extern "C" int ss_stft_tile_frames(void) { return 32; }
 extern "C" int ss_istft_tile_hops(void) { return 28; }
+
+// ---- RSH residual attention (archs/RSH.py:254-257 train, :277-281 test) and its backward ----
+namespace ssb {
+
+// next[r][0:F] = cur[r][0:F];  next[r][F:2F] = cur[r][F:2F] - sigmoid(z[r][0:F])  (relu'd when `relu`);
+// rows with t >= len_b are written as zeros (the reference repacks, which drops padded frames).
+__global__ void __launch_bounds__(256) rsh_residual_kernel(const float* __restrict__ cur, const float* __restrict__ z,
+                                                           long long ldz, const int* __restrict__ lens, int T, int B,
+                                                           int F, int relu, float* __restrict__ next) {
+  const long long n = (long long)T * B * 2 * F;
+  for (long long e = (long long)blockIdx.x * 256 + threadIdx.x; e < n; e += (long long)gridDim.x * 256) {
+    const long long r = e / (2 * F);
+    const int c = (int)(e - r * 2 * F);
+    const int t = (int)(r / B), b = (int)(r - (long long)t * B);
+    float v = 0.0f;
+    if (t < lens[b]) {
+      v = cur[e];
+      if (c >= F) {
+        v -= sigmoidf_(z[r * ldz + (c - F)]);
+        if (relu) v = fmaxf(v, 0.0f);
+      }
+    }
+    next[e] = v;
+  }
+}
+
+// carry_out[r][f] = (dx[r][F + f] + carry_in[r][f]) * [att_next[r][f] > 0];  dmask[r][f] = -carry_out[r][f]
+// att_next = attention half of the NEXT pass's input (row pitch 2F); dx = gradient wrt that input (row pitch 2F).
+__global__ void __launch_bounds__(256) rsh_residual_bwd_kernel(const float* __restrict__ dx,
+                                                               const float* __restrict__ carry_in,
+                                                               const float* __restrict__ next_in, long long R, int F,
+                                                               float* __restrict__ carry_out, float* __restrict__ dmask) {
+  const long long n = R * F;
+  for (long long e = (long long)blockIdx.x * 256 + threadIdx.x; e < n; e += (long long)gridDim.x * 256) {
+    const long long r = e / F;
+    const int f = (int)(e - r * F);
+    const long long o = r * 2 * F + F + f;
+    float g = dx[o] + (carry_in ? carry_in[e] : 0.0f);
+    g = next_in[o] > 0.0f ? g : 0.0f;
+    carry_out[e] = g;
+    dmask[e] = -g;
+  }
+}
+
+}  // namespace ssb
+
+extern "C" int ss_rsh_residual(const float* cur, const float* z, long long ldz, const int* lens, int T, int B, int F,
+                               int relu, float* next, void* stream) {
+  using namespace ssb;
+  const long long n = (long long)T * B * 2 * F;
+  if (n == 0) return 0;
+  rsh_residual_kernel<<<(int)min((long long)148 * 8, (n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(cur, z, ldz, lens, T, B,
+                                                                                                    F, relu, next);
+  return check_launch("ss_rsh_residual");
+}
+
+extern "C" int ss_rsh_residual_bwd(const float* dx, const float* carry_in, const float* next_in, long long R, int F,
+                                   float* carry_out, float* dmask, void* stream) {
+  using namespace ssb;
+  const long long n = R * F;
+  if (n == 0) return 0;
+  rsh_residual_bwd_kernel<<<(int)min((long long)148 * 8, (n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
+      dx, carry_in, next_in, R, F, carry_out, dmask);
+  return check_launch("ss_rsh_residual_bwd");
+}

@@ -142,23 +142,26 @@ def forward(ws, wt, p, x, lens_dev, h0, c0, bn_train, save=True, bn_momentum=0.1
     return ws.z
 
 
-def pit_loss(ws, mix, src, lens_dev, F, n_out, n_src, mode=0, accumulate=False, mask_out=None):
-    """mix fp32 (T*B,F); src fp32 (n_src,T*B,F).  Fills ws.losses/idx/assign/stats."""
+def pit_loss(ws, mix, src, lens_dev, F, n_out, n_src, mode=0, accumulate=False, mask_out=None, used=None, stats=None):
+    """mix fp32 (T*B,F); src fp32 (n_src,T*B,F).  Fills ws.losses/idx/assign and stats (ws.stats unless a shared
+    accumulator is given, as the RSH passes do together with the shared `used` bitmasks)."""
     st = stream_ptr()
     call("pit_loss_fwd", ws.z, LL(ws.ldz), mix, src, lens_dev, ws.T, ws.B, F, n_out, n_src, mask_out, ws.pit_partial, st)
     call("pit_select", ws.pit_partial, lib().ss_pit_chunks(ws.T), lens_dev, ws.B, F, n_out, n_src, mode,
-         int(accumulate), ws.losses, ws.idx, ws.assign, ws.used, ws.stats, st)
+         int(accumulate), ws.losses, ws.idx, ws.assign, ws.used if used is None else used,
+         ws.stats if stats is None else stats, st)
 
 
 def backward(ws, wt, p, grads, mix, src, lens_dev, c0, F, n_out, gout, dmask_extra=None, dhn=None, dcn=None,
-             want_dx=False, want_d0=False, training=True, accumulate=False, hook=None):
+             want_dx=False, want_d0=False, training=True, accumulate=False, hook=None, stats=None):
     """Backward of loss -> every parameter gradient in `grads` (dict name -> fp32 tensor, natural layouts).
     Returns (dx or None, dh0 or None, dc0 or None)."""
     T, B, TB = ws.T, ws.B, ws.TB
     st = stream_ptr()
     O = ws.out_dim
     beta = 1.0 if accumulate else 0.0
-    call("pit_loss_bwd", ws.z, LL(ws.ldz), mix, src, lens_dev, ws.assign, T, B, F, n_out, ws.stats, gout, dmask_extra,
+    call("pit_loss_bwd", ws.z, LL(ws.ldz), mix, src, lens_dev, ws.assign, T, B, F, n_out,
+         ws.stats if stats is None else stats, gout, dmask_extra,
          ws.dz.buf, LL(ws.dz.ld), LL(ws.dz.plane), ws.dzT.buf, LL(ws.dzT.ld), LL(ws.dzT.plane), st)
     top, topT = ws.out[-1], ws.outT[-1]
     # head: dlin.bias = colsum(dz); G = dz^T x; dW = s*(G - mean*dsum) + beta*dsum; dY = dz W

@@ -74,9 +74,13 @@ def allreduce_buckets(flat, buckets, group=None, tags=BUCKET_ORDER):
 class Trainer:
     """Owns the flat parameter / gradient / Adam buckets of one SepDNN and runs whole train steps."""
 
-    def __init__(self, model, arch, lr=1e-3, clip=0.25, betas=(0.9, 0.999), eps=1e-8, group=None):
+    def __init__(self, model, arch, lr=1e-3, clip=0.25, betas=(0.9, 0.999), eps=1e-8, group=None, host_rng=False):
+        """host_rng: draw the random initial state (h0, c0) of every batch on the CPU generator and copy it over,
+        exactly as the reference's init_hidden does (archs/uPIT.py:121-127); default draws the same N(0,1) state on
+        the device generator, which keeps ~2 ms of host work and a blocking copy out of every step."""
         import torch.distributed as dist
         self.model, self.arch = model, arch
+        self.host_rng = host_rng
         self.lr, self.clip, self.betas, self.eps = float(lr), float(clip), betas, float(eps)
         self.world = dist.get_world_size(group) if dist.is_available() and dist.is_initialized() else 1
         self.group = group
@@ -122,12 +126,18 @@ class Trainer:
 
     def step(self, batch_sample):
         """One optimisation step on a collated batch.  Returns device scalars (loss, norm) of this rank's shard."""
-        loss, norm = self.arch.loss_and_grads(self.model, batch_sample, self.grads, hook=self._bucket_ready)
+        loss, norm = self.arch.loss_and_grads(self.model, batch_sample, self.grads, hook=self._bucket_ready,
+                                              hidden=None if self.host_rng else self._device_hidden)
         loss, norm = loss.clone(), norm.clone()
         if self.world > 1:
             torch.cuda.current_stream().wait_stream(self.comm)
         self.apply_update()
         return loss, norm
+
+    def _device_hidden(self, batch_size):
+        dev = self.flat_p.device
+        n = 2 * self.model.num_layers
+        return (torch.randn(n, batch_size, 600, device=dev), torch.randn(n, batch_size, 600, device=dev))
 
     def apply_update(self):
         """clip_grad_norm_(clip) + Adam.step() on the flat buckets (steps/train_qsub.py:121-122)."""

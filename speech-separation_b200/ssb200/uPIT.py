@@ -128,8 +128,8 @@ class SepDNN(nn.Module):
             self._wt_versions = ver
         return self._wt
 
-    def workspace(self, T, B, training):
-        key = (T, B, training)
+    def workspace(self, T, B, training, slot=0):
+        key = (T, B, training, slot)
         ws = self._ws.get(key)
         if ws is None:
             if len(self._ws) >= getattr(self, "max_workspaces", 2):
@@ -150,32 +150,51 @@ class SepDNN(nn.Module):
         return mask.view(ws.T, ws.B, self.out_dim).transpose(0, 1)
 
 
-def unpack_batch(batch_sample, keys, device):
-    """PackedSequences -> time-major padded device tensors (rows t*B+b) + lengths."""
+def _to_device_async(arr, dtype, device):
+    """Small host array -> device without a blocking pageable copy (which would stall the launch queue)."""
+    t = torch.from_numpy(np.ascontiguousarray(arr, dtype=dtype))
+    return t.pin_memory().to(device, non_blocking=True)
+
+
+def unpack_batch(batch_sample, keys, device, src_keys=()):
+    """PackedSequences -> time-major padded device tensors (rows t*B+b) + lengths.  `src_keys` are unpacked side by
+    side into one (len(src_keys), T*B, F) tensor returned under 'src'."""
     mix = batch_sample[keys[0]]
     assert isinstance(mix, PackedSequence)
     bs = mix.batch_sizes.numpy().astype(np.int64)
     T, B = len(bs), int(bs[0])
     lens = (bs[None, :] > np.arange(B)[:, None]).sum(1).astype(np.int32)
-    toff = torch.as_tensor(np.concatenate([[0], np.cumsum(bs)]), device=device)
-    out = {"T": T, "B": B, "lens": lens, "lens_dev": torch.as_tensor(lens, device=device), "toff": toff}
-    for k in keys:
+    toff = _to_device_async(np.concatenate([[0], np.cumsum(bs)]), np.int64, device)
+    out = {"T": T, "B": B, "lens": lens, "lens_dev": _to_device_async(lens, np.int32, device), "toff": toff}
+
+    def unpack_into(k, dst):
         data = batch_sample[k].data.to(device=device, dtype=torch.float32, non_blocking=True).contiguous()
         C = data.shape[1]
+        call("unpack", data, toff, T, B, C, C, 0, dst, stream_ptr())
+        return C
+
+    for k in keys:
+        C = batch_sample[k].data.shape[1]
         pad = torch.empty(T * B, C, dtype=torch.float32, device=device)
-        call("unpack", data, toff, T, B, C, C, 0, pad, stream_ptr())
+        unpack_into(k, pad)
         out[k] = pad
+    if src_keys:
+        C = batch_sample[src_keys[0]].data.shape[1]
+        src = torch.empty(len(src_keys), T * B, C, dtype=torch.float32, device=device)
+        for i, k in enumerate(src_keys):
+            unpack_into(k, src[i])
+        out["src"] = src
     return out
 
 
-def run_forward(model, batch, hidden, save):
+def run_forward(model, batch, hidden, save, slot=0, x=None):
     p = model.param_dict()
     wt = model.weights(p, need_grad_copies=save)
-    ws = model.workspace(batch["T"], batch["B"], save)
+    ws = model.workspace(batch["T"], batch["B"], save, slot)
     batch["ws"], batch["wt"] = ws, wt
     h0, c0 = hidden
     pd = {k: v.detach() for k, v in p.items()}
-    return engine.forward(ws, wt, pd, batch["mix"], batch["lens_dev"], h0.contiguous(), c0.contiguous(),
+    return engine.forward(ws, wt, pd, batch["mix"] if x is None else x, batch["lens_dev"], h0.contiguous(), c0.contiguous(),
                           bn_train=model.training, save=save)
 
 
@@ -211,9 +230,7 @@ class _UPITLoss(torch.autograd.Function):
 def compute_loss(model, epoch, batch_sample, plotdir=""):
     """(loss, norm) as archs/uPIT.py:157-206; loss.backward() runs the CUDA backward."""
     dev = model.lin.weight.device
-    keys = ["mix"] + ["source%d" % (i + 1) for i in range(model.num_spk)]
-    batch = unpack_batch(batch_sample, keys, dev)
-    batch["src"] = torch.stack([batch[k] for k in keys[1:]]) if model.num_spk > 1 else batch[keys[1]][None]
+    batch = unpack_batch(batch_sample, ["mix"], dev, ["source%d" % (i + 1) for i in range(model.num_spk)])
     model.zero_grad()
     model.hidden = model.init_hidden(batch["B"])
     params = [v for _, v in model.named_parameters()]
@@ -225,15 +242,14 @@ def compute_loss(model, epoch, batch_sample, plotdir=""):
     return loss, norm.detach()
 
 
-def loss_and_grads(model, batch_sample, grads, hook=None):
+def loss_and_grads(model, batch_sample, grads, hook=None, hidden=None):
     """compute_loss + loss.backward() without the autograd tape: every parameter gradient is written (not
     accumulated) straight into grads[name] -- e.g. views of the trainer's flat bucket (ssb200/train.py).  `hook(tag)`
-    is called when a gradient bucket ('head', 'l1', 'l0') has been enqueued.  Returns device scalars (loss, norm)."""
+    is called when a gradient bucket ('head', 'l1', 'l0') has been enqueued; `hidden(B)` (optional) supplies (h0, c0)
+    instead of model.init_hidden.  Returns device scalars (loss, norm)."""
     dev = model.lin.weight.device
-    keys = ["mix"] + ["source%d" % (i + 1) for i in range(model.num_spk)]
-    batch = unpack_batch(batch_sample, keys, dev)
-    batch["src"] = torch.stack([batch[k] for k in keys[1:]]) if model.num_spk > 1 else batch[keys[1]][None]
-    model.hidden = model.init_hidden(batch["B"])
+    batch = unpack_batch(batch_sample, ["mix"], dev, ["source%d" % (i + 1) for i in range(model.num_spk)])
+    model.hidden = model.init_hidden(batch["B"]) if hidden is None else hidden(batch["B"])
     with torch.no_grad():
         run_forward(model, batch, model.hidden, save=True)
         ws, wt = batch["ws"], batch["wt"]

@@ -22,7 +22,7 @@ def test_trainer_matches_torch_clip_adam():
     model_a = _model(case)
     model_b = copy.deepcopy(model_a)
     opt = torch.optim.Adam(model_a.parameters(), lr=1e-3)
-    tr = train.Trainer(model_b, uPIT)
+    tr = train.Trainer(model_b, uPIT, host_rng=True)     # same CPU-generator (h0, c0) draws on both sides
     for it in range(3):
         torch.manual_seed(40 + it)
         loss_a, norm_a = uPIT.compute_loss(model_a, 0, batch)
