@@ -298,6 +298,14 @@ def run_train(args, rank, local, world):
             a = byts * B_PER_GPU * (fr / B_PER_GPU) / (prof[name]["ms_per_step"] * 1e-3) / 1e9
             rl[name] = {"bound": "hbm", "achieved": round(a, 1), "peak": hbm, "unit": "GB/s", "frac": round(a / hbm, 4),
                         "ms_per_step": round(prof[name]["ms_per_step"], 3)}
+    divergence = None
+    if world > 1:                       # replicas must still hold identical parameters after all those steps
+        import torch.distributed as dist
+        ref_p = trainer.flat_p.clone()
+        dist.broadcast(ref_p, src=0)
+        d = (trainer.flat_p - ref_p).abs().max().reshape(1)
+        dist.all_reduce(d, op=dist.ReduceOp.MAX)
+        divergence = float(d)
     dom = max(prof, key=lambda k: prof[k]["ms_per_step"])
     roofline = dict(rl.get(dom, {"bound": "tensor", "achieved": None, "peak": tf_sus, "unit": "TFLOP/s", "frac": None}))
     roofline.update({"kernel": dom, "traffic": None, "peak_source": peak_src,
@@ -315,6 +323,7 @@ def run_train(args, rank, local, world):
         "e2e": {"value": round(e2e, 1), "unit": "audio-sec/sec", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 8,
                 "ms_per_step": round(ms_e2e / K, 3)},
         "gpu_launches": launches, "clocks": clocks, "roofline": roofline, "rooflines": rl,
+        "dp_param_divergence": divergence,
         "kernel_ms_per_step": {k: round(v["ms_per_step"], 3) for k, v in sorted(prof.items(), key=lambda kv: -kv[1]["ms_per_step"])},
     }
     return line
