@@ -62,6 +62,12 @@ int ss_gemm_sb16(const void* A, long long lda, long long a_plane, const void* B,
                  float* C, long long ldc, int M, int N, int K, const float* bias, float alpha, float beta, int rowmap,
                  int hidden, void* stream);
 
+/* Two problems of the same shape in one launch (the two LSTM directions' weight gradients): entry z in {0,1} reads
+ * A rows [z*a_batch_rows, +M) and B rows [z*b_batch_rows, +N) of the same sb16 matrices and writes Cz. */
+int ss_gemm_sb16_x2(const void* A, long long lda, long long a_plane, int a_batch_rows, const void* B, long long ldb,
+                    long long b_plane, int b_batch_rows, float* C0, float* C1, long long ldc, int M, int N, int K,
+                    float alpha, float beta, int rowmap, int hidden, void* stream);
+
 /* ---- layout / precision conversion kernels (plumbing around the GEMMs) ----
  * ss_split: fp32 in[R][C] (pitch ld_in) -> sb16 out[rp(r)][C] (pitch ld_out, plane out_plane) and/or the
  * transposed sb16 outT[C][rp(r)] (pitch ld_outT).  rowperm = SS_ROWMAP_UNIT4 interleaves LSTM gate rows:

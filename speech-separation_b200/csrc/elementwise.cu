@@ -51,18 +51,42 @@ __global__ void __launch_bounds__(256) split_kernel(const float* __restrict__ in
 
 constexpr int CS_ROWS = 256;   // rows per partial block
 
+// partial[blockIdx.y][c] = sum over rows [256*blockIdx.y, +256) of (hi+lo)[r][c].  A warp reads 256 consecutive
+// columns of one row as 16-byte vectors (both planes); the 8 warps take interleaved rows and combine through smem.
 __global__ void __launch_bounds__(256) colsum_partial_kernel(const __nv_bfloat16* __restrict__ in, long long ld,
                                                              long long plane, int R, int C,
                                                              float* __restrict__ partial) {
-  const int c = blockIdx.x * 256 + threadIdx.x;
-  if (c >= C) return;
+  __shared__ float red[8][256 + 8];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int c0 = blockIdx.x * 256 + tx * 8;
   const int r0 = blockIdx.y * CS_ROWS, r1 = min(R, r0 + CS_ROWS);
-  float acc = 0.0f;
-  for (int r = r0; r < r1; ++r) {
-    const long long o = (long long)r * ld + c;
-    acc += join_bf16(in[o], in[o + plane]);
+  float acc[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) acc[i] = 0.0f;
+  if (c0 < C) {                                            // pitch is a multiple of 8: the vector stays inside the row
+    for (int r = r0 + ty; r < r1; r += 8) {
+      const long long o = (long long)r * ld + c0;
+      const uint4 h = *reinterpret_cast<const uint4*>(in + o), l = *reinterpret_cast<const uint4*>(in + o + plane);
+      const __nv_bfloat162* hp = reinterpret_cast<const __nv_bfloat162*>(&h);
+      const __nv_bfloat162* lp = reinterpret_cast<const __nv_bfloat162*>(&l);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const float2 a = __bfloat1622float2(hp[i]), b = __bfloat1622float2(lp[i]);
+        acc[2 * i] += a.x + b.x;
+        acc[2 * i + 1] += a.y + b.y;
+      }
+    }
   }
-  partial[(long long)blockIdx.y * C + c] = acc;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) red[ty][tx * 8 + i] = acc[i];
+  __syncthreads();
+  const int c = blockIdx.x * 256 + threadIdx.x;
+  if (c < C) {
+    float v = 0.0f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) v += red[w][threadIdx.x];
+    partial[(long long)blockIdx.y * C + c] = v;
+  }
 }
 
 __global__ void __launch_bounds__(256) colsum_final_kernel(const float* __restrict__ partial, int parts, int C,
@@ -174,6 +198,8 @@ extern "C" int ss_colsum_sb16(const void* in, long long ld, long long plane, int
                               int rowmap, int hidden, void* stream) {
   using namespace ssb;
   if (C == 0) return 0;
+  SS_REQUIRE(ld % 8 == 0 && plane % 8 == 0 && ((uintptr_t)in & 15) == 0,
+             "ss_colsum_sb16: pitch / plane stride must be multiples of 8 elements and the base 16-byte aligned");
   const int parts = cdiv(R, CS_ROWS);
   cudaStream_t st = (cudaStream_t)stream;
   if (parts > 0)

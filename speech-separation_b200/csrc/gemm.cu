@@ -13,27 +13,32 @@ constexpr int GB_M = 128, GB_N = 128, GB_K = 64, G_STAGES = 3, G_THREADS = 192;
 constexpr int G_PLANE = GB_M * GB_K * 2;                 // 16 KB: one bf16 plane of one operand tile
 constexpr int G_STAGE_BYTES = 4 * G_PLANE;               // A(hi,lo) + B(hi,lo)
 constexpr int G_SMEM = G_STAGES * G_STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/;
+constexpr int G_TMEM = 2 * GB_N;                         // two accumulators: epilogue of tile i overlaps mainloop of i+1
 
 struct GemmParams {
-  float* C;
+  float* C[2];               // per batch entry
   long long ldc;
   const float* bias;
   float alpha, beta;
   int M, N, K, rowmap, hidden;
+  int batch, a_batch_rows, b_batch_rows;   // batch entry z reads A rows [z*a_batch_rows, +M), B rows [z*b_batch_rows, +N)
 };
 
+// Persistent: CTA c works on tiles c, c + gridDim.x, ... (n fastest, then m, then batch).
 __global__ void __launch_bounds__(G_THREADS, 1)
 gemm_sb16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, GemmParams p) {
   extern __shared__ unsigned char smem_raw[];
   unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   uint64_t* full = reinterpret_cast<uint64_t*>(smem + G_STAGES * G_STAGE_BYTES);
   uint64_t* empty = full + G_STAGES;
-  uint64_t* accum_full = empty + G_STAGES;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(accum_full + 1);
+  uint64_t* tfull = empty + G_STAGES;
+  uint64_t* tempty = tfull + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int n0 = blockIdx.x * GB_N, m0 = blockIdx.y * GB_M;
   const int nkb = (p.K + GB_K - 1) / GB_K;
+  const int mt = (p.M + GB_M - 1) / GB_M, nt = (p.N + GB_N - 1) / GB_N;
+  const int tiles = p.batch * mt * nt;
 
   if (threadIdx.x == 0) {
     tma_prefetch_desc(&tmA);
@@ -42,94 +47,117 @@ gemm_sb16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       mbar_init(&full[s], 1);
       mbar_init(&empty[s], 1);
     }
-    mbar_init(accum_full, 1);
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(&tfull[a], 1);
+      mbar_init(&tempty[a], 4);
+    }
     fence_barrier_init();
   }
-  if (warp == 1) tmem_alloc<GB_N>(tmem_slot);
+  if (warp == 1) tmem_alloc<G_TMEM>(tmem_slot);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
-  const uint32_t tmem_d = *tmem_slot;
+  const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
     if (lane == 0) {
-      for (int kb = 0; kb < nkb; ++kb) {
-        const int s = kb % G_STAGES, ph = (kb / G_STAGES) & 1;
-        mbar_wait(&empty[s], ph ^ 1);
-        unsigned char* st = smem + s * G_STAGE_BYTES;
-        mbar_arrive_expect_tx(&full[s], G_STAGE_BYTES);
-        tma_load_3d(st, &tmA, &full[s], kb * GB_K, m0, 0);               // [plane][128 rows][64 k]
-        tma_load_3d(st + 2 * G_PLANE, &tmB, &full[s], kb * GB_K, n0, 0);
+      int it = 0;
+      for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
+        const int z = tile / (mt * nt), rem = tile - z * mt * nt;
+        const int m0 = (rem / nt) * GB_M + z * p.a_batch_rows, n0 = (rem % nt) * GB_N + z * p.b_batch_rows;
+        for (int kb = 0; kb < nkb; ++kb, ++it) {
+          const int s = it % G_STAGES, ph = (it / G_STAGES) & 1;
+          mbar_wait(&empty[s], ph ^ 1);
+          unsigned char* st = smem + s * G_STAGE_BYTES;
+          mbar_arrive_expect_tx(&full[s], G_STAGE_BYTES);
+          tma_load_3d(st, &tmA, &full[s], kb * GB_K, m0, 0);               // [plane][128 rows][64 k]
+          tma_load_3d(st + 2 * G_PLANE, &tmB, &full[s], kb * GB_K, n0, 0);
+        }
       }
     }
   } else if (warp == 1) {
     if (lane == 0) {
       constexpr uint32_t idesc = umma_idesc_bf16(GB_M, GB_N);
-      for (int kb = 0; kb < nkb; ++kb) {
-        const int s = kb % G_STAGES, ph = (kb / G_STAGES) & 1;
-        mbar_wait(&full[s], ph);
+      const uint64_t base = umma_desc_sw128(smem_u32(smem));
+      int it = 0, lt = 0;
+      for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x, ++lt) {
+        const int acc = lt & 1;
+        mbar_wait(&tempty[acc], ((lt >> 1) & 1) ^ 1);                      // epilogue drained this accumulator
         tc_fence_after();
-        const uint32_t a_hi = smem_u32(smem + s * G_STAGE_BYTES), a_lo = a_hi + G_PLANE;
-        const uint32_t b_hi = a_hi + 2 * G_PLANE, b_lo = b_hi + G_PLANE;
+        const uint32_t tmem_d = tmem_base + acc * GB_N;
+        for (int kb = 0; kb < nkb; ++kb, ++it) {
+          const int s = it % G_STAGES, ph = (it / G_STAGES) & 1;
+          mbar_wait(&full[s], ph);
+          tc_fence_after();
+          const uint64_t dah = base + (uint32_t)(s * (G_STAGE_BYTES >> 4)), dal = dah + (G_PLANE >> 4);
+          const uint64_t dbh = dah + (2 * G_PLANE >> 4), dbl = dbh + (G_PLANE >> 4);
 #pragma unroll
-        for (int k = 0; k < GB_K / 16; ++k) {
-          const uint32_t ko = k * 32;                                      // 16 bf16 = 32 bytes inside the 128B row
-          const uint64_t dah = umma_desc_sw128(a_hi + ko), dal = umma_desc_sw128(a_lo + ko);
-          const uint64_t dbh = umma_desc_sw128(b_hi + ko), dbl = umma_desc_sw128(b_lo + ko);
-          umma_bf16(tmem_d, dal, dbh, idesc, (kb | k) ? 1u : 0u);          // small terms first
-          umma_bf16(tmem_d, dah, dbl, idesc, 1u);
-          umma_bf16(tmem_d, dah, dbh, idesc, 1u);
+          for (int k = 0; k < GB_K / 16; ++k) {                            // 16 bf16 = 32 bytes inside the 128B row
+            umma_bf16(tmem_d, dal + 2 * k, dbh + 2 * k, idesc, (kb | k) ? 1u : 0u);   // small terms first
+            umma_bf16(tmem_d, dah + 2 * k, dbl + 2 * k, idesc, 1u);
+            umma_bf16(tmem_d, dah + 2 * k, dbh + 2 * k, idesc, 1u);
+          }
+          umma_commit(&empty[s]);
         }
-        umma_commit(&empty[s]);
+        umma_commit(&tfull[acc]);
       }
-      umma_commit(accum_full);
     }
   } else {
     // epilogue: warp w may touch TMEM lanes [32*(w%4), +32)
     const int q = warp & 3;
-    const int m = m0 + q * 32 + lane;
-    mbar_wait(accum_full, 0);
-    tc_fence_after();
-    long long orow = m;
-    if (p.rowmap == SS_ROWMAP_UNIT4) orow = (long long)(m & 3) * p.hidden + (m >> 2);
-    float* crow = p.C + orow * p.ldc;
-    const bool vec = ((p.ldc & 3) == 0) && ((reinterpret_cast<uintptr_t>(p.C) & 15) == 0);
-    for (int c = 0; c < GB_N; c += 16) {
-      if (n0 + c >= p.N) break;                       // warp-uniform
-      float v[16];
-      tmem_ld16(tmem_d + ((uint32_t)(q * 32) << 16) + c, v);
-      if (m < p.M) {
-        const int nb = n0 + c;
+    int lt = 0;
+    for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x, ++lt) {
+      const int z = tile / (mt * nt), rem = tile - z * mt * nt;
+      const int m0 = (rem / nt) * GB_M, n0 = (rem % nt) * GB_N;
+      const int acc = lt & 1;
+      const int m = m0 + q * 32 + lane;
+      mbar_wait(&tfull[acc], (lt >> 1) & 1);
+      tc_fence_after();
+      const uint32_t tmem_d = tmem_base + acc * GB_N;
+      long long orow = m;
+      if (p.rowmap == SS_ROWMAP_UNIT4) orow = (long long)(m & 3) * p.hidden + (m >> 2);
+      float* Cz = p.C[z];
+      float* crow = Cz + orow * p.ldc;
+      const bool vec = ((p.ldc & 3) == 0) && ((reinterpret_cast<uintptr_t>(Cz) & 15) == 0);
+      for (int c = 0; c < GB_N; c += 16) {
+        if (n0 + c >= p.N) break;                       // warp-uniform
+        float v[16];
+        tmem_ld16(tmem_d + ((uint32_t)(q * 32) << 16) + c, v);
+        if (m < p.M) {
+          const int nb = n0 + c;
 #pragma unroll
-        for (int i = 0; i < 16; ++i) {
-          float r = p.alpha * v[i];
-          if (p.bias && nb + i < p.N) r += p.bias[nb + i];
-          v[i] = r;
-        }
-        if (vec && nb + 16 <= p.N) {
-          float4* dst = reinterpret_cast<float4*>(crow + nb);
-#pragma unroll
-          for (int i = 0; i < 4; ++i) {
-            float4 o = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
-            if (p.beta != 0.0f) {
-              const float4 old = dst[i];
-              o.x += p.beta * old.x; o.y += p.beta * old.y; o.z += p.beta * old.z; o.w += p.beta * old.w;
-            }
-            dst[i] = o;
+          for (int i = 0; i < 16; ++i) {
+            float r = p.alpha * v[i];
+            if (p.bias && nb + i < p.N) r += p.bias[nb + i];
+            v[i] = r;
           }
-        } else {
+          if (vec && nb + 16 <= p.N) {
+            float4* dst = reinterpret_cast<float4*>(crow + nb);
 #pragma unroll
-          for (int i = 0; i < 16; ++i)
-            if (nb + i < p.N) crow[nb + i] = v[i] + (p.beta != 0.0f ? p.beta * crow[nb + i] : 0.0f);
+            for (int i = 0; i < 4; ++i) {
+              float4 o = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+              if (p.beta != 0.0f) {
+                const float4 old = dst[i];
+                o.x += p.beta * old.x; o.y += p.beta * old.y; o.z += p.beta * old.z; o.w += p.beta * old.w;
+              }
+              dst[i] = o;
+            }
+          } else {
+#pragma unroll
+            for (int i = 0; i < 16; ++i)
+              if (nb + i < p.N) crow[nb + i] = v[i] + (p.beta != 0.0f ? p.beta * crow[nb + i] : 0.0f);
+          }
         }
       }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tempty[acc]);         // this warp's TMEM lanes of the accumulator are free again
     }
-    tc_fence_before();
   }
   __syncthreads();
   if (warp == 1) {
     tc_fence_after();
-    tmem_free<GB_N>(tmem_d);
+    tmem_free<G_TMEM>(tmem_base);
   }
 }
 
@@ -144,28 +172,45 @@ static int sb16_tmap(CUtensorMap* tm, const void* base, long long rows, long lon
 
 }  // namespace ssb
 
-extern "C" int ss_gemm_sb16(const void* A, long long lda, long long a_plane, const void* B, long long ldb,
-                            long long b_plane, float* C, long long ldc, int M, int N, int K, const float* bias,
-                            float alpha, float beta, int rowmap, int hidden, void* stream) {
+static int gemm_launch(const void* A, long long lda, long long a_plane, int a_rows, const void* B, long long ldb,
+                       long long b_plane, int b_rows, ssb::GemmParams p, void* stream) {
   using namespace ssb;
-  SS_REQUIRE(M > 0 && N > 0 && K > 0, "ss_gemm_sb16: empty problem %dx%dx%d", M, N, K);
+  SS_REQUIRE(p.M > 0 && p.N > 0 && p.K > 0, "ss_gemm_sb16: empty problem %dx%dx%d", p.M, p.N, p.K);
   SS_REQUIRE(lda % 8 == 0 && ldb % 8 == 0 && a_plane % 8 == 0 && b_plane % 8 == 0,
              "ss_gemm_sb16: pitches/plane strides must be multiples of 8 elements (16 bytes)");
   SS_REQUIRE(((uintptr_t)A & 15) == 0 && ((uintptr_t)B & 15) == 0, "ss_gemm_sb16: operands must be 16-byte aligned");
-  SS_REQUIRE(rowmap == SS_ROWMAP_NONE || (rowmap == SS_ROWMAP_UNIT4 && hidden > 0 && M == 4 * hidden),
+  SS_REQUIRE(p.rowmap == SS_ROWMAP_NONE || (p.rowmap == SS_ROWMAP_UNIT4 && p.hidden > 0 && p.M == 4 * p.hidden),
              "ss_gemm_sb16: bad rowmap");
   CUtensorMap tmA, tmB;
-  int rc = sb16_tmap(&tmA, A, M, K, lda, a_plane, GB_M);
+  int rc = sb16_tmap(&tmA, A, a_rows, p.K, lda, a_plane, GB_M);
   if (rc) return rc;
-  rc = sb16_tmap(&tmB, B, N, K, ldb, b_plane, GB_N);
+  rc = sb16_tmap(&tmB, B, b_rows, p.K, ldb, b_plane, GB_N);
   if (rc) return rc;
-  GemmParams p{C, ldc, bias, alpha, beta, M, N, K, rowmap, hidden};
   static bool attr_set = false;
+  static int n_sm = 148;
   if (!attr_set) {
     cudaFuncSetAttribute(gemm_sb16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, G_SMEM);
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev);
     attr_set = true;
   }
-  dim3 grid(cdiv(N, GB_N), cdiv(M, GB_M));
-  gemm_sb16_kernel<<<grid, G_THREADS, G_SMEM, (cudaStream_t)stream>>>(tmA, tmB, p);
+  const int tiles = p.batch * cdiv(p.N, GB_N) * cdiv(p.M, GB_M);
+  gemm_sb16_kernel<<<tiles < n_sm ? tiles : n_sm, G_THREADS, G_SMEM, (cudaStream_t)stream>>>(tmA, tmB, p);
   return check_launch("ss_gemm_sb16");
+}
+
+extern "C" int ss_gemm_sb16(const void* A, long long lda, long long a_plane, const void* B, long long ldb,
+                            long long b_plane, float* C, long long ldc, int M, int N, int K, const float* bias,
+                            float alpha, float beta, int rowmap, int hidden, void* stream) {
+  ssb::GemmParams p{{C, nullptr}, ldc, bias, alpha, beta, M, N, K, rowmap, hidden, 1, 0, 0};
+  return gemm_launch(A, lda, a_plane, M, B, ldb, b_plane, N, p, stream);
+}
+
+extern "C" int ss_gemm_sb16_x2(const void* A, long long lda, long long a_plane, int a_batch_rows, const void* B,
+                               long long ldb, long long b_plane, int b_batch_rows, float* C0, float* C1,
+                               long long ldc, int M, int N, int K, float alpha, float beta, int rowmap, int hidden,
+                               void* stream) {
+  ssb::GemmParams p{{C0, C1}, ldc, nullptr, alpha, beta, M, N, K, rowmap, hidden, 2, a_batch_rows, b_batch_rows};
+  return gemm_launch(A, lda, a_plane, a_batch_rows + M, B, ldb, b_plane, b_batch_rows + N, p, stream);
 }

@@ -196,11 +196,13 @@ def backward(ws, wt, p, grads, mix, src, lens_dev, c0, F, n_out, gout, dmask_ext
              ws.dGT.buf, LL(ws.dGT.ld), LL(ws.dGT.plane), dh0[2 * l:2 * l + 2] if want_d0 else None,
              dc0[2 * l:2 * l + 2] if want_d0 else None, ws.bwd_sync, T, B, H, st)
         xT = ws.x0T if l == 0 else ws.outT[l - 1]
-        for d, suf in enumerate(("", "_reverse")):
-            gT = _sb_view(ws.dGT, d * 4 * H, 4 * H)
-            _gemm(gT, xT, grads["blstm.weight_ih_l%d%s" % (l, suf)], beta=beta, rowmap=UNIT4, hidden=H, K=TB)
-            _gemm(gT, _sb_view(ws.hprevT[l], d * H, H), grads["blstm.weight_hh_l%d%s" % (l, suf)], beta=beta,
-                  rowmap=UNIT4, hidden=H, K=TB)
+        # both directions' dW_ih = dG^T x and dW_hh = dG^T h_prev in one launch each (rows d*4H.. of dGT; d*H.. of hprevT)
+        I = xT.rows
+        for B_op, b_rows, N, kind in ((xT, 0, I, "ih"), (ws.hprevT[l], H, H, "hh")):
+            g0, g1 = grads["blstm.weight_%s_l%d" % (kind, l)], grads["blstm.weight_%s_l%d_reverse" % (kind, l)]
+            assert g0.stride(0) == g1.stride(0) and g0.stride(1) == 1
+            call("gemm_sb16_x2", ws.dGT.buf, LL(ws.dGT.ld), LL(ws.dGT.plane), 4 * H, B_op.buf, LL(B_op.ld), LL(B_op.plane),
+                 b_rows, g0, g1, LL(g0.stride(0)), 4 * H, N, TB, 1.0, float(beta), UNIT4, H, st)
         call("colsum_sb16", ws.dG.buf, LL(ws.dG.ld), LL(ws.dG.plane), TB, 8 * H, ws.cs_partial, ws.db, UNIT4, H, st)
         for d, suf in enumerate(("", "_reverse")):
             _acc(grads, "blstm.bias_ih_l%d%s" % (l, suf), ws.db[d * 4 * H:(d + 1) * 4 * H], accumulate)
