@@ -1,0 +1,95 @@
+"""Shapes beyond the golden cases, through the same drop-in module:
+ * batch 100 (the reference recipe's default, run_train.sh:17) -> the B > 64 kernels, checked against the fp64 oracle;
+ * config 5 lengths (16 kHz, 20 s -> T = 2501): size-independent properties -- STFT -> iSTFT with an all-ones mask
+   returns the signal, and eval-mode masks of a batch equal those of its utterances run one at a time."""
+import numpy as np
+import pytest
+import torch
+
+import common
+from oracle import upit_oracle as uo
+from ssb200 import ops, synth, uPIT
+
+pytestmark = pytest.mark.gpu
+
+
+def _rand_batch(seed, lens, F, S):
+    rng = np.random.default_rng(seed)
+    samples = []
+    for L in lens:
+        d = {"mix": rng.random((L, F), dtype=np.float32)}
+        for s in range(S):
+            d["source%d" % (s + 1)] = rng.random((L, F), dtype=np.float32) * 0.5
+        samples.append(d)
+    return samples
+
+
+def test_batch_100_matches_oracle():
+    F, S, B = 129, 2, 100
+    lens = sorted(np.random.default_rng(1).integers(6, 25, size=B).tolist(), reverse=True)
+    samples = _rand_batch(2, lens, F, S)
+    batch = uPIT.Collator("mix")(samples)
+    torch.manual_seed(9)
+    model = uPIT.SepDNN(0, feat_dim=str(F), num_spk=str(S)).cuda()
+    sd = {k: (v.detach().double().cpu().clone() if v.is_floating_point() else v.cpu().clone())
+          for k, v in model.state_dict().items()}
+    torch.manual_seed(21)
+    loss, norm = uPIT.compute_loss(model, 0, batch)
+    loss.backward()
+    torch.cuda.synchronize()
+    torch.manual_seed(21)
+    h0, c0 = torch.randn(4, B, 600).double(), torch.randn(4, B, 600).double()
+    order = np.argsort(np.array(lens))[::-1]
+    srt = [samples[i] for i in order]
+    mix, tl = common.pad_time_major([s["mix"] for s in srt])
+    sources = [common.pad_time_major([s["source%d" % (i + 1)] for s in srt])[0] for i in range(S)]
+    params = {k: v.requires_grad_(True) for k, v in sd.items() if v.is_floating_point() and "running" not in k}
+    sd.update(params)
+    oloss, onorm, _, oidx, _, _ = uo.upit_compute_loss(sd, mix, sources, tl, h0, c0)
+    oloss.backward()
+    assert float(norm) == float(onorm)
+    assert abs(float(loss.detach()) - float(oloss)) <= 1e-3 * float(oloss)
+    assert np.array_equal(model.last["indices"].cpu().numpy(), oidx.numpy())
+    for k, p in model.named_parameters():
+        assert common.rel(p.grad.cpu().numpy(), params[k].grad.numpy()) <= 1e-3, k
+
+
+def test_cfg5_stft_istft_roundtrip():
+    n, n_fft, hop = 320000, 512, 128
+    lens = [n, n - 777, 200000]
+    sigs = [synth.mixture(90 + i, L, 2, sr=16000)[0] for i, L in enumerate(lens)]
+    rag = ops.Ragged(lens, n_fft, hop, "cuda")
+    assert int(rag.T[0]) == 2501
+    flat = torch.from_numpy(np.concatenate(sigs)).cuda()
+    spec = ops.stft(flat, rag, complex_out=True)
+    ones = torch.ones(rag.total_frames * rag.F, device="cuda")
+    wav, off = ops.istft_masked(spec, ones, rag, 1, out_f32=True)
+    wav = wav.cpu().numpy()
+    for u, s in enumerate(sigs):
+        L = int(rag.L[u])
+        got = wav[off[u]:off[u] + L]
+        assert np.abs(got - s[:L]).max() <= 1e-4 * np.abs(s).max(), u
+
+
+def test_cfg5_masks_batch_invariance(tmp_path):
+    F, B, T = 257, 8, 2501
+    lens = [T - 37 * b for b in range(B)]
+    samples = [{"mix": s["mix"], "name": "u%d.npz" % i} for i, s in enumerate(_rand_batch(4, lens, F, 0))]
+    torch.manual_seed(2)
+    model = uPIT.SepDNN(0, feat_dim=str(F), num_spk="2").cuda()
+    model.eval()
+    coll = uPIT.Collator("mix")
+    h = torch.randn(4, B, 600)
+    c = torch.randn(4, B, 600)
+    model.init_hidden = lambda n: (h.cuda(), c.cuda())
+    (tmp_path / "all").mkdir()
+    uPIT.compute_masks(model, coll(samples), str(tmp_path / "all"))
+    (tmp_path / "one").mkdir()
+    for i in (0, 3, 7):
+        model.init_hidden = lambda n, i=i: (h[:, i:i + 1].contiguous().cuda(), c[:, i:i + 1].contiguous().cuda())
+        uPIT.compute_masks(model, coll([samples[i]]), str(tmp_path / "one"))
+        a = np.load(str(tmp_path / "all" / ("u%d.npz" % i)))
+        b = np.load(str(tmp_path / "one" / ("u%d.npz" % i)))
+        for k in ("s1", "s2"):
+            assert a[k].shape == (F, lens[i])
+            assert np.abs(a[k] - b[k]).max() <= 2e-5, (i, k)
