@@ -342,7 +342,9 @@ int launch_lstm_bwd_ks(const LstmBwdParams& p, const void* whhT, long long whhT_
   attr[1].id = cudaLaunchAttributeCooperative;
   attr[1].val.cooperative = 1;
   cfg.attrs = attr;
-  cfg.numAttrs = 2;
+  // SSB_NO_COOP=1 drops the co-residency guarantee: Nsight Compute 2025.x cannot replay a launch that is both
+  // cooperative and clustered; on an otherwise idle GPU the 80 CTAs are co-resident anyway.  Profiling aid only.
+  cfg.numAttrs = getenv("SSB_NO_COOP") ? 1 : 2;
   cudaError_t e = cudaLaunchKernelEx(&cfg, kern, tmW, tmG, p);
   if (e != cudaSuccess) {
     set_error("ss_lstm_bwd (K-split clusters): launch failed: %s", cudaGetErrorString(e));
