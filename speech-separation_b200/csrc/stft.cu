@@ -6,19 +6,23 @@
 
 namespace ssb {
 
-constexpr int STFT_TILE_T = 32;      // frames per tile
-constexpr int STFT_THREADS = 256;
+constexpr int STFT_TILE_T = 32;      // frames per tile (ss_stft_tile_frames)
+constexpr int STFT_HALF = 16;        // frame g of a tile rides in the lo lanes of the packed ops, frame 16 + g in the hi lanes
 
 // Packed real FFT: z[n] = x[2n] + i x[2n+1] (M = NFFT/2 complex points), M = 16 * P with P = 8 (NFFT 256) or 16 (512).
-// P threads own a frame.  Pass 1: thread n2 holds z[P*n1 + n2], n1 < 16, does a radix-16 FFT in registers and
-// multiplies by W_M^(n2*k1) (kept in registers).  One shared-memory exchange.  Pass 2: thread j does the radix-P FFT
-// over n2 for k1 = j (+ j+8 when P = 8): every lane is busy in both passes.  The split X[k] = E[k] - i w_k D[k] needs
-// Z[M-k], which lives in lane (P-j) mod P of the same group: fetched with warp shuffles, no second exchange.
-// The CTA is persistent over tiles so the per-thread twiddles / tables are built once.
+// P threads own a PAIR of frames (g, 16 + g) of the tile and run both transforms at once on the fp32x2 pipe
+// (fft.cuh, p2 / c2): the tile's samples sit in shared memory interleaved (A_i, B_i) so one 16-byte load yields
+// (re_A, re_B, im_A, im_B) of z[n], and the window / twiddle tables hold every factor duplicated.
+// Pass 1: thread n2 holds z[P*n1 + n2], n1 < 16, does a radix-16 FFT in registers and multiplies by W_M^(n2*k1).
+// One shared-memory exchange (re then im through the same buffer).  Pass 2: thread j does the radix-P FFT over n2
+// for k1 = j (+ j+8 when P = 8): every lane is busy in both passes.  The split X[k] = E[k] - i w_k D[k] needs
+// Z[M-k], which another lane of the group holds: second exchange through the same buffer in natural order.
+// The CTA is persistent over a contiguous range of tiles so the tables are built once.
 template <int NFFT>
 struct StftCfg {
-  static constexpr int M = NFFT / 2, F = M + 1, P = M / 16, NA = 16 / P, G = STFT_THREADS / P;
-  static constexpr int SCR = 16 * (P + 1) + (P == 8 ? 8 : 0);     // float2 per frame group (padded rows; the +8
+  static constexpr int M = NFFT / 2, F = M + 1, P = M / 16, NA = 16 / P, G = STFT_HALF;
+  static constexpr int THREADS = G * P, CTAS = 512 / THREADS;
+  static constexpr int SCR = 16 * (P + 1) + (P == 8 ? 8 : 0);     // p2 per frame-pair group (padded rows; the +8
                                                                   // puts the two groups of a half warp on disjoint banks)
   static constexpr int PITCH = P == 8 ? STFT_TILE_T + 4 : STFT_TILE_T + 2;   // staging pitch: conflict-free writes
 };
@@ -31,45 +35,43 @@ __device__ __forceinline__ float sqrt_approx(float x) {
 }
 
 template <int P>
-__device__ __forceinline__ void fft_p(float2* v) {
+__device__ __forceinline__ void fft_p(c2* v) {
   if (P == 8) fft8(v); else fft16(v);
 }
 
 template <int NFFT, bool COMPLEX, bool LAYOUT_TF, bool LOGMAG>
-__global__ void __launch_bounds__(STFT_THREADS, 2) stft_kernel(const float* __restrict__ sig,
-                                                              const long long* __restrict__ sig_off,
-                                                              const long long* __restrict__ frame_off,
-                                                              const int* __restrict__ tile_off, int n_utts,
-                                                              int total_tiles, int hop, float* __restrict__ out) {
+__global__ void __launch_bounds__(StftCfg<NFFT>::THREADS, StftCfg<NFFT>::CTAS)
+    stft_kernel(const float* __restrict__ sig, const long long* __restrict__ sig_off,
+                const long long* __restrict__ frame_off, const int* __restrict__ tile_off, int n_utts, int total_tiles,
+                int hop, float* __restrict__ out) {
   using C = StftCfg<NFFT>;
-  constexpr int M = C::M, F = C::F, P = C::P, NA = C::NA, G = C::G, TT = STFT_TILE_T, PITCH = C::PITCH;
+  constexpr int M = C::M, F = C::F, P = C::P, NA = C::NA, G = C::G, TT = STFT_TILE_T, PITCH = C::PITCH, NT = C::THREADS;
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  float2* wtab = reinterpret_cast<float2*>(smem_raw);          // [M] window pairs (w[2n], w[2n+1])
+  float2* wtab = reinterpret_cast<float2*>(smem_raw);          // [M] window pairs (w[2n], w[2n+1]) / 2
   float2* ptw = wtab + M;                                      // [M] exp(-i pi k / M)
-  float2* scr_all = ptw + M;                                   // [G][SCR]
+  float2* tw = ptw + M;                                        // [16][P] W_M^(j*k1)
+  const int half_span = (STFT_HALF - 1) * hop + NFFT;          // samples one half of the tile reads
+  float* sigs = reinterpret_cast<float*>(tw + 16 * P);         // [half_span][2]: (A_i, B_i), B = A shifted by 16 hops
+  p2* scr_all = reinterpret_cast<p2*>(sigs + 2 * half_span);   // [G][SCR]
   float* stage = reinterpret_cast<float*>(scr_all + G * C::SCR);          // [F][PITCH] (float or float2)
-  const int span = (TT - 1) * hop + NFFT;
-  float* sigs = stage + F * PITCH * (COMPLEX ? 2 : 1);
 
   const int tid = threadIdx.x, lane = tid & 31;
   const int g = tid / P, j = tid % P;
-  for (int n = tid; n < M; n += STFT_THREADS) {
+  for (int n = tid; n < M; n += NT) {
     float s, c;
     sincospif((float)n / (float)M, &s, &c);                    // angle pi*n/M = 2*pi*n/NFFT
-    ptw[n] = make_float2(0.5f * c, -0.5f * s);                  // 0.5 * exp(-i pi n / M): the 1/2 of the split folded in
+    ptw[n] = make_float2(c, -s);
     float c0 = cospif(2.0f * (float)(2 * n) / (float)NFFT), c1 = cospif(2.0f * (float)(2 * n + 1) / (float)NFFT);
-    wtab[n] = make_float2(0.5f - 0.5f * c0, 0.5f - 0.5f * c1);
+    wtab[n] = make_float2(0.5f * (0.5f - 0.5f * c0), 0.5f * (0.5f - 0.5f * c1));   // Hann / 2
   }
-  float2 tw1[16];                                              // W_M^(j*k1)
-#pragma unroll
-  for (int k1 = 0; k1 < 16; ++k1) {
+  for (int e = tid; e < 16 * P; e += NT) {
     float s, c;
-    sincospif(2.0f * (float)(j * k1) / (float)M, &s, &c);
-    tw1[k1] = make_float2(c, -s);
+    sincospif(2.0f * (float)((e % P) * (e / P)) / (float)M, &s, &c);
+    tw[e] = make_float2(c, -s);
   }
-  float2* scr = scr_all + g * C::SCR;
-  const int src_lane = (lane & ~(P - 1)) | ((P - j) & (P - 1));
-  (void)span;
+  p2* scr = scr_all + g * C::SCR;
+  const int warp_g0 = (tid & ~31) / P;                         // first frame of this warp's groups
+  const int boff = STFT_HALF * hop;
 
   // contiguous tile range per CTA: the utterance index only ever advances, no search per tile
   const int tile_begin = (int)((long long)total_tiles * blockIdx.x / gridDim.x);
@@ -83,147 +85,173 @@ __global__ void __launch_bounds__(STFT_THREADS, 2) stft_kernel(const float* __re
     }
     u = lo;
   }
-  constexpr int PF = NFFT == 256 ? 9 : 18;                                       // samples per thread prefetched in registers
-  float pre[PF];
-  // loads the span of `tile` (utterance uu) into registers: reflect padding as np.pad(y, n_fft//2, 'reflect')
-  auto prefetch = [&](int tile, int uu) {
-    const int t0 = (tile - tile_off[uu]) * TT;
-    const long long s0 = sig_off[uu];
-    const int n_samp = (int)(sig_off[uu + 1] - s0);
-    const int T = (int)(frame_off[uu + 1] - frame_off[uu]);
-    const int used = (min(TT, T - t0) - 1) * hop + NFFT;
-    const int p0 = t0 * hop - NFFT / 2;
-#pragma unroll
-    for (int i = 0; i < PF; ++i) {
-      const int idx = tid + i * STFT_THREADS;
-      int q = p0 + idx;
-      if (q < 0) q = -q;
-      if (q >= n_samp) q = 2 * (n_samp - 1) - q;
-      pre[i] = idx < used ? sig[s0 + q] : 0.0f;
+
+  // tile samples -> shared memory with 4-byte cp.async: no registers held while they fly, so the next tile's fill is
+  // issued as soon as pass 1 has read the current one and overlaps the rest of the transform.
+  // Reflect padding as np.pad(y, n_fft//2, 'reflect').
+  const uint32_t sig_s = smem_u32(sigs);
+  auto fill = [&](int tile_, int uu) {
+    const int t0_ = (tile_ - tile_off[uu]) * TT;
+    const long long s0_ = sig_off[uu];
+    const int n_samp_ = (int)(sig_off[uu + 1] - s0_);
+    const int T_ = (int)(frame_off[uu + 1] - frame_off[uu]);
+    const int used_ = (min(TT, T_ - t0_) - 1) * hop + NFFT;
+    const int p0_ = t0_ * hop - NFFT / 2;
+    const float* src = sig + s0_;
+    const bool interior = p0_ >= 0 && p0_ + used_ <= n_samp_;
+#pragma unroll 6
+    for (int idx = tid; idx < used_; idx += NT) {
+      int q = p0_ + idx;
+      if (!interior) {
+        if (q < 0) q = -q;
+        if (q >= n_samp_) q = 2 * (n_samp_ - 1) - q;
+      }
+      if (idx < half_span) cp_async4(sig_s + 8 * idx, src + q);
+      if (idx >= boff) cp_async4(sig_s + 8 * (idx - boff) + 4, src + q);
     }
+    cp_async_commit();
   };
-  if (tile_begin < tile_end) prefetch(tile_begin, u);
+  if (tile_begin < tile_end) fill(tile_begin, u);
 
   for (int tile = tile_begin; tile < tile_end; ++tile) {
     const int t0 = (tile - tile_off[u]) * TT;
-    const long long s0 = sig_off[u];
-    const int n_samp = (int)(sig_off[u + 1] - s0);
     const int T = (int)(frame_off[u + 1] - frame_off[u]);
     const int nt = min(TT, T - t0);
-    const int used = (nt - 1) * hop + NFFT;
-    __syncthreads();                                           // previous tile fully written out; tables ready
-#pragma unroll
-    for (int i = 0; i < PF; ++i) {
-      const int idx = tid + i * STFT_THREADS;
-      if (idx < used) sigs[idx] = pre[i];
-    }
-    {                                                          // spans longer than PF*256 samples (large hops)
-      const int p0 = t0 * hop - NFFT / 2;
-      for (int idx = tid + PF * STFT_THREADS; idx < used; idx += STFT_THREADS) {
-        int q = p0 + idx;
-        if (q < 0) q = -q;
-        if (q >= n_samp) q = 2 * (n_samp - 1) - q;
-        sigs[idx] = sig[s0 + q];
-      }
-    }
-    __syncthreads();
-    const int u_cur = u;
-    if (tile + 1 < tile_end) {                                 // next tile's samples fly while this one is transformed
-      while (tile_off[u + 1] <= tile + 1) ++u;
-      prefetch(tile + 1, u);
-    }
-    float* out_u = out + frame_off[u_cur] * (long long)F * (COMPLEX ? 2 : 1);
-#pragma unroll 1
-    for (int fb = 0; fb < TT; fb += G) {
-      if (fb >= nt) break;                                     // uniform
-      const int fl = fb + g;
-      const bool live = fl < nt;
-      const float* x = sigs + (live ? fl : 0) * hop;
-      float2 v[16];
+    float* out_u = out + frame_off[u] * (long long)F * (COMPLEX ? 2 : 1);
+    cp_async_wait_all();
+    __syncthreads();                                           // samples landed; previous tile fully written out
+    if (warp_g0 < nt) {
+      c2 v[16];
+      {
+      const ulonglong2* sp = reinterpret_cast<const ulonglong2*>(sigs) + g * (hop >> 1) + j;
 #pragma unroll
       for (int n1 = 0; n1 < 16; ++n1) {
-        const int n = P * n1 + j;
-        const float2 xs = *reinterpret_cast<const float2*>(x + 2 * n);
-        const float2 w = wtab[n];
-        v[n1] = make_float2(xs.x * w.x, xs.y * w.y);
+        const ulonglong2 xs = sp[P * n1];
+        const float2 w = wtab[P * n1 + j];
+        v[n1] = {scale2(xs.x, w.x), scale2(xs.y, w.y)};
       }
+    }
       fft16(v);
-      scr[j] = v[0];
 #pragma unroll
-      for (int k1 = 1; k1 < 16; ++k1) scr[k1 * (P + 1) + j] = cmul(v[k1], tw1[k1]);
-      __syncwarp();
-      float2 z[NA][P], r[NA][P];
-#pragma unroll
-      for (int a = 0; a < NA; ++a) {
-#pragma unroll
-        for (int n2 = 0; n2 < P; ++n2) z[a][n2] = scr[(j + P * a) * (P + 1) + n2];
-        fft_p<P>(z[a]);                                        // z[a][k2] = Z[(j + P*a) + 16*k2]
+      for (int k1 = 1; k1 < 16; ++k1) {
+        const float2 w = tw[k1 * P + j];
+        v[k1] = cmul_s(v[k1], w.x, w.y);
       }
-      __syncwarp();                                            // scr may be rewritten by the next frame block
+      c2 z[NA][P];
+#pragma unroll
+      for (int k1 = 0; k1 < 16; ++k1) scr[k1 * (P + 1) + j] = v[k1].re;
+      __syncwarp();
 #pragma unroll
       for (int a = 0; a < NA; ++a)
 #pragma unroll
-        for (int i = 0; i < P; ++i) {
-          r[a][i].x = __shfl_sync(0xffffffffu, z[a][i].x, src_lane);
-          r[a][i].y = __shfl_sync(0xffffffffu, z[a][i].y, src_lane);
-        }
-      if (!live) continue;
+        for (int n2 = 0; n2 < P; ++n2) z[a][n2].re = scr[(j + P * a) * (P + 1) + n2];
+      __syncwarp();
+#pragma unroll
+      for (int k1 = 0; k1 < 16; ++k1) scr[k1 * (P + 1) + j] = v[k1].im;
+      __syncwarp();
 #pragma unroll
       for (int a = 0; a < NA; ++a)
 #pragma unroll
-        for (int k2 = 0; k2 < P; ++k2) {
-          const int k = j + P * a + 16 * k2;
-          // partner Z[M-k]: lane (P-j)%P; for j >= 1 array NA-1-a, index P-1-k2; for j == 0 see the derivation above
-          float2 b;
-          if (NA == 2) {
-            const float2 b0 = a == 0 ? r[0][(P - k2) & (P - 1)] : r[1][P - 1 - k2];
-            const float2 b1 = r[1 - a][P - 1 - k2];
-            b = j == 0 ? b0 : b1;
+        for (int n2 = 0; n2 < P; ++n2) z[a][n2].im = scr[(j + P * a) * (P + 1) + n2];
+      __syncwarp();
+#pragma unroll
+      for (int a = 0; a < NA; ++a) fft_p<P>(z[a]);             // z[a][k2] = Z[(j + P*a) + 16*k2]
+
+      // Bins k and M-k share 2E = Z[k] + conj(Z[M-k]), 2D = Z[k] - conj(Z[M-k]) and the product w_k D:
+      //   X[k] = E - i w_k D,  X[M-k] = conj(E) - i conj(w_k D)
+      // so each thread finishes the pairs of its own bins below M/2 (k2 < P/2) and only the upper bins travel
+      // through the exchange buffer (natural order, re in [0, M/2), im in [M/2, M)).  The window table carries the
+      // 1/2 of E and D.
+#pragma unroll
+      for (int a = 0; a < NA; ++a)
+#pragma unroll
+        for (int k2 = P / 2; k2 < P; ++k2) {
+          scr[j + P * a + 16 * k2 - M / 2] = z[a][k2].re;
+          scr[j + P * a + 16 * k2] = z[a][k2].im;
+        }
+      __syncwarp();
+      const bool liveA = g < nt, liveB = STFT_HALF + g < nt;
+      const int fa = g, fb = STFT_HALF + g;
+      // one output bin of both frames
+      auto emit = [&](int k, p2 Xr, p2 Xi) {
+        if (COMPLEX) {
+          float ra, rb, ia, ib;
+          upk(Xr, ra, rb);
+          upk(Xi, ia, ib);
+          if (LAYOUT_TF) {
+            if (liveA) reinterpret_cast<float2*>(out_u)[(long long)(t0 + fa) * F + k] = make_float2(ra, ia);
+            if (liveB) reinterpret_cast<float2*>(out_u)[(long long)(t0 + fb) * F + k] = make_float2(rb, ib);
           } else {
-            const float2 b0 = r[0][(P - k2) & (P - 1)], b1 = r[0][P - 1 - k2];
-            b = j == 0 ? b0 : b1;
+            reinterpret_cast<float2*>(stage)[k * PITCH + fa] = make_float2(ra, ia);
+            reinterpret_cast<float2*>(stage)[k * PITCH + fb] = make_float2(rb, ib);
           }
-          const float2 za = z[a][k2];
-          const float2 e = make_float2(za.x + b.x, za.y - b.y);          // 2E = Z[k] + conj(Z[M-k])
-          const float2 d = make_float2(za.x - b.x, za.y + b.y);          // 2D = Z[k] - conj(Z[M-k])
-          const float2 wd = cmul(ptw[k], d);                             // (w_k / 2) * 2D
-          const float2 X = make_float2(fmaf(0.5f, e.x, wd.y), fmaf(0.5f, e.y, -wd.x));   // E - i w_k D
-          if (COMPLEX) {
-            if (LAYOUT_TF) reinterpret_cast<float2*>(out_u)[(long long)(t0 + fl) * F + k] = X;
-            else reinterpret_cast<float2*>(stage)[k * PITCH + fl] = X;
+        } else {
+          float ma, mb;
+          upk(fma2(Xr, Xr, mul2(Xi, Xi)), ma, mb);
+          ma = sqrt_approx(ma);
+          mb = sqrt_approx(mb);
+          if (LOGMAG) {
+            ma = logf(fmaxf(ma, 1e-8f));
+            mb = logf(fmaxf(mb, 1e-8f));
+          }
+          if (LAYOUT_TF) {
+            if (liveA) out_u[(long long)(t0 + fa) * F + k] = ma;
+            if (liveB) out_u[(long long)(t0 + fb) * F + k] = mb;
           } else {
-            float m = sqrt_approx(fmaf(X.x, X.x, X.y * X.y));
-            if (LOGMAG) m = logf(fmaxf(m, 1e-8f));
-            if (LAYOUT_TF) out_u[(long long)(t0 + fl) * F + k] = m;
-            else stage[k * PITCH + fl] = m;
-          }
-          if (k == 0) {                                        // Nyquist bin from Z[0]: X[M] = Re - Im
-            const float2 XN = make_float2(za.x - za.y, 0.0f);
-            if (COMPLEX) {
-              if (LAYOUT_TF) reinterpret_cast<float2*>(out_u)[(long long)(t0 + fl) * F + M] = XN;
-              else reinterpret_cast<float2*>(stage)[M * PITCH + fl] = XN;
-            } else {
-              float m = fabsf(XN.x);
-              if (LOGMAG) m = logf(fmaxf(m, 1e-8f));
-              if (LAYOUT_TF) out_u[(long long)(t0 + fl) * F + M] = m;
-              else stage[M * PITCH + fl] = m;
-            }
+            stage[k * PITCH + fa] = ma;
+            stage[k * PITCH + fb] = mb;
           }
         }
+      };
+#pragma unroll
+      for (int a = 0; a < NA; ++a)
+#pragma unroll
+        for (int k2 = 0; k2 < P / 2; ++k2) {
+          const int k = j + P * a + 16 * k2;                   // 0 <= k < M/2; the partner bin is M - k
+          const p2 bx = scr[(M / 2 - k) & (M / 2 - 1)], by = scr[M / 2 + ((M / 2 - k) & (M / 2 - 1))];
+          const p2 zx = z[a][k2].re, zy = z[a][k2].im;
+          const p2 ex = add2(zx, bx), dx = sub2(zx, bx), ey = sub2(zy, by), dy = add2(zy, by);
+          const float2 w = ptw[k];
+          const c2 wd = cmul_s(c2{dx, dy}, w.x, w.y);          // w_k D
+          const p2 wr = wd.re, wi = wd.im;
+          p2 Xr = add2(ex, wi), Xi = sub2(ey, wr);             // X[k]
+          p2 Yr = sub2(ex, wi), Yi = neg2(add2(ey, wr));       // X[M-k]
+          if (a == 0 && k2 == 0) {                             // k == 0 (lane j == 0): X[0] = Re Z + Im Z, X[M] = Re Z - Im Z
+            const p2 s = add2(zx, zy), d = sub2(zx, zy);
+            const bool k0 = j == 0;
+            Xr = k0 ? add2(s, s) : Xr;
+            Xi = k0 ? 0ull : Xi;
+            Yr = k0 ? add2(d, d) : Yr;
+            Yi = k0 ? 0ull : Yi;
+          }
+          emit(k, Xr, Xi);
+          emit(M - k, Yr, Yi);
+        }
+      if (j == 0) {                                            // k = M/2 pairs with itself: X = conj(Z)
+        const p2 zx = z[0][P / 2].re, zy = z[0][P / 2].im;
+        emit(M / 2, add2(zx, zx), neg2(add2(zy, zy)));
+      }
+    }
+    __syncthreads();                                           // every warp is done with the samples; stage complete
+    const int T_cur = T;
+    if (tile + 1 < tile_end) {                                 // next tile's samples fly during the write-out
+      while (tile_off[u + 1] <= tile + 1) ++u;
+      fill(tile + 1, u);
     }
     if (!LAYOUT_TF) {
-      __syncthreads();
       const int warp = tid >> 5;
       if (lane < nt) {
-        constexpr int NW = STFT_THREADS / 32;
+        constexpr int NW = NT / 32;
         if (COMPLEX) {
-          float2* o = reinterpret_cast<float2*>(out_u) + (long long)warp * T + t0 + lane;
+          float2* o = reinterpret_cast<float2*>(out_u) + (long long)warp * T_cur + t0 + lane;
           const float2* sgp = reinterpret_cast<const float2*>(stage) + warp * PITCH + lane;
-          for (int k = warp; k < F; k += NW, o += (long long)NW * T, sgp += NW * PITCH) *o = *sgp;
+#pragma unroll 4
+          for (int k = warp; k < F; k += NW, o += (long long)NW * T_cur, sgp += NW * PITCH) *o = *sgp;
         } else {
-          float* o = out_u + (long long)warp * T + t0 + lane;
+          float* o = out_u + (long long)warp * T_cur + t0 + lane;
           const float* sgp = stage + warp * PITCH + lane;
-          for (int k = warp; k < F; k += NW, o += (long long)NW * T, sgp += NW * PITCH) *o = *sgp;
+#pragma unroll 4
+          for (int k = warp; k < F; k += NW, o += (long long)NW * T_cur, sgp += NW * PITCH) *o = *sgp;
         }
       }
     }
@@ -234,12 +262,14 @@ template <int NFFT, bool COMPLEX, bool TF, bool LOGMAG>
 static int launch_stft(const float* sig, const long long* sig_off, const long long* frame_off, const int* tile_off,
                        int n_utts, int total_tiles, int hop, float* out, cudaStream_t st) {
   using C = StftCfg<NFFT>;
-  const int span = (STFT_TILE_T - 1) * hop + NFFT;
-  size_t smem = (size_t)(2 * C::M + C::G * C::SCR) * 8 + (size_t)C::F * C::PITCH * (COMPLEX ? 8 : 4) + (size_t)span * 4;
+  const int half_span = (STFT_HALF - 1) * hop + NFFT;
+  size_t smem = (size_t)(2 * C::M + 16 * C::P) * 8 + (size_t)half_span * 8 + (size_t)C::G * C::SCR * 8 +
+                (size_t)C::F * C::PITCH * (COMPLEX ? 8 : 4);
   auto kern = stft_kernel<NFFT, COMPLEX, TF, LOGMAG>;
   cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-  const int grid = total_tiles < 148 * 2 ? total_tiles : 148 * 2;      // persistent: 2 CTAs per SM
-  kern<<<grid, STFT_THREADS, smem, st>>>(sig, sig_off, frame_off, tile_off, n_utts, total_tiles, hop, out);
+  const int resident = 148 * C::CTAS;                                  // persistent: every SM full
+  const int grid = total_tiles < resident ? total_tiles : resident;
+  kern<<<grid, C::THREADS, smem, st>>>(sig, sig_off, frame_off, tile_off, n_utts, total_tiles, hop, out);
   return check_launch("ss_stft");
 }
 
