@@ -73,7 +73,8 @@ __global__ void __launch_bounds__(StftCfg<NFFT>::THREADS, StftCfg<NFFT>::CTAS)
   const int warp_g0 = (tid & ~31) / P;                         // first frame of this warp's groups
   const int boff = STFT_HALF * hop;
 
-  // contiguous tile range per CTA: the utterance index only ever advances, no search per tile
+  // contiguous tile range per CTA: the utterance cursor only ever advances, and its offsets stay in registers
+  // until the range crosses into the next utterance (no dependent global loads per tile)
   const int tile_begin = (int)((long long)total_tiles * blockIdx.x / gridDim.x);
   const int tile_end = (int)((long long)total_tiles * (blockIdx.x + 1) / gridDim.x);
   int u = 0;
@@ -85,39 +86,55 @@ __global__ void __launch_bounds__(StftCfg<NFFT>::THREADS, StftCfg<NFFT>::CTAS)
     }
     u = lo;
   }
+  int u_tlo, u_thi, u_nsamp, u_T;                              // cursor = utterance of the tile being filled
+  long long u_s0, u_fo;
+  auto load_utt = [&]() {
+    u_tlo = tile_off[u];
+    u_thi = tile_off[u + 1];
+    u_s0 = sig_off[u];
+    u_nsamp = (int)(sig_off[u + 1] - u_s0);
+    u_fo = frame_off[u];
+    u_T = (int)(frame_off[u + 1] - u_fo);
+  };
+  load_utt();
 
   // tile samples -> shared memory with 4-byte cp.async: no registers held while they fly, so the next tile's fill is
-  // issued as soon as pass 1 has read the current one and overlaps the rest of the transform.
-  // Reflect padding as np.pad(y, n_fft//2, 'reflect').
+  // issued before the current tile is written out.  Reflect padding as np.pad(y, n_fft//2, 'reflect').
   const uint32_t sig_s = smem_u32(sigs);
-  auto fill = [&](int tile_, int uu) {
-    const int t0_ = (tile_ - tile_off[uu]) * TT;
-    const long long s0_ = sig_off[uu];
-    const int n_samp_ = (int)(sig_off[uu + 1] - s0_);
-    const int T_ = (int)(frame_off[uu + 1] - frame_off[uu]);
-    const int used_ = (min(TT, T_ - t0_) - 1) * hop + NFFT;
-    const int p0_ = t0_ * hop - NFFT / 2;
-    const float* src = sig + s0_;
-    const bool interior = p0_ >= 0 && p0_ + used_ <= n_samp_;
-#pragma unroll 6
-    for (int idx = tid; idx < used_; idx += NT) {
-      int q = p0_ + idx;
-      if (!interior) {
-        if (q < 0) q = -q;
-        if (q >= n_samp_) q = 2 * (n_samp_ - 1) - q;
+  int f_t0 = 0;                                                // frame offset of the filled tile inside its utterance
+  auto fill = [&](int tile_) {
+    while (tile_ >= u_thi) {
+      ++u;
+      load_utt();
+    }
+    f_t0 = (tile_ - u_tlo) * TT;
+    const int used_ = (min(TT, u_T - f_t0) - 1) * hop + NFFT;
+    const int p0_ = f_t0 * hop - NFFT / 2;
+    const float* sp = sig + u_s0 + p0_ + tid;
+    uint32_t d = sig_s + 8 * tid;
+    if (p0_ >= 0 && p0_ + used_ <= u_nsamp) {                  // interior tile: straight copy
+#pragma unroll 2
+      for (int idx = tid; idx < used_; idx += NT, sp += NT, d += 8 * NT) {
+        if (idx < half_span) cp_async4(d, sp);
+        if (idx >= boff) cp_async4(d - 8 * boff + 4, sp);
       }
-      if (idx < half_span) cp_async4(sig_s + 8 * idx, src + q);
-      if (idx >= boff) cp_async4(sig_s + 8 * (idx - boff) + 4, src + q);
+    } else {
+      for (int idx = tid; idx < used_; idx += NT, d += 8 * NT) {
+        int q = p0_ + idx;
+        if (q < 0) q = -q;
+        if (q >= u_nsamp) q = 2 * (u_nsamp - 1) - q;
+        if (idx < half_span) cp_async4(d, sig + u_s0 + q);
+        if (idx >= boff) cp_async4(d - 8 * boff + 4, sig + u_s0 + q);
+      }
     }
     cp_async_commit();
   };
-  if (tile_begin < tile_end) fill(tile_begin, u);
+  if (tile_begin < tile_end) fill(tile_begin);
 
   for (int tile = tile_begin; tile < tile_end; ++tile) {
-    const int t0 = (tile - tile_off[u]) * TT;
-    const int T = (int)(frame_off[u + 1] - frame_off[u]);
+    const int t0 = f_t0, T = u_T;                              // the cursor still points at this tile's utterance
     const int nt = min(TT, T - t0);
-    float* out_u = out + frame_off[u] * (long long)F * (COMPLEX ? 2 : 1);
+    float* out_u = out + u_fo * (long long)F * (COMPLEX ? 2 : 1);
     cp_async_wait_all();
     __syncthreads();                                           // samples landed; previous tile fully written out
     if (warp_g0 < nt) {
@@ -234,10 +251,7 @@ __global__ void __launch_bounds__(StftCfg<NFFT>::THREADS, StftCfg<NFFT>::CTAS)
     }
     __syncthreads();                                           // every warp is done with the samples; stage complete
     const int T_cur = T;
-    if (tile + 1 < tile_end) {                                 // next tile's samples fly during the write-out
-      while (tile_off[u + 1] <= tile + 1) ++u;
-      fill(tile + 1, u);
-    }
+    if (tile + 1 < tile_end) fill(tile + 1);                    // next tile's samples fly during the write-out
     if (!LAYOUT_TF) {
       const int warp = tid >> 5;
       if (lane < nt) {
