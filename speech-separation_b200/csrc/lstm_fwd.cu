@@ -16,38 +16,9 @@
 #include <stdlib.h>
 
 #include "../../include/ssb200.h"
-#include "common.cuh"
+#include "lstm_fwd.cuh"
 
 namespace ssb {
-
-constexpr int LF_U = 12;                    // hidden units per CTA
-constexpr int LF_N = 4 * LF_U;              // gate columns per CTA
-constexpr int LF_EPI_WARPS = 12;            // 4 TMEM lane quadrants x 3 column groups of 4 units
-constexpr int LF_THREADS = 32 * LF_EPI_WARPS + 64;
-constexpr int LF_WCHUNK = 2 * LF_N * 128;   // one 64-wide K chunk of the W slice: [hi 48 rows][lo 48 rows] x 128 B
-constexpr int LF_MAXKC = 10;                // H <= 640
-constexpr int LF_XPITCH = 52;               // floats per row of the lo-row exchange buffer
-constexpr int LF_TMEM = 128;
-
-struct LstmFwdParams {
-  float* gx;                 // [T*B][8H] in: x-projection + biases (interleaved gate columns); out: activated gates
-  const float* h0;           // [2][B][H]
-  const float* c0;
-  const int* lens;           // [B]
-  __nv_bfloat16* out;        // sb16 [T*B][2H]
-  long long out_plane;
-  __nv_bfloat16* outT;       // sb16 [2H][ldT] or null: transposed outputs (X^T of the next layer's dW GEMM)
-  __nv_bfloat16* hprevT;     // sb16 [2H][ldT] or null: transposed carried state BEFORE each step (dW_hh GEMM)
-  long long ldT, outT_plane;
-  float* cs;                 // [T*B][2H] or null
-  float* hn;                 // [2][B][H]
-  float* cn;
-  __nv_bfloat16* hbuf;       // [rep][slot 2][dir 2][kc][plane 2][R][64], rows pre-swizzled (SWIZZLE_128B)
-  int REP, EXP, ROT;
-  unsigned int* sync;        // [2]
-  int T, B, H, R, NC, KC, NS;
-  long long* dbg;            // optional clock64 trace of CTA 0: [step][32]
-};
 
 #define LF_STAMP(slot)                                                        \
   do {                                                                        \
@@ -330,7 +301,7 @@ extern "C" int ss_lstm_fwd(float* gx, const void* whh_r, long long whh_ld, long 
   const long long hbuf_bytes = (long long)p.REP * 2 * 2 * p.KC * 2 * p.R * 64 * 2;
   p.hbuf = (__nv_bfloat16*)ws;
   p.sync = (unsigned int*)((char*)ws + hbuf_bytes);
-  cudaMemsetAsync(ws, 0, hbuf_bytes + 256, st);
+  cudaMemsetAsync(ws, 0, hbuf_bytes + 1024, st);
 
   CUtensorMap tmW;
   {
@@ -340,6 +311,12 @@ extern "C" int ss_lstm_fwd(float* gx, const void* whh_r, long long whh_ld, long 
     int rc = make_tmap_bf16(&tmW, whh_r, 3, dims, str, box);
     if (rc) return rc;
   }
+  const bool dual = H == 600 && B > 32 && B <= 64 && p.REP == 1 && p.ROT == 0 &&
+                    !getenv("SSB_GENERIC") && getenv("SSB_FWD_DUAL");
+  if (dual) {   // experimental: two batch halves interleaved per CTA (lstm_fwd_dual.cu); slower today, see its header
+    int rc = launch_lstm_fwd_dual(tmW, p, st);
+    if (rc) return rc;
+  } else {
   const int smem = p.NS * 2 * p.R * 128 + p.KC * LF_WCHUNK + 64 * LF_XPITCH * 4 + 1024 + 256;
   const bool fast = H == 600 && p.R == 64 && p.ROT == 0 && p.dbg == nullptr && !getenv("SSB_GENERIC");
   void* kern = fast ? (void*)lstm_fwd_kernel<true> : (void*)lstm_fwd_kernel<false>;
@@ -349,6 +326,7 @@ extern "C" int ss_lstm_fwd(float* gx, const void* whh_r, long long whh_ld, long 
   if (e != cudaSuccess) {
     set_error("ss_lstm_fwd: cooperative launch failed: %s", cudaGetErrorString(e));
     return -2;
+  }
   }
   if (outT) {   // transposed copies for the dW GEMMs, one HBM-bound pass each instead of scattered stores per step
     int rc = launch_transpose_sb16(out, 2LL * H, out_plane, T * B, 2 * H, outT, ldT, outT_plane, st);

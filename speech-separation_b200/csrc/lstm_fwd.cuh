@@ -1,0 +1,39 @@
+// Shared declarations of the forward recurrence kernels (lstm_fwd.cu: generic + single-context fast path,
+// lstm_fwd_dual.cu: two batch halves interleaved per CTA).
+#pragma once
+#include "common.cuh"
+
+namespace ssb {
+
+constexpr int LF_U = 12;                    // hidden units per CTA
+constexpr int LF_N = 4 * LF_U;              // gate columns per CTA
+constexpr int LF_EPI_WARPS = 12;            // 4 TMEM lane quadrants x 3 column groups of 4 units
+constexpr int LF_THREADS = 32 * LF_EPI_WARPS + 64;
+constexpr int LF_WCHUNK = 2 * LF_N * 128;   // one 64-wide K chunk of the W slice: [hi 48 rows][lo 48 rows] x 128 B
+constexpr int LF_MAXKC = 10;                // H <= 640
+constexpr int LF_XPITCH = 52;               // floats per row of the lo-row exchange buffer
+constexpr int LF_TMEM = 128;
+
+struct LstmFwdParams {
+  float* gx;                 // [T*B][8H] in: x-projection + biases (interleaved gate columns); out: activated gates
+  const float* h0;           // [2][B][H]
+  const float* c0;
+  const int* lens;           // [B]
+  __nv_bfloat16* out;        // sb16 [T*B][2H]
+  long long out_plane;
+  __nv_bfloat16* outT;       // sb16 [2H][ldT] or null: transposed outputs (X^T of the next layer's dW GEMM)
+  __nv_bfloat16* hprevT;     // sb16 [2H][ldT] or null: transposed carried state BEFORE each step (dW_hh GEMM)
+  long long ldT, outT_plane;
+  float* cs;                 // [T*B][2H] or null
+  float* hn;                 // [2][B][H]
+  float* cn;
+  __nv_bfloat16* hbuf;       // [rep][slot 2][dir 2][kc][plane 2][R][64], rows pre-swizzled (SWIZZLE_128B)
+  int REP, EXP, ROT;
+  unsigned int* sync;        // [2]
+  int T, B, H, R, NC, KC, NS;
+  long long* dbg;            // optional clock64 trace of CTA 0: [step][32]
+};
+
+int launch_lstm_fwd_dual(const CUtensorMap& tmW, LstmFwdParams p, cudaStream_t st);
+
+}  // namespace ssb
