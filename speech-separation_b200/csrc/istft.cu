@@ -6,118 +6,233 @@
 
 namespace ssb {
 
-constexpr int IST_TILE_T = 28;     // hops of output per CTA (2 CTAs/SM at n_fft=512)
-constexpr int IST_THREADS = 256;
-constexpr int IST_MAXF = IST_TILE_T + 5;
+constexpr int IST_TILE_T = 28;     // hops of output per tile (ss_istft_tile_hops): at most 32 frames contribute
+constexpr int IST_HALF = 16;       // frame g of the tile rides in the lo lanes of the packed ops, frame 16 + g in the hi lanes
+
+// Same machinery as stft.cu run backwards: P = NFFT/32 threads own a PAIR of frames (g, 16 + g) of the (up to) 32
+// frames that touch the tile's 28 output hops and run both inverse transforms on the packed fp32x2 pipe.
+//   1. X = spec * mask is staged as two planes Re[k][g], Im[k][g] of (frame g, frame 16+g) pairs (coalesced loads
+//      along t in the (F,T) file layout);
+//   2. thread j rebuilds conj(2 Z[k]) for k = P*n1 + j from X[k] and X[M-k] (2E = X[k] + conj X[M-k],
+//      2D = X[k] - conj X[M-k], 2Z = 2E + i conj(w_k) 2D), which is pass-1 input order of the forward FFT;
+//   3. radix-16 in registers, twiddle, one shared-memory exchange (re then im), radix-P: r = FFT(conj 2Z), so
+//      x[2n] = Re r[n] / 2M, x[2n+1] = -Im r[n] / 2M; the synthesis-window table carries the 1/2M and the sign;
+//   4. windowed frames go to shared memory (aliasing the X planes), then overlap-add in ascending frame order like
+//      the reference's python loop, divide by the window-sum-square (table for the fully overlapped interior),
+//      *32767 and the truncating int16 cast, two samples per thread.
+// Persistent CTAs walk (tile, source) work items so the tables are built once and the second source's spectrum
+// reads hit L2.
+template <int NFFT>
+struct IstftCfg {
+  static constexpr int M = NFFT / 2, F = M + 1, P = M / 16, NA = 16 / P, G = IST_HALF;
+  static constexpr int THREADS = G * P, CTAS = 512 / THREADS;
+  static constexpr int XP = P == 8 ? 18 : 17;                      // p2 per row of an X plane (conflict-free both ways)
+  static constexpr int SCR = 16 * (P + 1) + (P == 8 ? 8 : 0);      // p2 per frame-pair group of the FFT exchange
+  static constexpr int FP = NFFT + 16;                             // floats per synthesised frame (bank skew)
+  static constexpr int PLANES = 2 * F * XP * 8;                    // bytes
+  static constexpr int WORK = G * SCR * 8 + 2 * IST_HALF * FP * 4; // bytes: exchange + frames (the planes alias it)
+  static constexpr int REGION = PLANES > WORK ? PLANES : WORK;
+};
+
+template <int P>
+__device__ __forceinline__ void ifft_p(c2* v) {
+  if (P == 8) fft8(v); else fft16(v);
+}
 
 template <int NFFT, bool LAYOUT_TF, bool OUT_F32>
-__global__ void __launch_bounds__(IST_THREADS) istft_kernel(const float2* __restrict__ spec,
-                                                           const float* __restrict__ mask,
-                                                           const long long* __restrict__ frame_off,
-                                                           const long long* __restrict__ wav_off,
-                                                           const int* __restrict__ tile_off, int n_utts, int n_src,
-                                                           int hop, void* __restrict__ out) {
-  constexpr int N = NFFT / 2, F = N + 1, R1 = N / 16, SCR = R1 * 17, XP = 17;
+__global__ void __launch_bounds__(IstftCfg<NFFT>::THREADS, IstftCfg<NFFT>::CTAS)
+    istft_kernel(const float2* __restrict__ spec, const float* __restrict__ mask, const long long* __restrict__ frame_off,
+                 const long long* __restrict__ wav_off, const int* __restrict__ tile_off, int n_utts, int n_src,
+                 int total_tiles, int hop, void* __restrict__ out) {
+  using C = IstftCfg<NFFT>;
+  constexpr int M = C::M, F = C::F, P = C::P, NA = C::NA, G = C::G, NT = C::THREADS, XP = C::XP, FP = C::FP;
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  float2* tw = reinterpret_cast<float2*>(smem_raw);                 // NFFT
-  float2* regA = tw + NFFT;                                         // max(F*XP, 16*SCR) float2: staged X / FFT scratch
-  constexpr int REGA = (F * XP > 16 * SCR) ? F * XP : 16 * SCR;
-  float* frames = reinterpret_cast<float*>(regA + REGA);            // IST_MAXF * NFFT
+  float2* ptw = reinterpret_cast<float2*>(smem_raw);           // [M] exp(+i pi k / M) = conj(w_k)
+  float2* tw = ptw + M;                                        // [16][P] W_M^(j*k1)
+  float2* wsyn = tw + 16 * P;                                  // [M] (hann[2n], -hann[2n+1]) / 2M
+  float* hsq = reinterpret_cast<float*>(wsyn + M);             // [NFFT] hann^2
+  float* wfull = hsq + NFFT;                                   // [hop] window-sum-square of the interior, by q mod hop
+  unsigned char* region = reinterpret_cast<unsigned char*>(wfull + ((hop + 3) & ~3));
+  p2* xre = reinterpret_cast<p2*>(region);                     // [F][XP]
+  p2* xim = xre + F * XP;
+  p2* scr_all = reinterpret_cast<p2*>(region);                 // [G][SCR]   (after the planes are consumed)
+  float* frames = reinterpret_cast<float*>(scr_all + G * C::SCR);          // [32][FP]
 
-  const int tid = threadIdx.x;
-  int lo = 0, hi = n_utts;
-  const int tile = blockIdx.x;
-  while (hi - lo > 1) {
-    int mid = (lo + hi) >> 1;
-    if (tile_off[mid] <= tile) lo = mid; else hi = mid;
-  }
-  const int u = lo, src = blockIdx.y;
-  const int T = (int)(frame_off[u + 1] - frame_off[u]);
-  const int L = hop * (T - 1);                                      // trimmed output length
-  const int j0 = (tile - tile_off[u]) * IST_TILE_T * hop;
-  const int nj = min(IST_TILE_T * hop, L - j0);
-  const int q0 = j0 + NFFT / 2, q1 = q0 + nj - 1;
-  const int i_lo = max(0, (q0 - NFFT + hop) / hop);                 // ceil((q0-NFFT+1)/hop)
-  const int i_hi = min(T - 1, q1 / hop);
-  const int nf = i_hi - i_lo + 1;
-
-  for (int j = tid; j < NFFT; j += IST_THREADS) {
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int g = tid / P, j = tid % P;
+  for (int n = tid; n < M; n += NT) {
     float s, c;
-    sincospif(2.0f * (float)j / (float)NFFT, &s, &c);
-    tw[j] = make_float2(c, -s);
+    sincospif((float)n / (float)M, &s, &c);
+    ptw[n] = make_float2(c, s);
+    const float h0 = 0.5f - 0.5f * cospif(2.0f * (float)(2 * n) / (float)NFFT);
+    const float h1 = 0.5f - 0.5f * cospif(2.0f * (float)(2 * n + 1) / (float)NFFT);
+    wsyn[n] = make_float2(h0 * (0.5f / (float)M), -h1 * (0.5f / (float)M));
+    hsq[2 * n] = h0 * h0;
+    hsq[2 * n + 1] = h1 * h1;
   }
-  const float2* spec_u = spec + frame_off[u] * F;
-  const float* mask_u = mask + (frame_off[u] * n_src + (long long)src * T) * F;
-  const int grp = tid >> 4, l16 = tid & 15;
-  const float invN = 1.0f / (float)N;
+  for (int e = tid; e < 16 * P; e += NT) {
+    float s, c;
+    sincospif(2.0f * (float)((e % P) * (e / P)) / (float)M, &s, &c);
+    tw[e] = make_float2(c, -s);
+  }
+  __syncthreads();
+  for (int r = tid; r < hop; r += NT) {                        // same ascending-frame order as the general path
+    float s = 0.0f;
+    for (int n = r + ((NFFT - 1 - r) / hop) * hop; n >= 0; n -= hop) s += hsq[n];
+    wfull[r] = s;
+  }
+  p2* scr = scr_all + g * C::SCR;
+  const int n_work = total_tiles * n_src;
 
-  for (int fb = 0; fb < nf; fb += 16) {
-    const int nb = min(16, nf - fb);
-    __syncthreads();                     // regA free (previous batch's scratch reads done); tw ready
-    // stage X = mix_spec * mask for frames [i_lo+fb, +nb) as regA[k*XP + f]
+  int u = 0;
+  for (int work = blockIdx.x; work < n_work; work += gridDim.x) {
+    const int tile = work / n_src, src = work - tile * n_src;
+    if (tile_off[u] > tile) u = 0;                             // (never: work items ascend)
+    {
+      int lo = u, hi = n_utts;
+      while (hi - lo > 1) {
+        const int mid = (lo + hi) >> 1;
+        if (tile_off[mid] <= tile) lo = mid; else hi = mid;
+      }
+      u = lo;
+    }
+    const long long fo = frame_off[u];
+    const int T = (int)(frame_off[u + 1] - fo);
+    const int L = hop * (T - 1);                               // trimmed output length
+    const int j0 = (tile - tile_off[u]) * IST_TILE_T * hop;
+    const int nj = min(IST_TILE_T * hop, L - j0);
+    const int q0 = j0 + NFFT / 2, q1 = q0 + nj - 1;
+    const int i_lo = max(0, (q0 - NFFT + hop) / hop);           // ceil((q0-NFFT+1)/hop)
+    const int i_hi = min(T - 1, q1 / hop);
+    const int nf = i_hi - i_lo + 1;                             // <= 32
+    const float2* spec_u = spec + fo * F;
+    const float* mask_u = mask + (fo * n_src + (long long)src * T) * F;
+
+    __syncthreads();                                           // previous item's frames consumed; tables ready
+    // 1. X = spec * mask -> planes.  word address of (k, frame f): (k*XP + f%16)*2 + f/16
     if (LAYOUT_TF) {
-      for (int e = tid; e < nb * F; e += IST_THREADS) {
+      for (int e = tid; e < nf * F; e += NT) {
         const int f = e / F, k = e - f * F;
-        const long long g = (long long)(i_lo + fb + f) * F + k;
-        const float2 s = spec_u[g];
-        const float m = mask_u[g];
-        regA[k * XP + f] = make_float2(s.x * m, s.y * m);
+        const long long gi = (long long)(i_lo + f) * F + k;
+        const float2 s = spec_u[gi];
+        const float m = mask_u[gi];
+        const int w = (k * XP + (f & 15)) * 2 + (f >> 4);
+        reinterpret_cast<float*>(xre)[w] = s.x * m;
+        reinterpret_cast<float*>(xim)[w] = s.y * m;
       }
     } else {
-      for (int e = tid; e < 16 * F; e += IST_THREADS) {
-        const int k = e >> 4, f = e & 15;
-        if (f < nb) {
-          const long long g = (long long)k * T + (i_lo + fb + f);
-          const float2 s = spec_u[g];
-          const float m = mask_u[g];
-          regA[k * XP + f] = make_float2(s.x * m, s.y * m);
-        }
+      const int w0 = (lane & 15) * 2 + (lane >> 4);
+      const bool ok = lane < nf;
+      const long long base = (long long)i_lo + (ok ? lane : 0);
+      constexpr int NW = NT / 32;
+#pragma unroll 4
+      for (int k = warp; k < F; k += NW) {
+        const long long gi = (long long)k * T + base;
+        const float2 s = ok ? spec_u[gi] : make_float2(0.0f, 0.0f);
+        const float m = ok ? mask_u[gi] : 0.0f;
+        reinterpret_cast<float*>(xre)[k * XP * 2 + w0] = s.x * m;
+        reinterpret_cast<float*>(xim)[k * XP * 2 + w0] = s.y * m;
       }
     }
     __syncthreads();
-    // build conj(Z[k]), Z = E + iO, E = (X[k]+conj(X[N-k]))/2, O = W^-k (X[k]-conj(X[N-k]))/2
-    float2 v[R1];
-    const int fsel = (grp < nb) ? grp : 0;
+    const int warp_g0 = (tid & ~31) / P;
+    const bool warp_live = warp_g0 < nf;
+    c2 v[16];
+    if (warp_live) {
+      // 2. conj(2 Z[k]), k = P*n1 + j
 #pragma unroll
-    for (int n1 = 0; n1 < R1; ++n1) {
-      const int k = 16 * n1 + l16;
-      float2 a = regA[k * XP + fsel], b = regA[(N - k) * XP + fsel];
-      if (k == 0) { a.y = 0.0f; b.y = 0.0f; }                       // irfft ignores Im of DC and Nyquist
-      b = cconj(b);
-      const float2 e = make_float2(0.5f * (a.x + b.x), 0.5f * (a.y + b.y));
-      const float2 d = make_float2(0.5f * (a.x - b.x), 0.5f * (a.y - b.y));
-      const float2 o = cmul(cconj(tw[k]), d);                       // W^-k * d
-      v[n1] = make_float2(e.x - o.y, -(e.y + o.x));                 // conj(e + i*o)
-    }
-    __syncthreads();                     // everyone has read regA -> reuse as FFT scratch
-    float2* scr = regA + grp * SCR;
-    fft_group16<N>(v, scr, tw, l16);
-    if (grp < nb) {
-      float* fr = frames + (fb + grp) * NFFT;
-      for (int n = l16; n < N; n += 16) {
-        const float2 r = scr[n];
-        const float w0 = 0.5f - 0.5f * tw[2 * n].x, w1 = 0.5f - 0.5f * tw[2 * n + 1].x;
-        *reinterpret_cast<float2*>(fr + 2 * n) = make_float2(r.x * invN * w0, -r.y * invN * w1);
+      for (int n1 = 0; n1 < 16; ++n1) {
+        const int k = P * n1 + j;
+        p2 ax = xre[k * XP + g], ay = xim[k * XP + g];
+        p2 bx = xre[(M - k) * XP + g], by = xim[(M - k) * XP + g];
+        if (n1 == 0 && j == 0) {                               // irfft ignores Im of DC and Nyquist
+          ay = 0ull;
+          by = 0ull;
+        }
+        const p2 ex = add2(ax, bx), ey = sub2(ay, by), dx = sub2(ax, bx), dy = add2(ay, by);
+        const float2 w = ptw[k];
+        const c2 o = cmul_s(c2{dx, dy}, w.x, w.y);             // conj(w_k) * 2D
+        v[n1] = {sub2(ex, o.im), neg2(add2(ey, o.re))};        // conj(2E + i o)
       }
     }
-  }
-  __syncthreads();
-  // overlap-add in ascending frame order (as the reference's python loop), normalise, convert
-  const long long obase = wav_off[u] + (long long)src * L + j0;
-  for (int j = tid; j < nj; j += IST_THREADS) {
-    const int q = q0 + j;
-    float y = 0.0f, wss = 0.0f;
-    int i = max(0, (q - NFFT + hop) / hop);
-    const int iend = min(T - 1, q / hop);
-    for (; i <= iend; ++i) {
-      const int n = q - i * hop;
-      y += frames[(i - i_lo) * NFFT + n];
-      const float w = 0.5f - 0.5f * tw[n].x;
-      wss += w * w;
+    __syncthreads();                                           // planes consumed -> exchange buffer + frames
+    if (warp_live) {
+      // 3. forward FFT of conj(2Z)
+      fft16(v);
+#pragma unroll
+      for (int k1 = 1; k1 < 16; ++k1) {
+        const float2 w = tw[k1 * P + j];
+        v[k1] = cmul_s(v[k1], w.x, w.y);
+      }
+      c2 z[NA][P];
+#pragma unroll
+      for (int k1 = 0; k1 < 16; ++k1) scr[k1 * (P + 1) + j] = v[k1].re;
+      __syncwarp();
+#pragma unroll
+      for (int a = 0; a < NA; ++a)
+#pragma unroll
+        for (int n2 = 0; n2 < P; ++n2) z[a][n2].re = scr[(j + P * a) * (P + 1) + n2];
+      __syncwarp();
+#pragma unroll
+      for (int k1 = 0; k1 < 16; ++k1) scr[k1 * (P + 1) + j] = v[k1].im;
+      __syncwarp();
+#pragma unroll
+      for (int a = 0; a < NA; ++a)
+#pragma unroll
+        for (int n2 = 0; n2 < P; ++n2) z[a][n2].im = scr[(j + P * a) * (P + 1) + n2];
+#pragma unroll
+      for (int a = 0; a < NA; ++a) ifft_p<P>(z[a]);            // z[a][k2] = r[(j + P*a) + 16*k2]
+      // 4. synthesis window, frames to shared memory
+      float* fa = frames + g * FP;
+      float* fb = frames + (IST_HALF + g) * FP;
+#pragma unroll
+      for (int a = 0; a < NA; ++a)
+#pragma unroll
+        for (int k2 = 0; k2 < P; ++k2) {
+          const int n = j + P * a + 16 * k2;
+          const float2 w = wsyn[n];
+          float xa, xb, ya, yb;
+          upk(z[a][k2].re, xa, xb);
+          upk(z[a][k2].im, ya, yb);
+          *reinterpret_cast<float2*>(fa + 2 * n) = make_float2(xa * w.x, ya * w.y);
+          *reinterpret_cast<float2*>(fb + 2 * n) = make_float2(xb * w.x, yb * w.y);
+        }
     }
-    if (wss > 1.17549435e-38f) y /= wss;
-    if (OUT_F32) reinterpret_cast<float*>(out)[obase + j] = y;
-    else reinterpret_cast<short*>(out)[obase + j] = (short)(int)(y * 32767.0f);
+    __syncthreads();
+    // 5. overlap-add in ascending frame order, normalise, convert; two samples per thread (hop, L, offsets are even)
+    const long long obase = wav_off[u] + (long long)src * L + j0;
+    for (int jj = 2 * tid; jj < nj; jj += 2 * NT) {
+      const int q = q0 + jj;
+      int i = max(0, (q - NFFT + hop) / hop);
+      const int iend = min(T - 1, q / hop);
+      const bool interior = (q - NFFT + hop >= 0) && (q / hop <= T - 1);   // neither end of the frame range is clipped
+      float y0 = 0.0f, y1 = 0.0f, s0 = 0.0f, s1 = 0.0f;
+      for (; i <= iend; ++i) {
+        const int n = q - i * hop;
+        const float2 fv = *reinterpret_cast<const float2*>(frames + (i - i_lo) * FP + n);
+        y0 += fv.x;
+        y1 += fv.y;
+        if (!interior) {
+          s0 += hsq[n];
+          s1 += hsq[n + 1];
+        }
+      }
+      if (interior) {
+        const int r = q % hop;
+        s0 = wfull[r];
+        s1 = wfull[r + 1];
+      }
+      if (s0 > 1.17549435e-38f) y0 /= s0;
+      if (s1 > 1.17549435e-38f) y1 /= s1;
+      if (OUT_F32) {
+        *reinterpret_cast<float2*>(reinterpret_cast<float*>(out) + obase + jj) = make_float2(y0, y1);
+      } else {
+        short2 o2;
+        o2.x = (short)(int)(y0 * 32767.0f);
+        o2.y = (short)(int)(y1 * 32767.0f);
+        *reinterpret_cast<short2*>(reinterpret_cast<short*>(out) + obase + jj) = o2;
+      }
+    }
   }
 }
 
@@ -125,13 +240,14 @@ template <int NFFT, bool TF, bool F32>
 static int launch_istft(const float2* spec, const float* mask, const long long* frame_off, const long long* wav_off,
                         const int* tile_off, int n_utts, int n_src, int total_tiles, int hop, void* out,
                         cudaStream_t st) {
-  constexpr int N = NFFT / 2, F = N + 1, SCR = (N / 16) * 17;
-  constexpr int REGA = (F * 17 > 16 * SCR) ? F * 17 : 16 * SCR;
-  const size_t smem = (size_t)NFFT * 8 + (size_t)REGA * 8 + (size_t)IST_MAXF * NFFT * 4;
+  using C = IstftCfg<NFFT>;
+  const size_t smem = (size_t)(2 * C::M + 16 * C::P) * 8 + (size_t)NFFT * 4 + (size_t)((hop + 3) & ~3) * 4 + C::REGION;
   auto kern = istft_kernel<NFFT, TF, F32>;
   cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-  kern<<<dim3(total_tiles, n_src), IST_THREADS, smem, st>>>(spec, mask, frame_off, wav_off, tile_off, n_utts, n_src,
-                                                            hop, out);
+  const long long n_work = (long long)total_tiles * n_src;
+  const int resident = 148 * C::CTAS;
+  const int grid = n_work < resident ? (int)n_work : resident;
+  kern<<<grid, C::THREADS, smem, st>>>(spec, mask, frame_off, wav_off, tile_off, n_utts, n_src, total_tiles, hop, out);
   return check_launch("ss_istft_masked");
 }
 
