@@ -84,22 +84,35 @@ __global__ void __launch_bounds__(IstftCfg<NFFT>::THREADS, IstftCfg<NFFT>::CTAS)
   p2* scr = scr_all + g * C::SCR;
   const int n_work = total_tiles * n_src;
 
+  // contiguous range of (tile, source) items per CTA: the utterance cursor only ever advances and its offsets stay
+  // in registers; the sources of a tile are consecutive items, so the second one reads the spectrum from L2
+  const int w_begin = (int)((long long)n_work * blockIdx.x / gridDim.x);
+  const int w_end = (int)((long long)n_work * (blockIdx.x + 1) / gridDim.x);
   int u = 0;
-  for (int work = blockIdx.x; work < n_work; work += gridDim.x) {
-    const int tile = work / n_src, src = work - tile * n_src;
-    if (tile_off[u] > tile) u = 0;                             // (never: work items ascend)
-    {
-      int lo = u, hi = n_utts;
-      while (hi - lo > 1) {
-        const int mid = (lo + hi) >> 1;
-        if (tile_off[mid] <= tile) lo = mid; else hi = mid;
-      }
-      u = lo;
+  if (w_begin < w_end) {
+    const int t_first = w_begin / n_src;
+    int lo = 0, hi = n_utts;
+    while (hi - lo > 1) {
+      const int mid = (lo + hi) >> 1;
+      if (tile_off[mid] <= t_first) lo = mid; else hi = mid;
     }
-    const long long fo = frame_off[u];
-    const int T = (int)(frame_off[u + 1] - fo);
+    u = lo;
+  }
+  int u_tlo = tile_off[u], u_thi = tile_off[u + 1];
+  long long fo = frame_off[u], wo = wav_off[u];
+  int T = (int)(frame_off[u + 1] - fo);
+  for (int work = w_begin; work < w_end; ++work) {
+    const int tile = work / n_src, src = work - tile * n_src;
+    while (tile >= u_thi) {
+      ++u;
+      u_tlo = u_thi;
+      u_thi = tile_off[u + 1];
+      fo = frame_off[u];
+      wo = wav_off[u];
+      T = (int)(frame_off[u + 1] - fo);
+    }
     const int L = hop * (T - 1);                               // trimmed output length
-    const int j0 = (tile - tile_off[u]) * IST_TILE_T * hop;
+    const int j0 = (tile - u_tlo) * IST_TILE_T * hop;
     const int nj = min(IST_TILE_T * hop, L - j0);
     const int q0 = j0 + NFFT / 2, q1 = q0 + nj - 1;
     const int i_lo = max(0, (q0 - NFFT + hop) / hop);           // ceil((q0-NFFT+1)/hop)
@@ -124,14 +137,32 @@ __global__ void __launch_bounds__(IstftCfg<NFFT>::THREADS, IstftCfg<NFFT>::CTAS)
       const int w0 = (lane & 15) * 2 + (lane >> 4);
       const bool ok = lane < nf;
       const long long base = (long long)i_lo + (ok ? lane : 0);
-      constexpr int NW = NT / 32;
-#pragma unroll 4
-      for (int k = warp; k < F; k += NW) {
-        const long long gi = (long long)k * T + base;
-        const float2 s = ok ? spec_u[gi] : make_float2(0.0f, 0.0f);
-        const float m = ok ? mask_u[gi] : 0.0f;
-        reinterpret_cast<float*>(xre)[k * XP * 2 + w0] = s.x * m;
-        reinterpret_cast<float*>(xim)[k * XP * 2 + w0] = s.y * m;
+      constexpr int NW = NT / 32, RB = 8;                      // 8 rows = 16 loads in flight per thread
+      const float2* sp = spec_u + (long long)warp * T + base;
+      const float* mp = mask_u + (long long)warp * T + base;
+      const long long rstride = (long long)NW * T;
+      float* pre = reinterpret_cast<float*>(xre) + warp * XP * 2 + w0;
+      float* pim = reinterpret_cast<float*>(xim) + warp * XP * 2 + w0;
+      for (int k0 = warp; k0 < F; k0 += NW * RB) {
+        float2 sv[RB];
+        float mv[RB];
+#pragma unroll
+        for (int r = 0; r < RB; ++r) {
+          const bool in = ok && k0 + r * NW < F;
+          sv[r] = in ? sp[r * rstride] : make_float2(0.0f, 0.0f);
+          mv[r] = in ? mp[r * rstride] : 0.0f;
+        }
+#pragma unroll
+        for (int r = 0; r < RB; ++r) {
+          if (k0 + r * NW < F) {
+            pre[r * NW * XP * 2] = sv[r].x * mv[r];
+            pim[r * NW * XP * 2] = sv[r].y * mv[r];
+          }
+        }
+        sp += RB * rstride;
+        mp += RB * rstride;
+        pre += RB * NW * XP * 2;
+        pim += RB * NW * XP * 2;
       }
     }
     __syncthreads();
@@ -200,27 +231,47 @@ __global__ void __launch_bounds__(IstftCfg<NFFT>::THREADS, IstftCfg<NFFT>::CTAS)
     }
     __syncthreads();
     // 5. overlap-add in ascending frame order, normalise, convert; two samples per thread (hop, L, offsets are even)
-    const long long obase = wav_off[u] + (long long)src * L + j0;
+    const long long obase = wo + (long long)src * L + j0;
+    // q = hb*hop + r walks forward by 2*NT samples per iteration: one division per thread and tile
+    int hb = (q0 + 2 * tid) / hop, r = (q0 + 2 * tid) - hb * hop;
+    const int dstep = (2 * NT) / hop, rstep = (2 * NT) - dstep * hop;
+    const int nov = (NFFT - 1) / hop;                           // frames hb-nov .. hb can reach sample q
     for (int jj = 2 * tid; jj < nj; jj += 2 * NT) {
-      const int q = q0 + jj;
-      int i = max(0, (q - NFFT + hop) / hop);
-      const int iend = min(T - 1, q / hop);
-      const bool interior = (q - NFFT + hop >= 0) && (q / hop <= T - 1);   // neither end of the frame range is clipped
+      int i = hb - nov, n = r + nov * hop;                      // n = q - i*hop
+      if (n >= NFFT) {                                          // (hop does not divide NFFT: first frame may miss)
+        ++i;
+        n -= hop;
+      }
+      const bool interior = i >= 0 && hb <= T - 1;              // neither end of the frame range is clipped
+      const int iend = min(T - 1, hb);
+      if (i < 0) {
+        n += i * hop;
+        i = 0;
+      }
       float y0 = 0.0f, y1 = 0.0f, s0 = 0.0f, s1 = 0.0f;
-      for (; i <= iend; ++i) {
-        const int n = q - i * hop;
-        const float2 fv = *reinterpret_cast<const float2*>(frames + (i - i_lo) * FP + n);
-        y0 += fv.x;
-        y1 += fv.y;
-        if (!interior) {
+      const float* fp = frames + (i - i_lo) * FP + n;
+      if (interior) {
+        for (; i <= iend; ++i, fp += FP - hop) {
+          const float2 fv = *reinterpret_cast<const float2*>(fp);
+          y0 += fv.x;
+          y1 += fv.y;
+        }
+        s0 = wfull[r];
+        s1 = wfull[r + 1];
+      } else {
+        for (; i <= iend; ++i, fp += FP - hop, n -= hop) {
+          const float2 fv = *reinterpret_cast<const float2*>(fp);
+          y0 += fv.x;
+          y1 += fv.y;
           s0 += hsq[n];
           s1 += hsq[n + 1];
         }
       }
-      if (interior) {
-        const int r = q % hop;
-        s0 = wfull[r];
-        s1 = wfull[r + 1];
+      hb += dstep;
+      r += rstep;
+      if (r >= hop) {
+        r -= hop;
+        ++hb;
       }
       if (s0 > 1.17549435e-38f) y0 /= s0;
       if (s1 > 1.17549435e-38f) y1 /= s1;
