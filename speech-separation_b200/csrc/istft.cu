@@ -26,10 +26,11 @@ template <int NFFT>
 struct IstftCfg {
   static constexpr int M = NFFT / 2, F = M + 1, P = M / 16, NA = 16 / P, G = IST_HALF;
   static constexpr int THREADS = G * P, CTAS = 512 / THREADS;
-  static constexpr int XP = P == 8 ? 18 : 17;                      // p2 per row of an X plane (conflict-free both ways)
+  static constexpr int SP = 32 + (P == 8 ? 2 : 1);                 // float2 per row of the staged spectrum (32 frames + skew)
+  static constexpr int MP = 32 + (P == 8 ? 4 : 2);                 // floats per row of the staged mask
   static constexpr int SCR = 16 * (P + 1) + (P == 8 ? 8 : 0);      // p2 per frame-pair group of the FFT exchange
   static constexpr int FP = NFFT + 16;                             // floats per synthesised frame (bank skew)
-  static constexpr int PLANES = 2 * F * XP * 8;                    // bytes
+  static constexpr int PLANES = F * SP * 8 + F * MP * 4;           // bytes: staged spectrum + mask
   static constexpr int WORK = G * SCR * 8 + 2 * IST_HALF * FP * 4; // bytes: exchange + frames (the planes alias it)
   static constexpr int REGION = PLANES > WORK ? PLANES : WORK;
 };
@@ -45,16 +46,17 @@ __global__ void __launch_bounds__(IstftCfg<NFFT>::THREADS, IstftCfg<NFFT>::CTAS)
                  const long long* __restrict__ wav_off, const int* __restrict__ tile_off, int n_utts, int n_src,
                  int total_tiles, int hop, void* __restrict__ out) {
   using C = IstftCfg<NFFT>;
-  constexpr int M = C::M, F = C::F, P = C::P, NA = C::NA, G = C::G, NT = C::THREADS, XP = C::XP, FP = C::FP;
+  constexpr int M = C::M, F = C::F, P = C::P, NA = C::NA, G = C::G, NT = C::THREADS, SP = C::SP, MP = C::MP, FP = C::FP;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   float2* ptw = reinterpret_cast<float2*>(smem_raw);           // [M] exp(+i pi k / M) = conj(w_k)
   float2* tw = ptw + M;                                        // [16][P] W_M^(j*k1)
   float2* wsyn = tw + 16 * P;                                  // [M] (hann[2n], -hann[2n+1]) / 2M
   float* hsq = reinterpret_cast<float*>(wsyn + M);             // [NFFT] hann^2
   float* wfull = hsq + NFFT;                                   // [hop] window-sum-square of the interior, by q mod hop
-  unsigned char* region = reinterpret_cast<unsigned char*>(wfull + ((hop + 3) & ~3));
-  p2* xre = reinterpret_cast<p2*>(region);                     // [F][XP]
-  p2* xim = xre + F * XP;
+  float* rfull = wfull + ((hop + 3) & ~3);                     // [hop] its correctly rounded reciprocal
+  unsigned char* region = reinterpret_cast<unsigned char*>(rfull + ((hop + 3) & ~3));
+  float2* rs = reinterpret_cast<float2*>(region);              // [F][SP] mixture spectrum of the tile's frames
+  float* rm = reinterpret_cast<float*>(rs + F * SP);           // [F][MP] mask
   p2* scr_all = reinterpret_cast<p2*>(region);                 // [G][SCR]   (after the planes are consumed)
   float* frames = reinterpret_cast<float*>(scr_all + G * C::SCR);          // [32][FP]
 
@@ -79,7 +81,9 @@ __global__ void __launch_bounds__(IstftCfg<NFFT>::THREADS, IstftCfg<NFFT>::CTAS)
   for (int r = tid; r < hop; r += NT) {                        // same ascending-frame order as the general path
     float s = 0.0f;
     for (int n = r + ((NFFT - 1 - r) / hop) * hop; n >= 0; n -= hop) s += hsq[n];
-    wfull[r] = s;
+    const bool tiny = !(s > 1.17549435e-38f);                   // the reference leaves such samples undivided
+    wfull[r] = tiny ? 1.0f : s;
+    rfull[r] = tiny ? 1.0f : 1.0f / s;
   }
   p2* scr = scr_all + g * C::SCR;
   const int n_work = total_tiles * n_src;
@@ -122,48 +126,31 @@ __global__ void __launch_bounds__(IstftCfg<NFFT>::THREADS, IstftCfg<NFFT>::CTAS)
     const float* mask_u = mask + (fo * n_src + (long long)src * T) * F;
 
     __syncthreads();                                           // previous item's frames consumed; tables ready
-    // 1. X = spec * mask -> planes.  word address of (k, frame f): (k*XP + f%16)*2 + f/16
-    if (LAYOUT_TF) {
-      for (int e = tid; e < nf * F; e += NT) {
-        const int f = e / F, k = e - f * F;
-        const long long gi = (long long)(i_lo + f) * F + k;
-        const float2 s = spec_u[gi];
-        const float m = mask_u[gi];
-        const int w = (k * XP + (f & 15)) * 2 + (f >> 4);
-        reinterpret_cast<float*>(xre)[w] = s.x * m;
-        reinterpret_cast<float*>(xim)[w] = s.y * m;
-      }
-    } else {
-      const int w0 = (lane & 15) * 2 + (lane >> 4);
-      const bool ok = lane < nf;
-      const long long base = (long long)i_lo + (ok ? lane : 0);
-      constexpr int NW = NT / 32, RB = 8;                      // 8 rows = 16 loads in flight per thread
-      const float2* sp = spec_u + (long long)warp * T + base;
-      const float* mp = mask_u + (long long)warp * T + base;
-      const long long rstride = (long long)NW * T;
-      float* pre = reinterpret_cast<float*>(xre) + warp * XP * 2 + w0;
-      float* pim = reinterpret_cast<float*>(xim) + warp * XP * 2 + w0;
-      for (int k0 = warp; k0 < F; k0 += NW * RB) {
-        float2 sv[RB];
-        float mv[RB];
-#pragma unroll
-        for (int r = 0; r < RB; ++r) {
-          const bool in = ok && k0 + r * NW < F;
-          sv[r] = in ? sp[r * rstride] : make_float2(0.0f, 0.0f);
-          mv[r] = in ? mp[r * rstride] : 0.0f;
+    // 1. spectrum and mask of the tile's frames -> shared memory by cp.async: every load of the item is in flight at
+    //    once and no register is held (the other CTA of the SM computes meanwhile)
+    {
+      const uint32_t rs_s = smem_u32(rs), rm_s = smem_u32(rm);
+      if (LAYOUT_TF) {
+        for (int e = tid; e < nf * F; e += NT) {
+          const int f = e / F, k = e - f * F;
+          const long long gi = (long long)(i_lo + f) * F + k;
+          cp_async8(rs_s + (k * SP + f) * 8, spec_u + gi);
+          cp_async4(rm_s + (k * MP + f) * 4, mask_u + gi);
         }
-#pragma unroll
-        for (int r = 0; r < RB; ++r) {
-          if (k0 + r * NW < F) {
-            pre[r * NW * XP * 2] = sv[r].x * mv[r];
-            pim[r * NW * XP * 2] = sv[r].y * mv[r];
-          }
+      } else if (lane < nf) {
+        constexpr int NW = NT / 32;
+        const float2* sp = spec_u + (long long)warp * T + i_lo + lane;
+        const float* mp = mask_u + (long long)warp * T + i_lo + lane;
+        const long long rstride = (long long)NW * T;
+        uint32_t ds = rs_s + (warp * SP + lane) * 8, dm = rm_s + (warp * MP + lane) * 4;
+#pragma unroll 4
+        for (int k = warp; k < F; k += NW, sp += rstride, mp += rstride, ds += NW * SP * 8, dm += NW * MP * 4) {
+          cp_async8(ds, sp);
+          cp_async4(dm, mp);
         }
-        sp += RB * rstride;
-        mp += RB * rstride;
-        pre += RB * NW * XP * 2;
-        pim += RB * NW * XP * 2;
       }
+      cp_async_commit();
+      cp_async_wait_all();
     }
     __syncthreads();
     const int warp_g0 = (tid & ~31) / P;
@@ -174,8 +161,13 @@ __global__ void __launch_bounds__(IstftCfg<NFFT>::THREADS, IstftCfg<NFFT>::CTAS)
 #pragma unroll
       for (int n1 = 0; n1 < 16; ++n1) {
         const int k = P * n1 + j;
-        p2 ax = xre[k * XP + g], ay = xim[k * XP + g];
-        p2 bx = xre[(M - k) * XP + g], by = xim[(M - k) * XP + g];
+        // X = spec * mask of frames g (lo) and 16+g (hi), rows k and M-k
+        const float2 sa = rs[k * SP + g], sb = rs[k * SP + IST_HALF + g];
+        const float ma = rm[k * MP + g], mb = rm[k * MP + IST_HALF + g];
+        const float2 ta = rs[(M - k) * SP + g], tb = rs[(M - k) * SP + IST_HALF + g];
+        const float na = rm[(M - k) * MP + g], nb = rm[(M - k) * MP + IST_HALF + g];
+        p2 ax = pk(sa.x * ma, sb.x * mb), ay = pk(sa.y * ma, sb.y * mb);
+        p2 bx = pk(ta.x * na, tb.x * nb), by = pk(ta.y * na, tb.y * nb);
         if (n1 == 0 && j == 0) {                               // irfft ignores Im of DC and Nyquist
           ay = 0ull;
           by = 0ull;
@@ -236,6 +228,7 @@ __global__ void __launch_bounds__(IstftCfg<NFFT>::THREADS, IstftCfg<NFFT>::CTAS)
     int hb = (q0 + 2 * tid) / hop, r = (q0 + 2 * tid) - hb * hop;
     const int dstep = (2 * NT) / hop, rstep = (2 * NT) - dstep * hop;
     const int nov = (NFFT - 1) / hop;                           // frames hb-nov .. hb can reach sample q
+    const bool hop4 = 4 * hop == NFFT;
     for (int jj = 2 * tid; jj < nj; jj += 2 * NT) {
       int i = hb - nov, n = r + nov * hop;                      // n = q - i*hop
       if (n >= NFFT) {                                          // (hop does not divide NFFT: first frame may miss)
@@ -248,17 +241,31 @@ __global__ void __launch_bounds__(IstftCfg<NFFT>::THREADS, IstftCfg<NFFT>::CTAS)
         n += i * hop;
         i = 0;
       }
-      float y0 = 0.0f, y1 = 0.0f, s0 = 0.0f, s1 = 0.0f;
+      float y0 = 0.0f, y1 = 0.0f;
       const float* fp = frames + (i - i_lo) * FP + n;
       if (interior) {
-        for (; i <= iend; ++i, fp += FP - hop) {
-          const float2 fv = *reinterpret_cast<const float2*>(fp);
-          y0 += fv.x;
-          y1 += fv.y;
+        if (hop4) {
+          const float2 f0 = *reinterpret_cast<const float2*>(fp);
+          const float2 f1 = *reinterpret_cast<const float2*>(fp + (FP - hop));
+          const float2 f2 = *reinterpret_cast<const float2*>(fp + 2 * (FP - hop));
+          const float2 f3 = *reinterpret_cast<const float2*>(fp + 3 * (FP - hop));
+          y0 = ((f0.x + f1.x) + f2.x) + f3.x;
+          y1 = ((f0.y + f1.y) + f2.y) + f3.y;
+        } else {
+          for (; i <= iend; ++i, fp += FP - hop) {
+            const float2 fv = *reinterpret_cast<const float2*>(fp);
+            y0 += fv.x;
+            y1 += fv.y;
+          }
         }
-        s0 = wfull[r];
-        s1 = wfull[r + 1];
+        // y / s from the tabulated s and 1/s: quotient estimate plus one residual correction (the division's own
+        // fast path without its reciprocal refinement)
+        const float2 sw = *reinterpret_cast<const float2*>(wfull + r), rc = *reinterpret_cast<const float2*>(rfull + r);
+        const float e0 = y0 * rc.x, e1 = y1 * rc.y;
+        y0 = fmaf(fmaf(-e0, sw.x, y0), rc.x, e0);
+        y1 = fmaf(fmaf(-e1, sw.y, y1), rc.y, e1);
       } else {
+        float s0 = 0.0f, s1 = 0.0f;
         for (; i <= iend; ++i, fp += FP - hop, n -= hop) {
           const float2 fv = *reinterpret_cast<const float2*>(fp);
           y0 += fv.x;
@@ -266,6 +273,8 @@ __global__ void __launch_bounds__(IstftCfg<NFFT>::THREADS, IstftCfg<NFFT>::CTAS)
           s0 += hsq[n];
           s1 += hsq[n + 1];
         }
+        if (s0 > 1.17549435e-38f) y0 /= s0;
+        if (s1 > 1.17549435e-38f) y1 /= s1;
       }
       hb += dstep;
       r += rstep;
@@ -273,8 +282,6 @@ __global__ void __launch_bounds__(IstftCfg<NFFT>::THREADS, IstftCfg<NFFT>::CTAS)
         r -= hop;
         ++hb;
       }
-      if (s0 > 1.17549435e-38f) y0 /= s0;
-      if (s1 > 1.17549435e-38f) y1 /= s1;
       if (OUT_F32) {
         *reinterpret_cast<float2*>(reinterpret_cast<float*>(out) + obase + jj) = make_float2(y0, y1);
       } else {
@@ -292,7 +299,7 @@ static int launch_istft(const float2* spec, const float* mask, const long long* 
                         const int* tile_off, int n_utts, int n_src, int total_tiles, int hop, void* out,
                         cudaStream_t st) {
   using C = IstftCfg<NFFT>;
-  const size_t smem = (size_t)(2 * C::M + 16 * C::P) * 8 + (size_t)NFFT * 4 + (size_t)((hop + 3) & ~3) * 4 + C::REGION;
+  const size_t smem = (size_t)(2 * C::M + 16 * C::P) * 8 + (size_t)NFFT * 4 + (size_t)((hop + 3) & ~3) * 8 + C::REGION;
   auto kern = istft_kernel<NFFT, TF, F32>;
   cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   const long long n_work = (long long)total_tiles * n_src;
