@@ -262,7 +262,13 @@ def run_train(args, rank, local, world):
         sink["loss"], _ = trainer.step(dev[i % N_BATCHES])
 
     def step_e2e(i):
-        loss, norm = trainer.step(host[i % N_BATCHES])
+        # the user-facing loop: the copy of batch i+1 (pinned host memory) is started before step i is enqueued, so it
+        # overlaps step i's kernels; every step still copies one full batch H2D and reads its loss back
+        staged = sink.pop("staged", None)
+        if staged is None or sink.get("staged_i") != i:
+            staged = trainer.prefetch(host[i % N_BATCHES])
+        sink["staged"], sink["staged_i"] = trainer.prefetch(host[(i + 1) % N_BATCHES]), i + 1
+        loss, norm = trainer.step(staged)
         sink["host_loss"] = (float(loss), float(norm))          # D2H read of the step's result, every step
 
     K, W = args.steps, args.warmup

@@ -71,6 +71,11 @@ def allreduce_buckets(flat, buckets, group=None, tags=BUCKET_ORDER):
     return works
 
 
+class _Staged(dict):
+    """A collated batch whose PackedSequence data already travels to (or sits on) the device; .event marks the copy."""
+    event = None
+
+
 class Trainer:
     """Owns the flat parameter / gradient / Adam buckets of one SepDNN and runs whole train steps."""
 
@@ -110,6 +115,7 @@ class Trainer:
         self.norm = torch.zeros(1, dtype=torch.float32, device=dev)
         self.steps = 0
         self.comm = torch.cuda.Stream(device=dev) if self.world > 1 else None
+        self.copy_stream = None
         self._works = []
 
     # -- gradient exchange: called by the engine as each bucket's last kernel has been enqueued --
@@ -124,8 +130,33 @@ class Trainer:
         with torch.cuda.stream(self.comm):
             dist.all_reduce(self.flat_g[o:o + n], op=dist.ReduceOp.SUM, group=self.group)
 
+    def prefetch(self, batch_sample):
+        """Start the host->device copy of a collated batch (pinned PackedSequences) on a copy stream and return the
+        staged batch; pass it to step() later.  Lets the copy of batch i+1 overlap the kernels of batch i, the usual
+        DataLoader(pin_memory=True) + non_blocking pattern.  Batches that are not plain dicts are returned as is."""
+        if not isinstance(batch_sample, dict):
+            return batch_sample
+        from torch.nn.utils.rnn import PackedSequence
+        if self.copy_stream is None:
+            self.copy_stream = torch.cuda.Stream()
+        main = torch.cuda.current_stream()
+        staged = _Staged()
+        with torch.cuda.stream(self.copy_stream):
+            for k, v in batch_sample.items():
+                if isinstance(v, PackedSequence):
+                    data = v.data.to(device=self.flat_p.device, non_blocking=True)
+                    data.record_stream(main)
+                    staged[k] = PackedSequence(data, v.batch_sizes)
+                else:
+                    staged[k] = v
+            staged.event = torch.cuda.Event()
+            staged.event.record(self.copy_stream)
+        return staged
+
     def step(self, batch_sample):
         """One optimisation step on a collated batch.  Returns device scalars (loss, norm) of this rank's shard."""
+        if getattr(batch_sample, "event", None) is not None:
+            torch.cuda.current_stream().wait_event(batch_sample.event)
         loss, norm = self.arch.loss_and_grads(self.model, batch_sample, self.grads, hook=self._bucket_ready,
                                               hidden=None if self.host_rng else self._device_hidden)
         loss, norm = loss.clone(), norm.clone()

@@ -42,6 +42,29 @@ def test_trainer_matches_torch_clip_adam():
         assert torch.allclose(getattr(model_a.bn, k), getattr(model_b.bn, k), atol=1e-6)
 
 
+def test_prefetched_batch_gives_the_same_step():
+    """Trainer.prefetch (H2D on a copy stream, overlapping the previous step) must not change the arithmetic."""
+    from torch.nn.utils.rnn import PackedSequence
+    z, case = common.load_golden("upit_s2_f129")
+    batch, _, _ = _batch(case)
+    pinned = {k: PackedSequence(v.data.pin_memory(), v.batch_sizes) for k, v in batch.items()}
+    model_a = _model(case)
+    model_b = copy.deepcopy(model_a)
+    tr_a = train.Trainer(model_a, uPIT, host_rng=True)
+    tr_b = train.Trainer(model_b, uPIT, host_rng=True)
+    staged = tr_b.prefetch(pinned)
+    for it in range(3):
+        torch.manual_seed(7 + it)
+        la, _ = tr_a.step(batch)
+        nxt = tr_b.prefetch(pinned)                       # copy of the next batch flies during this step
+        torch.manual_seed(7 + it)
+        lb, _ = tr_b.step(staged)
+        staged = nxt
+        assert float(la) == float(lb), it
+    for (k, pa), (_, pb) in zip(model_a.named_parameters(), model_b.named_parameters()):
+        assert torch.equal(pa.detach(), pb.detach()), k
+
+
 def test_clip_adam_kernels_unaligned_sizes():
     from ssb200._lib import LL, call, lib, stream_ptr
     import ctypes
