@@ -127,8 +127,7 @@ lstm_bwd_ks_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
         KS_STAMP(0);
         while (ld_acquire(counter) < need) {
         }
-        KS_STAMP(1);
-        fence_proxy_async();
+        KS_STAMP(1);                                           // (proxy fence: writer side, before the CTA barrier)
 #pragma unroll
         for (int i = 0; i < KS_MAXCH; ++i) {
           if (i < nch) {
@@ -286,6 +285,7 @@ lstm_bwd_ks_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
       cptr += rstep * (2LL * H);
       dptr += rstep * (2LL * H);
       optr += rstep * (8LL * H);
+      fence_proxy_async();                                     // this thread's dG stores -> the consumers' TMA reads
       if (threadIdx.x == 64) KS_STAMP(7);
       asm volatile("bar.sync 1, %0;" ::"n"(32 * KS_EPI_WARPS) : "memory");
       if (threadIdx.x == 64) {

@@ -82,7 +82,8 @@ lstm_fwd_kernel(const __grid_constant__ CUtensorMap tmW, LstmFwdParams p) {
         while (ld_acquire(counter) < need) {
         }
         LF_STAMP(1);
-        fence_proxy_async();
+        // (the generic->async proxy fence sits on the writer side, in publish(): there it overlaps the other
+        // threads' stores instead of adding ~1000 cycles between the acquire and the first copy)
         const __nv_bfloat16* src = p.hbuf + (((long long)(cta % p.REP) * 2 + (s & 1)) * 2 + dir) * PKC * blk;
 #pragma unroll
         for (int i = 0; i < PKC; ++i, ++it) {
@@ -161,6 +162,7 @@ lstm_fwd_kernel(const __grid_constant__ CUtensorMap tmW, LstmFwdParams p) {
       }
       // CTA barrier, then ONE thread releases at gpu scope (cumulative over the other threads' stores, the
       // cooperative-groups grid.sync pattern) and orders them against the consumers' async-proxy reads.
+      fence_proxy_async();                                     // writer side: this thread's h stores -> async-proxy readers
       if (!FAST && threadIdx.x == 0 && p.dbg && blockIdx.x == 0) p.dbg[dbg_s * 32 + 20] = clock64();
       asm volatile("bar.sync 1, %0;" ::"n"(32 * LF_EPI_WARPS) : "memory");
       if (threadIdx.x == 0) {

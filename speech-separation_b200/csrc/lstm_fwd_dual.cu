@@ -94,7 +94,6 @@ lstm_fwd_dual_kernel(const __grid_constant__ CUtensorMap tmW, LstmFwdParams p) {
           while (ld_acquire(counter) < need) {
           }
           LD_STAMP(1);
-          fence_proxy_async();
           const __nv_bfloat16* src = p.hbuf + ((((long long)(s & 1)) * 2 + dir) * 2 + ctx) * LD_KC * blk;
 #pragma unroll
           for (int i = 0; i < LD_KC; ++i) {
@@ -167,6 +166,7 @@ lstm_fwd_dual_kernel(const __grid_constant__ CUtensorMap tmW, LstmFwdParams p) {
         *reinterpret_cast<uint2*>(dst) = *reinterpret_cast<uint2*>(hi);
         *reinterpret_cast<uint2*>(dst + 32 * 64) = *reinterpret_cast<uint2*>(lo);
       }
+      fence_proxy_async();                                     // writer side of the generic -> async proxy hand-over
       // context barrier, then ONE thread releases at gpu scope (cumulative over the other threads' stores)
       asm volatile("bar.sync %0, %1;" ::"r"(bar0), "n"(LD_CTX_THREADS) : "memory");
       if (leader) {
