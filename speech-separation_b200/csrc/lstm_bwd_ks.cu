@@ -67,6 +67,16 @@ __device__ __forceinline__ bool mbar_try_wait_cluster(uint64_t* bar, uint32_t pa
   return ok != 0;
 }
 
+// all-CTA skew probe (DBG only): globaltimer of 4 events for steps 100..115 behind the per-step rows of CTA 0
+#define KS_GSTAMP(ev)                                                                                              \
+  do {                                                                                                             \
+    if (DBG && s >= 100 && s < 116) {                                                                              \
+      unsigned long long gt_;                                                                                      \
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt_));                                                      \
+      p.dbg[(long long)(p.T + 2) * 32 + ((long long)blockIdx.x * 16 + (s - 100)) * 4 + (ev)] = (long long)gt_;    \
+    }                                                                                                              \
+  } while (0)
+
 #define KS_STAMP(slot)                                                 \
   do {                                                                 \
     if (DBG && blockIdx.x == 0) p.dbg[s * 32 + (slot)] = clock64();    \
@@ -216,6 +226,7 @@ lstm_bwd_ks_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
         if (warp == 2) mbar_wait(accum_full, (s - 1) & 1);     // one warp polls, the others sleep on a hardware barrier
         asm volatile("bar.sync 2, %0;" ::"n"(32 * KS_EPI_WARPS) : "memory");
         if (threadIdx.x == 64) KS_STAMP(4);
+        if (threadIdx.x == 64) KS_GSTAMP(0);
         tc_fence_after();
         float v[16], e[16];
         tmem_ld16(trow + 16 * dst, v);                         // x W_hi columns of the 16 units peer `dst` finalises
@@ -237,6 +248,7 @@ lstm_bwd_ks_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
         while (!mbar_try_wait_cluster(rfull, (s - 1) & 1)) {
         }
         if (threadIdx.x == 64) KS_STAMP(6);
+        if (threadIdx.x == 64) KS_GSTAMP(1);
         const float* rb = rbuf + fb * 16 + (((u2 >> 1) ^ fsw) * 4) + (u2 & 1) * 2;
 #pragma unroll
         for (int r = 0; r < KS_CL; ++r) {
@@ -287,11 +299,13 @@ lstm_bwd_ks_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
       optr += rstep * (8LL * H);
       fence_proxy_async();                                     // this thread's dG stores -> the consumers' TMA reads
       if (threadIdx.x == 64) KS_STAMP(7);
+      if (threadIdx.x == 64) KS_GSTAMP(2);
       asm volatile("bar.sync 1, %0;" ::"n"(32 * KS_EPI_WARPS) : "memory");
       if (threadIdx.x == 64) {
         KS_STAMP(8);
         red_release_add(counter, 1u);     // cumulative over the CTA's stores ordered before the bar.sync
         KS_STAMP(9);
+        KS_GSTAMP(3);
       }
     }
     if (row_ok && p.want_d0) {

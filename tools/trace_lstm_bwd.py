@@ -15,13 +15,15 @@ for _ in range(2):
     loss, _ = uPIT.compute_loss(model, 0, batch)
     loss.backward()
 loss, _ = uPIT.compute_loss(model, 0, batch)
-dbg = torch.zeros((T + 2) * 32, dtype=torch.int64, device="cuda")
+dbg = torch.zeros((T + 2) * 32 + 80 * 16 * 4, dtype=torch.int64, device="cuda")
 torch.cuda.synchronize()
 _lib.call("lstm_debug", dbg)
 loss.backward()
 torch.cuda.synchronize()
 _lib.call("lstm_debug", None)
-d = dbg.cpu().numpy().reshape(T + 2, 32)
+allv = dbg.cpu().numpy()
+d = allv[:(T + 2) * 32].reshape(T + 2, 32)
+g = allv[(T + 2) * 32:].reshape(80, 16, 4)
 seg = d[50:350]
 print("cycles/step %.0f" % np.diff(d[50:350, 1]).mean())
 def m(a, b): return (seg[:, b] - seg[:, a]).mean()
@@ -35,3 +37,15 @@ print("sent->peers' partials landed %.0f" % m(5, 6))
 print("landed->math+dG stored %.0f" % m(6, 7))
 print("bar %.0f ; fence+release %.0f" % (m(7, 8), m(8, 9)))
 print("published->next poll_done %.0f" % (seg[1:, 1] - seg[:-1, 9]).mean())
+
+# all-CTA skew (globaltimer ns) at step 108 of the last launch, relative to the earliest "accum seen"
+st = 8
+base = g[:, st, 0].min()
+print("per CTA (dir,cluster,rank): accum_seen / partials_landed / before_bar / released  [ns rel.]")
+for cta in range(80):
+    if cta % 4 == 0 or cta in (37, 38, 39, 77, 78, 79):
+        print(cta, (cta // 40, (cta % 40) // 4, cta % 4), [int(x - base) for x in g[cta, st]])
+print("released: min %d max %d ; step period %.0f ns" % ((g[:, st, 3] - base).min(), (g[:, st, 3] - base).max(), np.diff(g[0, :, 3]).mean()))
+for dname, sl in (("dir0", slice(0, 40)), ("dir1", slice(40, 80))):
+    r = g[sl, st, 3] - base
+    print(dname, "released spread", int(r.min()), int(r.max()), "slowest cta", int(np.argmax(r)) + sl.start, "accum_seen spread", int((g[sl, st, 0] - base).min()), int((g[sl, st, 0] - base).max()))
