@@ -74,7 +74,7 @@ int main() {
   long long* out; cudaMalloc(&out, 160 * 8);
   const int smem = NS * CHUNK + 32 * 1024 + 1024;
   cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-  for (int with_mma : {7, 15, 31, 63}) for (int N : {96, 32}) for (int same : {1}) for (int ctas : {1, 100}) {
+  for (int with_mma : {1, 3, 5, 7, 15, 31}) for (int N : {96, 128}) for (int same : {1}) for (int ctas : {100}) {
     if (!with_mma && N != 96) continue;
     long long h[160];
     for (int rep = 0; rep < 2; ++rep) {

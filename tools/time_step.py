@@ -44,7 +44,12 @@ def timed_call(name, *a):
     e0.record()
     r = orig_call(name, *a)
     e1.record()
-    records.setdefault(name, []).append((e0, e1))
+    key = name
+    if name == "gemm_sb16":
+        key = "gemm_sb16 M=%d N=%d K=%d" % (a[8], a[9], a[10])
+    elif name == "gemm_sb16_x2":
+        key = "gemm_sb16_x2 M=%d N=%d K=%d" % (a[12], a[13], a[14])
+    records.setdefault(key, []).append((e0, e1))
     return r
 
 
@@ -64,5 +69,10 @@ tot = 0.0
 for k, v in records.items():
     ms = sum(a.elapsed_time(b) for a, b in v) / args.iters
     tot += ms
-    print("%-16s calls/step %3d   ms/step %8.3f" % (k, len(v) // args.iters, ms))
+    extra = ""
+    if k.startswith("gemm"):
+        M_, N_, K_ = (int(x.split("=")[1]) for x in k.split()[1:4])
+        fl = 2.0 * M_ * N_ * K_ * (2 if "x2" in k else 1) * (len(v) // args.iters)
+        extra = "  %6.1f TF/s algorithmic, %6.1f issued" % (fl / ms / 1e9, 3 * fl / ms / 1e9)
+    print("%-40s calls/step %3d   ms/step %8.3f%s" % (k, len(v) // args.iters, ms, extra))
 print("sum of kernels ms/step %.3f ; audio-s/step %.1f" % (tot, sum(lens) * 128 / 8000.0))
