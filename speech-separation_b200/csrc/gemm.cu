@@ -12,7 +12,9 @@ namespace ssb {
 constexpr int GB_M = 128, GB_N = 128, GB_K = 64, G_STAGES = 3, G_THREADS = 192;
 constexpr int G_PLANE = GB_M * GB_K * 2;                 // 16 KB: one bf16 plane of one operand tile
 constexpr int G_STAGE_BYTES = 4 * G_PLANE;               // A(hi,lo) + B(hi,lo)
-constexpr int G_SMEM = G_STAGES * G_STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/;
+constexpr int G_EPI_PITCH = 36;                          // floats per staged row: conflict-free 16-byte writes and reads
+constexpr int G_EPI_BYTES = 4 * 32 * G_EPI_PITCH * 4;    // one 32 x 32 block per epilogue warp
+constexpr int G_SMEM = G_STAGES * G_STAGE_BYTES + G_EPI_BYTES + 1024 /*align*/ + 256 /*barriers*/;
 constexpr int G_TMEM = 2 * GB_N;                         // two accumulators: epilogue of tile i overlaps mainloop of i+1
 
 struct GemmParams {
@@ -29,7 +31,8 @@ __global__ void __launch_bounds__(G_THREADS, 1)
 gemm_sb16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, GemmParams p) {
   extern __shared__ unsigned char smem_raw[];
   unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-  uint64_t* full = reinterpret_cast<uint64_t*>(smem + G_STAGES * G_STAGE_BYTES);
+  float* epi = reinterpret_cast<float*>(smem + G_STAGES * G_STAGE_BYTES);
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + G_STAGES * G_STAGE_BYTES + G_EPI_BYTES);
   uint64_t* empty = full + G_STAGES;
   uint64_t* tfull = empty + G_STAGES;
   uint64_t* tempty = tfull + 2;
@@ -119,34 +122,47 @@ gemm_sb16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       float* Cz = p.C[z];
       float* crow = Cz + orow * p.ldc;
       const bool vec = ((p.ldc & 3) == 0) && ((reinterpret_cast<uintptr_t>(Cz) & 15) == 0);
-      for (int c = 0; c < GB_N; c += 16) {
+      float* stg = epi + (warp - 2) * 32 * G_EPI_PITCH;         // this warp's staging block
+      const int sr = lane >> 3, sc = (lane & 7) * 4;            // store role: row within a group of 4, column quad
+      for (int c = 0; c < GB_N; c += 32) {
         if (n0 + c >= p.N) break;                       // warp-uniform
-        float v[16];
+        float v[32];
         tmem_ld16(tmem_d + ((uint32_t)(q * 32) << 16) + c, v);
-        if (m < p.M) {
-          const int nb = n0 + c;
+        tmem_ld16(tmem_d + ((uint32_t)(q * 32) << 16) + c + 16, v + 16);
+        const int nb = n0 + c;
 #pragma unroll
-          for (int i = 0; i < 16; ++i) {
-            float r = p.alpha * v[i];
-            if (p.bias && nb + i < p.N) r += p.bias[nb + i];
-            v[i] = r;
-          }
-          if (vec && nb + 16 <= p.N) {
-            float4* dst = reinterpret_cast<float4*>(crow + nb);
+        for (int i = 0; i < 32; ++i) {
+          float r = p.alpha * v[i];
+          if (p.bias && nb + i < p.N) r += p.bias[nb + i];
+          v[i] = r;
+        }
+        if (vec && nb + 32 <= p.N) {
+          // a thread owns an accumulator ROW; through shared memory a warp instruction stores 4 rows x 128 contiguous
+          // bytes instead of 32 rows x 16 bytes
 #pragma unroll
-            for (int i = 0; i < 4; ++i) {
-              float4 o = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+          for (int i = 0; i < 8; ++i)
+            *reinterpret_cast<float4*>(stg + lane * G_EPI_PITCH + 4 * i) = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+          __syncwarp();
+#pragma unroll
+          for (int rr = 0; rr < 8; ++rr) {
+            const int rl = rr * 4 + sr, mm = m0 + q * 32 + rl;
+            float4 o = *reinterpret_cast<const float4*>(stg + rl * G_EPI_PITCH + sc);
+            if (mm < p.M) {
+              long long orow2 = mm;
+              if (p.rowmap == SS_ROWMAP_UNIT4) orow2 = (long long)(mm & 3) * p.hidden + (mm >> 2);
+              float4* dst = reinterpret_cast<float4*>(Cz + orow2 * p.ldc + nb + sc);
               if (p.beta != 0.0f) {
-                const float4 old = dst[i];
+                const float4 old = *dst;
                 o.x += p.beta * old.x; o.y += p.beta * old.y; o.z += p.beta * old.z; o.w += p.beta * old.w;
               }
-              dst[i] = o;
+              *dst = o;
             }
-          } else {
-#pragma unroll
-            for (int i = 0; i < 16; ++i)
-              if (nb + i < p.N) crow[nb + i] = v[i] + (p.beta != 0.0f ? p.beta * crow[nb + i] : 0.0f);
           }
+          __syncwarp();
+        } else if (m < p.M) {
+#pragma unroll
+          for (int i = 0; i < 32; ++i)
+            if (nb + i < p.N) crow[nb + i] = v[i] + (p.beta != 0.0f ? p.beta * crow[nb + i] : 0.0f);
         }
       }
       tc_fence_before();
