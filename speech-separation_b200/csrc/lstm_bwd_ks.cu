@@ -4,7 +4,7 @@
 //   dh_rec[b][j] = sum_{n < 4H} dG_prev[b][n] * W_hh[n][j]            (n = 4u+gate, interleaved)
 //
 // has K = 4H = 2400: an output-stationary CTA must stream all of dG_prev (614 KB split-bf16) through shared memory
-// every step, and TMA delivers ~58 B/clk per SM (tools/microbench/bulk_rate.cu) -> >= 10.6k cycles per step.  Here a
+// every step, at ~260 cycles per 16 KB copy (tools/microbench/bulk_size.cu) -> >= 10k cycles per step.  Here a
 // cluster of 4 CTAs owns 64 hidden units; CTA r streams only K-quarter r of dG_prev (154 KB), multiplies it with
 // its resident [K-quarter x 64 units] slice of W_hh^T (one stacked tcgen05.mma per 16-wide k-step: A = dG rows with
 // hi/lo planes interleaved, B = [W_hi; W_lo], D = 128 x 128 in TMEM), and the four partial products are reduced over
