@@ -157,6 +157,12 @@ def dist_setup(n_gpus):
     return rank, local, world
 
 
+# dram__bytes_read.sum + dram__bytes_write.sum per launch, from the `ncu --set full` captures summarised in
+# profiles/r01_summary.md (sections E, F, H) for the same workloads bench.py runs (largest batch shape for lstm_bwd)
+NCU_TRAFFIC = {"lstm_bwd": 1.319e9, "stft": 37.9e9, "istft": 6.08e9}
+NCU_TRAFFIC_NOTE = "ncu --set full, one launch, profiles/r01_summary.md"
+
+
 def timed_region(fn, steps, warmup, world, sampler=None):
     """W untimed + K timed calls of fn(i), barrier + synchronize on both sides, CUDA events, max over ranks (ms)."""
     import torch
@@ -321,7 +327,8 @@ def run_train(args, rank, local, world):
         divergence = float(d)
     dom = max(prof, key=lambda k: prof[k]["ms_per_step"])
     roofline = dict(rl.get(dom, {"bound": "tensor", "achieved": None, "peak": tf_sus, "unit": "TFLOP/s", "frac": None}))
-    roofline.update({"kernel": dom, "traffic": None, "peak_source": peak_src,
+    roofline.update({"kernel": dom, "traffic": NCU_TRAFFIC.get(dom), "traffic_source": NCU_TRAFFIC_NOTE if dom in NCU_TRAFFIC else None,
+                     "peak_source": peak_src,
                      "share_of_step": round(prof[dom]["ms_per_step"] / sum(v["ms_per_step"] for v in prof.values()), 3)})
     line = {
         "metric": "uPIT train audio-sec/sec", "value": round(value, 1), "unit": "audio-sec/sec", "n_gpus": world,
@@ -434,8 +441,8 @@ def run_stft(args, rank, local, world, n_mix=20000, e2e_mix=2000):
                 "d2h_bytes_per_step": rag_e.total_frames * STFT_F * 4, "sample": "%d-mixture shard via pinned host memory" % e2e_mix},
         "gpu_launches": launches, "clocks": clocks,
         "roofline": {"bound": "hbm", "kernel": "stft_kernel<256>", "achieved": round(ach, 1), "peak": hbm, "unit": "GB/s",
-                     "frac": round(ach / hbm, 4), "traffic": None, "peak_source": peak_src,
-                     "algorithmic_bytes_per_frame": bytes_per_frame, "kernel_ms": round(kms, 3)},
+                     "frac": round(ach / hbm, 4), "traffic": NCU_TRAFFIC["stft"], "traffic_source": NCU_TRAFFIC_NOTE,
+                     "peak_source": peak_src, "algorithmic_bytes_per_frame": bytes_per_frame, "kernel_ms": round(kms, 3)},
     }
 
 
@@ -470,7 +477,8 @@ def run_istft(args, rank, local, world, n_utts=3000, n_src=2):
             "unit": "frame-sources/sec", "n_gpus": world,
             "config": {"workload": "mask x mixture-phase iSTFT, 512/128, %d utts x %d sources, int16 out" % (n_utts, n_src)},
             "roofline": {"bound": "hbm", "kernel": "istft_kernel<512>", "achieved": round(ach, 1), "peak": hbm,
-                         "unit": "GB/s", "frac": round(ach / hbm, 4), "traffic": None, "peak_source": peak_src,
+                         "unit": "GB/s", "frac": round(ach / hbm, 4), "traffic": NCU_TRAFFIC["istft"],
+                         "traffic_source": NCU_TRAFFIC_NOTE, "peak_source": peak_src,
                          "algorithmic_bytes_per_frame_source": byts, "kernel_ms": round(kms, 3)}}
 
 
@@ -539,9 +547,9 @@ def main():
             line["istft"] = run_istft(sub, rank, local, world)
     if rank == 0 and world == 1 and not args.no_extras:
         if args.workload == "train":
-            aps, sec, cores = cpu_train_sample(4, 1, 1)
+            aps, sec, cores = cpu_train_sample(16, 3, 1)        # ~15 s of CPU work on this box
             line["cpu_baseline"] = {"value": round(aps, 2), "unit": "audio-sec/sec", "cores": cores, "kind": "port",
-                                    "sample": "1 train step on 4 of the 64 utterances (%.1f s)" % sec}
+                                    "sample": "3 train steps (+1 warm-up) on 16 of the 64 utterances (%.1f s/step)" % sec}
             fps, n, c1 = cpu_stft_sample(5.0)
             line["stft"]["cpu_baseline"] = {"value": round(fps, 0), "unit": "frames/sec", "cores": c1, "kind": "port",
                                             "sample": "%d utterances, single process" % n}

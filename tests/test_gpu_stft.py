@@ -24,7 +24,7 @@ def _rel(a, b):
     return float(np.abs(a - b).max() / np.abs(b).max()), float(np.linalg.norm(a - b) / np.linalg.norm(b))
 
 
-@pytest.mark.parametrize("n_fft,hop", [(512, 128), (256, 64)])
+@pytest.mark.parametrize("n_fft,hop", [(512, 128), (256, 64), (512, 256), (256, 96), (512, 160)])
 @pytest.mark.parametrize("complex_out", [False, True])
 @pytest.mark.parametrize("layout_tf", [False, True])
 def test_stft_matches_oracle(n_fft, hop, complex_out, layout_tf):
@@ -62,7 +62,7 @@ def test_stft_linearity_full_size():
     assert float(err) <= 1e-5
 
 
-@pytest.mark.parametrize("n_fft,hop", [(512, 128), (256, 64)])
+@pytest.mark.parametrize("n_fft,hop", [(512, 128), (256, 64), (512, 256), (256, 96), (512, 160)])
 @pytest.mark.parametrize("layout_tf", [False, True])
 def test_masked_istft_matches_oracle(n_fft, hop, layout_tf):
     lens = [16000, 29 * hop, 28 * hop + 1, 5000, n_fft + 3, n_fft // 2 + hop]
