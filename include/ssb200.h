@@ -129,6 +129,13 @@ long long ss_lstm_ws_bytes(int B, int H);
 int ss_lstm_fwd(float* gx, const void* whh_r, long long whh_ld, long long whh_plane, const float* h0, const float* c0,
                 const int* lens, void* out, long long out_plane, void* outT, void* hprevT, long long ldT,
                 long long outT_plane, float* cs, float* hn, float* cn, void* ws, int T, int B, int H, void* stream);
+/* Overlap aids (engine.py runs the upper layer's weight-gradient GEMMs beside the lower layer's backward recurrence):
+ * ss_lstm_bwd_start_flag: the NEXT ss_lstm_bwd launch stores `value` to *flag once its grid is resident;
+ * ss_stream_wait_value32: stream-ordered wait until *addr >= value (no SM occupied while waiting);
+ * ss_gemm_sm_limit: grid cap of the following ss_gemm_* launches from this host thread (0 = all SMs). */
+int ss_lstm_bwd_start_flag(unsigned int* flag, unsigned int value);
+int ss_stream_wait_value32(void* stream, unsigned int* addr, unsigned int value);
+int ss_gemm_sm_limit(int n);
 int ss_lstm_bwd(const float* gates, const float* cs, const float* c0, const float* dout, const float* dhn,
                 const float* dcn, const int* lens, const void* whhT, long long whhT_ld, long long whhT_plane, void* dG,
                 long long dG_plane, void* dGT, long long ldT, long long dGT_plane, float* dh0, float* dc0, void* ws,

@@ -65,6 +65,28 @@ extern "C" {
 
 const char* ss_last_error(void) { return ssb::g_err; }
 
+// Stream-ordered wait until *addr >= value (cuStreamWaitValue32, GEQ): no SM is occupied while waiting.
+int ss_stream_wait_value32(void* stream, unsigned int* addr, unsigned int value) {
+  typedef CUresult (*wait_fn)(CUstream, CUdeviceptr, cuuint32_t, unsigned int);
+  static wait_fn wait = nullptr;
+  if (!wait) {
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    cudaError_t e = cudaGetDriverEntryPoint("cuStreamWaitValue32", &fn, cudaEnableDefault, &qres);
+    if (e != cudaSuccess || qres != cudaDriverEntryPointSuccess || !fn) {
+      ssb::set_error("cuStreamWaitValue32 unavailable (%s)", cudaGetErrorString(e));
+      return -3;
+    }
+    wait = (wait_fn)fn;
+  }
+  CUresult r = wait((CUstream)stream, (CUdeviceptr)addr, value, CU_STREAM_WAIT_VALUE_GEQ);
+  if (r != CUDA_SUCCESS) {
+    ssb::set_error("cuStreamWaitValue32 failed: CUresult %d", (int)r);
+    return -3;
+  }
+  return 0;
+}
+
 int ss_version(void) { return SSB200_VERSION; }
 
 int ss_device_check(void) {

@@ -188,6 +188,14 @@ static int sb16_tmap(CUtensorMap* tm, const void* base, long long rows, long lon
 
 }  // namespace ssb
 
+// Grid cap for the following launches of this host thread (0 = all SMs): lets a GEMM run beside a resident
+// recurrence kernel on the SMs that kernel leaves idle (engine.py, backward of the upper layer's weights).
+static int g_sm_limit = 0;
+extern "C" int ss_gemm_sm_limit(int n) {
+  g_sm_limit = n > 0 ? n : 0;
+  return 0;
+}
+
 static int gemm_launch(const void* A, long long lda, long long a_plane, int a_rows, const void* B, long long ldb,
                        long long b_plane, int b_rows, ssb::GemmParams p, void* stream) {
   using namespace ssb;
@@ -212,7 +220,9 @@ static int gemm_launch(const void* A, long long lda, long long a_plane, int a_ro
     attr_set = true;
   }
   const int tiles = p.batch * cdiv(p.N, GB_N) * cdiv(p.M, GB_M);
-  gemm_sb16_kernel<<<tiles < n_sm ? tiles : n_sm, G_THREADS, G_SMEM, (cudaStream_t)stream>>>(tmA, tmB, p);
+  int grid = tiles < n_sm ? tiles : n_sm;
+  if (g_sm_limit > 0 && grid > g_sm_limit) grid = g_sm_limit;
+  gemm_sb16_kernel<<<grid, G_THREADS, G_SMEM, (cudaStream_t)stream>>>(tmA, tmB, p);
   return check_launch("ss_gemm_sb16");
 }
 

@@ -36,6 +36,7 @@ lstm_bwd_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
   uint64_t* wfull = accum_full + 1;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(wfull + 1);
 
+  if (p.start_flag && blockIdx.x == 0 && threadIdx.x == 0) *reinterpret_cast<volatile unsigned int*>(p.start_flag) = p.start_value;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int dir = blockIdx.x / p.NC, cta = blockIdx.x % p.NC;
   const int j0 = cta * LB_U;
@@ -232,6 +233,16 @@ lstm_bwd_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
 
 }  // namespace ssb
 
+// The NEXT ss_lstm_bwd launch writes `value` to *flag as soon as its grid is resident (both kernels are cooperative
+// launches): stream-ordered work gated on it with ss_stream_wait_value32 then runs on the SMs the recurrence leaves idle.
+static unsigned int* g_start_flag = nullptr;
+static unsigned int g_start_value = 0;
+extern "C" int ss_lstm_bwd_start_flag(unsigned int* flag, unsigned int value) {
+  g_start_flag = flag;
+  g_start_value = value;
+  return 0;
+}
+
 extern "C" int ss_lstm_bwd(const float* gates, const float* cs, const float* c0, const float* dout, const float* dhn,
                            const float* dcn, const int* lens, const void* whhT, long long whhT_ld,
                            long long whhT_plane, void* dG, long long dG_plane, void* dGT, long long ldT,
@@ -254,6 +265,9 @@ extern "C" int ss_lstm_bwd(const float* gates, const float* cs, const float* c0,
   p.dbg = g_lstm_dbg;
   p.ROT = getenv("SSB_ROT") ? atoi(getenv("SSB_ROT")) : 1;
   p.sync = (unsigned int*)ws;
+  p.start_flag = g_start_flag;                                 // one-shot, see ss_lstm_bwd_start_flag
+  p.start_value = g_start_value;
+  g_start_flag = nullptr;
   cudaMemsetAsync(ws, 0, 256, st);
   if (H == 600 && B <= 64 && !getenv("SSB_BWD_V1")) {
     int rc = launch_lstm_bwd_ks(p, whhT, whhT_ld, whhT_plane, st);

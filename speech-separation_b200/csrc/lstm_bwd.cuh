@@ -19,6 +19,8 @@ struct LstmBwdParams {
   float* dh0;                // [2][B][H] or null
   float* dc0;
   unsigned int* sync;
+  unsigned int* start_flag;  // optional: *start_flag = start_value once the kernel is resident (ss_lstm_bwd_start_flag)
+  unsigned int start_value;
   int T, B, H, R, NC, KC, NS, want_d0, ROT;
   long long* dbg;            // optional clock64 trace of CTA 0: [step][32]
 };

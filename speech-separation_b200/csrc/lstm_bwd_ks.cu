@@ -99,6 +99,8 @@ lstm_bwd_ks_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int rank = (int)cluster_rank();
+  // cooperative launch: block 0 running means the whole grid is resident -> work waiting on the flag may start
+  if (p.start_flag && blockIdx.x == 0 && threadIdx.x == 0) *reinterpret_cast<volatile unsigned int*>(p.start_flag) = p.start_value;
   const int cl = blockIdx.x / KS_CL;
   const int dir = cl / KS_NCL, c = cl % KS_NCL;
   const int T = p.T, B = p.B;

@@ -103,11 +103,16 @@ class Workspace:
             self.dzT = SB16(out_dim, TB, device)
             self.dy = torch.empty(TB, 2 * H, **f32)           # dY -> dout of the top layer (in place)
             self.dout = torch.empty(TB, 2 * H, **f32)         # dout of lower layers
-            self.dG = SB16(TB, 8 * H, device)
-            self.dGT = SB16(8 * H, TB, device)
+            # one gradient buffer per layer: the upper layer's weight-gradient GEMMs still read theirs while the lower
+            # layer's recurrence writes its own (see backward())
+            self.dG = [SB16(TB, 8 * H, device) for _ in range(num_layers)]
+            self.dGT = [SB16(8 * H, TB, device) for _ in range(num_layers)]
             self.G = torch.empty(out_dim, 2 * H, **f32)
             self.bn_bwd = torch.empty(2, 2 * H, **f32)
-            self.cs_partial = torch.empty(max(1, lib().ss_colsum_parts(TB)) * 8 * H, **f32)
+            self.cs_partial = [torch.empty(max(1, lib().ss_colsum_parts(TB)) * 8 * H, **f32) for _ in range(num_layers + 1)]
+            self.db_l = [torch.empty(8 * H, **f32) for _ in range(num_layers)]
+            self.start_flag = torch.zeros(1, dtype=torch.int32, device=device)
+            self.start_seq = 0
             self.bwd_sync = torch.empty(256, dtype=torch.uint8, device=device)
 
 
@@ -172,7 +177,7 @@ def backward(ws, wt, p, grads, mix, src, lens_dev, c0, F, n_out, gout, dmask_ext
         ws.dgamma = torch.empty(2 * H, dtype=torch.float32, device=mix.device)
         ws.dbeta = torch.empty(2 * H, dtype=torch.float32, device=mix.device)
         ws.db = torch.empty(8 * H, dtype=torch.float32, device=mix.device)
-    call("colsum_sb16", ws.dz.buf, LL(ws.dz.ld), LL(ws.dz.plane), TB, O, ws.cs_partial, dsum, 0, 0, st)
+    call("colsum_sb16", ws.dz.buf, LL(ws.dz.ld), LL(ws.dz.plane), TB, O, ws.cs_partial[-1], dsum, 0, 0, st)
     _gemm(ws.dzT, topT, ws.G, K=TB)
     call("head_dw_fix", ws.G, dsum, ws.coef, p["bn.bias"], O, 2 * H, ws.dlinW, st)
     _gemm(ws.dz, wt.linT, ws.dy, K=O)
@@ -189,33 +194,75 @@ def backward(ws, wt, p, grads, mix, src, lens_dev, c0, F, n_out, gout, dmask_ext
     if want_d0:
         dh0 = torch.zeros(2 * ws.L, B, H, dtype=torch.float32, device=mix.device)
         dc0 = torch.zeros(2 * ws.L, B, H, dtype=torch.float32, device=mix.device)
-    for l in range(ws.L - 1, -1, -1):
-        call("lstm_bwd", ws.gx[l], ws.cs[l], c0[2 * l:2 * l + 2], dout,
-             dhn[2 * l:2 * l + 2] if dhn is not None else None, dcn[2 * l:2 * l + 2] if dcn is not None else None,
-             lens_dev, wt.whhT[l].buf, LL(wt.whhT[l].ld), LL(wt.whhT[l].plane), ws.dG.buf, LL(ws.dG.plane),
-             ws.dGT.buf, LL(ws.dGT.ld), LL(ws.dGT.plane), dh0[2 * l:2 * l + 2] if want_d0 else None,
-             dc0[2 * l:2 * l + 2] if want_d0 else None, ws.bwd_sync, T, B, H, st)
-        xT = ws.x0T if l == 0 else ws.outT[l - 1]
-        # both directions' dW_ih = dG^T x and dW_hh = dG^T h_prev in one launch each (rows d*4H.. of dGT; d*H.. of hprevT)
-        I = xT.rows
-        for B_op, b_rows, N, kind in ((xT, 0, I, "ih"), (ws.hprevT[l], H, H, "hh")):
+
+    def weight_grads(l):
+        """dW_ih, dW_hh (both directions per launch: rows d*4H.. of dGT; d*H.. of hprevT), biases; then the bucket hook."""
+        s = stream_ptr()
+        dGT, xT = ws.dGT[l], (ws.x0T if l == 0 else ws.outT[l - 1])
+        for B_op, b_rows, N, kind in ((xT, 0, xT.rows, "ih"), (ws.hprevT[l], H, H, "hh")):
             g0, g1 = grads["blstm.weight_%s_l%d" % (kind, l)], grads["blstm.weight_%s_l%d_reverse" % (kind, l)]
             assert g0.stride(0) == g1.stride(0) and g0.stride(1) == 1
-            call("gemm_sb16_x2", ws.dGT.buf, LL(ws.dGT.ld), LL(ws.dGT.plane), 4 * H, B_op.buf, LL(B_op.ld), LL(B_op.plane),
-                 b_rows, g0, g1, LL(g0.stride(0)), 4 * H, N, TB, 1.0, float(beta), UNIT4, H, st)
-        call("colsum_sb16", ws.dG.buf, LL(ws.dG.ld), LL(ws.dG.plane), TB, 8 * H, ws.cs_partial, ws.db, UNIT4, H, st)
+            call("gemm_sb16_x2", dGT.buf, LL(dGT.ld), LL(dGT.plane), 4 * H, B_op.buf, LL(B_op.ld), LL(B_op.plane),
+                 b_rows, g0, g1, LL(g0.stride(0)), 4 * H, N, TB, 1.0, float(beta), UNIT4, H, s)
+        db = ws.db_l[l]
+        call("colsum_sb16", ws.dG[l].buf, LL(ws.dG[l].ld), LL(ws.dG[l].plane), TB, 8 * H, ws.cs_partial[l], db, UNIT4, H, s)
         for d, suf in enumerate(("", "_reverse")):
-            _acc(grads, "blstm.bias_ih_l%d%s" % (l, suf), ws.db[d * 4 * H:(d + 1) * 4 * H], accumulate)
-            _acc(grads, "blstm.bias_hh_l%d%s" % (l, suf), ws.db[d * 4 * H:(d + 1) * 4 * H], accumulate)
+            _acc(grads, "blstm.bias_ih_l%d%s" % (l, suf), db[d * 4 * H:(d + 1) * 4 * H], accumulate)
+            _acc(grads, "blstm.bias_hh_l%d%s" % (l, suf), db[d * 4 * H:(d + 1) * 4 * H], accumulate)
         if hook is not None:
             hook("l%d" % l)
+
+    # The K-split backward recurrence occupies 80 of the 148 SMs for ~5 ms; the weight gradients of layer l+1 are not
+    # on the critical path, so they run on a side stream, capped to the idle SMs, once layer l's recurrence is
+    # resident (it raises ws.start_flag at its start; the side stream waits on that value without holding an SM).
+    overlap = OVERLAP and ws.L > 1 and B <= 64
+    side = _side_stream(mix.device) if overlap else None
+    pending = None                                             # layer whose weight gradients wait for the next recurrence
+    main = torch.cuda.current_stream()
+    for l in range(ws.L - 1, -1, -1):
+        if pending is not None:
+            ws.start_seq += 1
+            call("lstm_bwd_start_flag", ws.start_flag, ws.start_seq)
+        call("lstm_bwd", ws.gx[l], ws.cs[l], c0[2 * l:2 * l + 2], dout,
+             dhn[2 * l:2 * l + 2] if dhn is not None else None, dcn[2 * l:2 * l + 2] if dcn is not None else None,
+             lens_dev, wt.whhT[l].buf, LL(wt.whhT[l].ld), LL(wt.whhT[l].plane), ws.dG[l].buf, LL(ws.dG[l].plane),
+             ws.dGT[l].buf, LL(ws.dGT[l].ld), LL(ws.dGT[l].plane), dh0[2 * l:2 * l + 2] if want_d0 else None,
+             dc0[2 * l:2 * l + 2] if want_d0 else None, ws.bwd_sync, T, B, H, stream_ptr())
+        if pending is not None:
+            with torch.cuda.stream(side):
+                call("stream_wait_value32", stream_ptr(), ws.start_flag, ws.start_seq)
+                call("gemm_sm_limit", IDLE_SMS)
+                weight_grads(pending)
+                call("gemm_sm_limit", 0)
+            pending = None
+        if overlap and l > 0:
+            ev = torch.cuda.Event()
+            ev.record(main)                                    # dG / dGT of layer l are complete
+            side.wait_event(ev)
+            pending = l
+        else:
+            weight_grads(l)
         if l > 0:
-            _gemm(ws.dG, wt.wihT[l], ws.dout, K=8 * H)
+            _gemm(ws.dG[l], wt.wihT[l], ws.dout, K=8 * H)
             dout = ws.dout
         elif want_dx:
             dx = torch.empty(TB, ws.in_dim, dtype=torch.float32, device=mix.device)
-            _gemm(ws.dG, wt.wihT[0], dx, K=8 * H)
+            _gemm(ws.dG[0], wt.wihT[0], dx, K=8 * H)
+    if side is not None:
+        main.wait_stream(side)
     return dx, dh0, dc0
+
+
+OVERLAP = not __import__("os").environ.get("SSB_NO_OVERLAP")
+IDLE_SMS = 68                                                  # 148 SMs - the 80 CTAs of the K-split backward recurrence
+_SIDE = {}
+
+
+def _side_stream(device):
+    key = torch.device(device).index if torch.device(device).index is not None else torch.cuda.current_device()
+    if key not in _SIDE:
+        _SIDE[key] = torch.cuda.Stream(device=device)
+    return _SIDE[key]
 
 
 def _acc(grads, name, val, accumulate):
