@@ -129,6 +129,13 @@ long long ss_lstm_ws_bytes(int B, int H);
 int ss_lstm_fwd(float* gx, const void* whh_r, long long whh_ld, long long whh_plane, const float* h0, const float* c0,
                 const int* lens, void* out, long long out_plane, void* outT, void* hprevT, long long ldT,
                 long long outT_plane, float* cs, float* hn, float* cn, void* ws, int T, int B, int H, void* stream);
+/* The transposed sb16 copies the weight-gradient GEMMs read, as separate calls (ss_lstm_fwd with outT = hprevT = NULL
+ * and ss_lstm_bwd with dGT = NULL skip them): out[c][r] = in[r][c] for both planes; hprevT[d*H+j][t*B+b] = the state
+ * direction d carried INTO frame t of row b (h0 at the row's first processed frame, zero at t >= len_b). */
+int ss_transpose_sb16(const void* in, long long ld, long long plane, int R, int C, void* out, long long ldT,
+                      long long planeT, void* stream);
+int ss_hprev_transpose(const void* out_sb, long long ld, long long plane, int T, int B, int H, const int* lens,
+                       const float* h0, void* hprevT, long long ldT, long long planeT, void* stream);
 /* Overlap aids (engine.py runs the upper layer's weight-gradient GEMMs beside the lower layer's backward recurrence):
  * ss_lstm_bwd_start_flag: the NEXT ss_lstm_bwd launch stores `value` to *flag once its grid is resident;
  * ss_stream_wait_value32: stream-ordered wait until *addr >= value (no SM occupied while waiting);

@@ -272,7 +272,7 @@ extern "C" int ss_lstm_bwd(const float* gates, const float* cs, const float* c0,
   if (H == 600 && B <= 64 && !getenv("SSB_BWD_V1")) {
     int rc = launch_lstm_bwd_ks(p, whhT, whhT_ld, whhT_plane, st);
     if (rc) return rc;
-    return launch_transpose_sb16(dG, 8LL * H, dG_plane, T * B, 8 * H, dGT, ldT, dGT_plane, st);
+    return dGT ? launch_transpose_sb16(dG, 8LL * H, dG_plane, T * B, 8 * H, dGT, ldT, dGT_plane, st) : 0;
   }
 
   CUtensorMap tmW, tmG;
@@ -298,5 +298,5 @@ extern "C" int ss_lstm_bwd(const float* gates, const float* cs, const float* c0,
     set_error("ss_lstm_bwd: cooperative launch failed: %s", cudaGetErrorString(e));
     return -2;
   }
-  return launch_transpose_sb16(dG, 8LL * H, dG_plane, T * B, 8 * H, dGT, ldT, dGT_plane, st);
+  return dGT ? launch_transpose_sb16(dG, 8LL * H, dG_plane, T * B, 8 * H, dGT, ldT, dGT_plane, st) : 0;
 }

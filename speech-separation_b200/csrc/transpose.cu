@@ -78,3 +78,14 @@ int launch_hprev_transpose(const void* out_sb, long long ld, long long plane, in
 }
 
 }  // namespace ssb
+
+// The transposed operand copies on their own, so the caller can keep them off the critical stream
+// (ss_lstm_fwd with outT = hprevT = NULL, ss_lstm_bwd with dGT = NULL skip them).
+extern "C" int ss_transpose_sb16(const void* in, long long ld, long long plane, int R, int C, void* out, long long ldT,
+                                 long long planeT, void* stream) {
+  return ssb::launch_transpose_sb16(in, ld, plane, R, C, out, ldT, planeT, (cudaStream_t)stream);
+}
+extern "C" int ss_hprev_transpose(const void* out_sb, long long ld, long long plane, int T, int B, int H, const int* lens,
+                                  const float* h0, void* hprevT, long long ldT, long long planeT, void* stream) {
+  return ssb::launch_hprev_transpose(out_sb, ld, plane, T, B, H, lens, h0, hprevT, ldT, planeT, (cudaStream_t)stream);
+}

@@ -132,11 +132,23 @@ def forward(ws, wt, p, x, lens_dev, h0, c0, bn_train, save=True, bn_momentum=0.1
     for l in range(ws.L):
         _gemm(inp, wt.wih[l], ws.gx[l], bias=wt.bias[l])
         o = ws.out[l]
+        inline_T = training and not OVERLAP                    # transposed copies inside the call, on this stream
         call("lstm_fwd", ws.gx[l], wt.whh_r[l].buf, LL(wt.whh_r[l].ld), LL(wt.whh_r[l].plane),
              h0[2 * l:2 * l + 2], c0[2 * l:2 * l + 2], lens_dev, o.buf, LL(o.plane),
-             ws.outT[l].buf if training else None, ws.hprevT[l].buf if training else None,
-             LL(ws.outT[l].ld if training else 0), LL(ws.outT[l].plane if training else 0),
+             ws.outT[l].buf if inline_T else None, ws.hprevT[l].buf if inline_T else None,
+             LL(ws.outT[l].ld if inline_T else 0), LL(ws.outT[l].plane if inline_T else 0),
              ws.cs[l] if training else None, ws.hn[2 * l:2 * l + 2], ws.cn[2 * l:2 * l + 2], ws.lstm_ws, T, B, H, st)
+        if training and OVERLAP:
+            # only the backward pass reads outT / hprevT: the side stream makes them while the next GEMM and
+            # recurrence run (backward() joins the side stream before it needs them)
+            side, ev = _side_stream(x.device), torch.cuda.Event()
+            ev.record()
+            side.wait_event(ev)
+            with torch.cuda.stream(side):
+                oT, hT = ws.outT[l], ws.hprevT[l]
+                call("transpose_sb16", o.buf, LL(o.ld), LL(o.plane), TB, 2 * H, oT.buf, LL(oT.ld), LL(oT.plane), stream_ptr())
+                call("hprev_transpose", o.buf, LL(o.ld), LL(o.plane), T, B, H, lens_dev, h0[2 * l:2 * l + 2], hT.buf,
+                     LL(hT.ld), LL(hT.plane), stream_ptr())
         inp = o
     top = ws.out[-1]
     call("bn_stats", top.buf, LL(top.ld), LL(top.plane), TB, 2 * H, p["bn.weight"], p["bn.bias"], float(bn_eps),
@@ -177,18 +189,22 @@ def backward(ws, wt, p, grads, mix, src, lens_dev, c0, F, n_out, gout, dmask_ext
         ws.dgamma = torch.empty(2 * H, dtype=torch.float32, device=mix.device)
         ws.dbeta = torch.empty(2 * H, dtype=torch.float32, device=mix.device)
         ws.db = torch.empty(8 * H, dtype=torch.float32, device=mix.device)
-    call("colsum_sb16", ws.dz.buf, LL(ws.dz.ld), LL(ws.dz.plane), TB, O, ws.cs_partial[-1], dsum, 0, 0, st)
-    _gemm(ws.dzT, topT, ws.G, K=TB)
-    call("head_dw_fix", ws.G, dsum, ws.coef, p["bn.bias"], O, 2 * H, ws.dlinW, st)
+    def head_weight_grads():
+        """dlin.weight, dlin.bias (needs dz only: off the critical path), then the bucket hook."""
+        s = stream_ptr()
+        call("colsum_sb16", ws.dz.buf, LL(ws.dz.ld), LL(ws.dz.plane), TB, O, ws.cs_partial[-1], dsum, 0, 0, s)
+        _gemm(ws.dzT, topT, ws.G, K=TB)
+        call("head_dw_fix", ws.G, dsum, ws.coef, p["bn.bias"], O, 2 * H, ws.dlinW, s)
+        _acc(grads, "lin.weight", ws.dlinW, accumulate)
+        _acc(grads, "lin.bias", dsum, accumulate)
+        if hook is not None:
+            hook("head")
+
     _gemm(ws.dz, wt.linT, ws.dy, K=O)
     call("bn_bwd", ws.dy, top.buf, LL(top.ld), LL(top.plane), TB, 2 * H, ws.coef, int(training), ws.bn_partial,
          ws.dgamma, ws.dbeta, ws.bn_bwd, st)
-    _acc(grads, "lin.weight", ws.dlinW, accumulate)
-    _acc(grads, "lin.bias", dsum, accumulate)
     _acc(grads, "bn.weight", ws.dgamma, accumulate)
     _acc(grads, "bn.bias", ws.dbeta, accumulate)
-    if hook is not None:
-        hook("head")
     dout = ws.dy
     dx = dh0 = dc0 = None
     if want_d0:
@@ -199,6 +215,9 @@ def backward(ws, wt, p, grads, mix, src, lens_dev, c0, F, n_out, gout, dmask_ext
         """dW_ih, dW_hh (both directions per launch: rows d*4H.. of dGT; d*H.. of hprevT), biases; then the bucket hook."""
         s = stream_ptr()
         dGT, xT = ws.dGT[l], (ws.x0T if l == 0 else ws.outT[l - 1])
+        if overlap:
+            dG = ws.dG[l]
+            call("transpose_sb16", dG.buf, LL(dG.ld), LL(dG.plane), TB, 8 * H, dGT.buf, LL(dGT.ld), LL(dGT.plane), s)
         for B_op, b_rows, N, kind in ((xT, 0, xT.rows, "ih"), (ws.hprevT[l], H, H, "hh")):
             g0, g1 = grads["blstm.weight_%s_l%d" % (kind, l)], grads["blstm.weight_%s_l%d_reverse" % (kind, l)]
             assert g0.stride(0) == g1.stride(0) and g0.stride(1) == 1
@@ -215,31 +234,43 @@ def backward(ws, wt, p, grads, mix, src, lens_dev, c0, F, n_out, gout, dmask_ext
     # The K-split backward recurrence occupies 80 of the 148 SMs for ~5 ms; the weight gradients of layer l+1 are not
     # on the critical path, so they run on a side stream, capped to the idle SMs, once layer l's recurrence is
     # resident (it raises ws.start_flag at its start; the side stream waits on that value without holding an SM).
-    overlap = OVERLAP and ws.L > 1 and B <= 64
-    side = _side_stream(mix.device) if overlap else None
-    pending = None                                             # layer whose weight gradients wait for the next recurrence
+    overlap = OVERLAP and B <= 64
+    side = _side_stream(mix.device) if OVERLAP else None
     main = torch.cuda.current_stream()
+    if side is not None:
+        main.wait_stream(side)                                 # the forward pass's transposed copies
+    deferred = []                                              # work that waits for the next recurrence to be resident
+
+    def defer(fn):
+        ev = torch.cuda.Event()
+        ev.record(main)                                        # its inputs are complete at this point of the main stream
+        side.wait_event(ev)
+        deferred.append(fn)
+
+    if overlap:
+        defer(head_weight_grads)
+    else:
+        head_weight_grads()
     for l in range(ws.L - 1, -1, -1):
-        if pending is not None:
+        if deferred:
             ws.start_seq += 1
             call("lstm_bwd_start_flag", ws.start_flag, ws.start_seq)
         call("lstm_bwd", ws.gx[l], ws.cs[l], c0[2 * l:2 * l + 2], dout,
              dhn[2 * l:2 * l + 2] if dhn is not None else None, dcn[2 * l:2 * l + 2] if dcn is not None else None,
              lens_dev, wt.whhT[l].buf, LL(wt.whhT[l].ld), LL(wt.whhT[l].plane), ws.dG[l].buf, LL(ws.dG[l].plane),
-             ws.dGT[l].buf, LL(ws.dGT[l].ld), LL(ws.dGT[l].plane), dh0[2 * l:2 * l + 2] if want_d0 else None,
-             dc0[2 * l:2 * l + 2] if want_d0 else None, ws.bwd_sync, T, B, H, stream_ptr())
-        if pending is not None:
+             None if overlap else ws.dGT[l].buf, LL(ws.dGT[l].ld), LL(ws.dGT[l].plane),
+             dh0[2 * l:2 * l + 2] if want_d0 else None, dc0[2 * l:2 * l + 2] if want_d0 else None, ws.bwd_sync, T, B, H,
+             stream_ptr())
+        if deferred:
             with torch.cuda.stream(side):
                 call("stream_wait_value32", stream_ptr(), ws.start_flag, ws.start_seq)
                 call("gemm_sm_limit", IDLE_SMS)
-                weight_grads(pending)
+                for fn in deferred:
+                    fn()
                 call("gemm_sm_limit", 0)
-            pending = None
+            deferred = []
         if overlap and l > 0:
-            ev = torch.cuda.Event()
-            ev.record(main)                                    # dG / dGT of layer l are complete
-            side.wait_event(ev)
-            pending = l
+            defer(lambda l=l: weight_grads(l))
         else:
             weight_grads(l)
         if l > 0:
