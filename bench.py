@@ -389,7 +389,7 @@ def run_stft(args, rank, local, world, n_mix=20000, e2e_mix=2000):
     K, W = args.steps, args.warmup
     per_rank = n_mix * 3 // world
     lens = stft_corpus_lengths(n_mix * 3)[rank * per_rank:(rank + 1) * per_rank]
-    rag = ops.Ragged(lens, STFT_NFFT, STFT_HOP, "cuda")
+    rag = ops.Ragged(lens, STFT_NFFT, STFT_HOP, "cuda", align=4)
     n = int(rag.sig_off[-1])
     sig = torch.empty(n, dtype=torch.float32, device="cuda").uniform_(-0.5, 0.5)
     out = torch.empty(rag.total_frames * STFT_F, dtype=torch.float32, device="cuda")
@@ -414,7 +414,7 @@ def run_stft(args, rank, local, world, n_mix=20000, e2e_mix=2000):
     ach = bytes_per_frame * rag.total_frames / (kms * 1e-3) / 1e9
     # e2e shard
     ne = e2e_mix * 3 // world
-    rag_e = ops.Ragged(lens[:ne], STFT_NFFT, STFT_HOP, "cuda")
+    rag_e = ops.Ragged(lens[:ne], STFT_NFFT, STFT_HOP, "cuda", align=4)
     n_e = int(rag_e.sig_off[-1])
     h_sig = torch.empty(n_e, dtype=torch.float32).uniform_(-0.5, 0.5).pin_memory()
     h_out = torch.empty(rag_e.total_frames * STFT_F, dtype=torch.float32).pin_memory()

@@ -40,6 +40,16 @@ int ss_stft_tile_frames(void);
 int ss_stft(const float* sig, const long long* sig_off, const long long* frame_off, const int* tile_off, int n_utts,
             int total_tiles, int n_fft, int hop, int flags, void* out, void* stream);
 
+/* K1 on the tensor cores (csrc/stft_mma.cu): the same magnitude STFT as ss_stft(n_fft = 256, hop = 64, flags = 0),
+ * replacing librosa.core.stft + np.abs at steps/extract_feats.py:87,89, evaluated as split-bf16 tcgen05 GEMMs of the
+ * folded frames against a resident windowed cos/sin basis.  Work is described per tile of
+ * ss_stft_dft256_tile_frames() consecutive frames of ONE utterance: tiles[i] = four int64
+ * { s0 = first sample of the utterance in sig, obase = first output element of the utterance (frame_off[u]*129),
+ *   N_u | T_u << 32, t0 = first frame of the tile }.  Output as ss_stft: (129, T_u) row-major per utterance.
+ * Utterances whose first sample is not 16-byte aligned take a slower scalar load path (same results). */
+int ss_stft_dft256_tile_frames(void);
+int ss_stft_dft256(const float* sig, const long long* tiles, int n_tiles, float* out, void* stream);
+
 /* ---- K7: masked iSTFT.  Replaces steps/reconstruct_sources.py:39-42 (np.multiply, librosa.core.istft,
  * *32767, astype('int16')) ----
  * spec: complex64 mixture STFT blocks as written by ss_stft(COMPLEX); mask: for utterance u, n_src blocks of

@@ -21,14 +21,19 @@ def up8(n):
 class Ragged:
     """Offsets of a ragged batch of utterances (lengths in samples)."""
 
-    def __init__(self, n_samples, n_fft, hop, device):
+    def __init__(self, n_samples, n_fft, hop, device, align=1):
+        """align > 1 starts every utterance at a multiple of `align` samples of the flat buffer (gaps are never
+        read); align=4 gives the tensor-core STFT its 16-byte loads.  Only ss_stft_dft256 takes the lengths
+        explicitly, so an aligned layout is accepted by `stft` on that path alone."""
         n = np.asarray(n_samples, dtype=np.int64)
         if n.size and n.min() <= n_fft // 2:
             raise ValueError("every utterance must be longer than n_fft//2 samples (reflect padding)")
         self.n_fft, self.hop, self.F = n_fft, hop, n_fft // 2 + 1
         self.n_samples = n
         self.T = 1 + n // hop
-        self.sig_off = np.concatenate([[0], np.cumsum(n)])
+        self.align = int(align)
+        self.sig_off = np.concatenate([[0], np.cumsum((n + align - 1) // align * align)])
+        self._dft_tiles = None
         self.frame_off = np.concatenate([[0], np.cumsum(self.T)])
         tf = lib().ss_stft_tile_frames()
         self.stft_tiles = np.concatenate([[0], np.cumsum((self.T + tf - 1) // tf)]).astype(np.int32)
@@ -41,6 +46,19 @@ class Ragged:
         self.d_stft_tiles = _i32(self.stft_tiles, device)
         self.d_istft_tiles = _i32(self.istft_tiles, device)
 
+    def dft_tiles(self):
+        """Tile table of ss_stft_dft256 (include/ssb200.h): one row of four int64 per 128-frame tile."""
+        if self._dft_tiles is None:
+            tf = lib().ss_stft_dft256_tile_frames()
+            nt = (self.T + tf - 1) // tf
+            u = np.repeat(np.arange(self.n_utts), nt)
+            first = np.concatenate([[0], np.cumsum(nt)])[:-1]
+            t0 = (np.arange(int(nt.sum())) - np.repeat(first, nt)) * tf
+            tab = np.stack([self.sig_off[:-1][u], self.frame_off[:-1][u] * self.F,
+                            self.n_samples[u] | (self.T[u] << 32), t0], axis=1).astype(np.int64)
+            self._dft_tiles = torch.as_tensor(np.ascontiguousarray(tab), device=self.device)
+        return self._dft_tiles
+
     @property
     def n_utts(self):
         return len(self.n_samples)
@@ -51,6 +69,7 @@ class Ragged:
 
 
 STFT_COMPLEX, STFT_TF, STFT_LOG = 1, 2, 4
+STFT_DFT256 = True   # 256/64 magnitude features on the tensor cores (csrc/stft_mma.cu); False = FFT kernel
 ISTFT_TF, ISTFT_F32 = 1, 2
 
 
@@ -63,6 +82,12 @@ def stft(sig, rag, complex_out=False, layout_tf=False, log=False, out=None):
     if out is None:
         out = torch.empty(n, dtype=torch.complex64 if complex_out else torch.float32, device=sig.device)
     flags = (STFT_COMPLEX if complex_out else 0) | (STFT_TF if layout_tf else 0) | (STFT_LOG if log else 0)
+    if flags == 0 and rag.n_fft == 256 and rag.hop == 64 and STFT_DFT256:
+        tiles = rag.dft_tiles()
+        call("stft_dft256", sig, tiles, int(tiles.shape[0]), out, stream_ptr())
+        return out
+    if rag.align != 1:
+        raise ValueError("an aligned Ragged layout is only read by the 256/64 magnitude path")
     call("stft", sig, rag.d_sig_off, rag.d_frame_off, rag.d_stft_tiles, rag.n_utts, int(rag.stft_tiles[-1]),
          rag.n_fft, rag.hop, flags, out, stream_ptr())
     return out
