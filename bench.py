@@ -389,7 +389,7 @@ def run_stft(args, rank, local, world, n_mix=20000, e2e_mix=2000):
     K, W = args.steps, args.warmup
     per_rank = n_mix * 3 // world
     lens = stft_corpus_lengths(n_mix * 3)[rank * per_rank:(rank + 1) * per_rank]
-    rag = ops.Ragged(lens, STFT_NFFT, STFT_HOP, "cuda", align=4)
+    rag = ops.Ragged(lens, STFT_NFFT, STFT_HOP, "cuda", align=4 if ops.STFT_DFT256 else 1)
     n = int(rag.sig_off[-1])
     sig = torch.empty(n, dtype=torch.float32, device="cuda").uniform_(-0.5, 0.5)
     out = torch.empty(rag.total_frames * STFT_F, dtype=torch.float32, device="cuda")
@@ -414,7 +414,7 @@ def run_stft(args, rank, local, world, n_mix=20000, e2e_mix=2000):
     ach = bytes_per_frame * rag.total_frames / (kms * 1e-3) / 1e9
     # e2e shard
     ne = e2e_mix * 3 // world
-    rag_e = ops.Ragged(lens[:ne], STFT_NFFT, STFT_HOP, "cuda", align=4)
+    rag_e = ops.Ragged(lens[:ne], STFT_NFFT, STFT_HOP, "cuda", align=4 if ops.STFT_DFT256 else 1)
     n_e = int(rag_e.sig_off[-1])
     h_sig = torch.empty(n_e, dtype=torch.float32).uniform_(-0.5, 0.5).pin_memory()
     h_out = torch.empty(rag_e.total_frames * STFT_F, dtype=torch.float32).pin_memory()
@@ -442,7 +442,7 @@ def run_stft(args, rank, local, world, n_mix=20000, e2e_mix=2000):
         "e2e": {"value": round(e2e, 0), "unit": "frames/sec", "h2d_bytes_per_step": n_e * 4,
                 "d2h_bytes_per_step": rag_e.total_frames * STFT_F * 4, "sample": "%d-mixture shard via pinned host memory" % e2e_mix},
         "gpu_launches": launches, "clocks": clocks,
-        "roofline": {"bound": "hbm", "kernel": "stft_kernel<256>", "achieved": round(ach, 1), "peak": hbm, "unit": "GB/s",
+        "roofline": {"bound": "hbm", "kernel": "stft_dft256_kernel" if ops.STFT_DFT256 else "stft_kernel<256>", "achieved": round(ach, 1), "peak": hbm, "unit": "GB/s",
                      "frac": round(ach / hbm, 4), "traffic": NCU_TRAFFIC["stft"], "traffic_source": NCU_TRAFFIC_NOTE,
                      "peak_source": peak_src, "algorithmic_bytes_per_frame": bytes_per_frame, "kernel_ms": round(kms, 3)},
     }

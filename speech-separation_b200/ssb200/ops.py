@@ -1,5 +1,7 @@
 """Host-side wrappers (torch tensors in, torch tensors out) over the C ABI.  No arithmetic happens here:
 torch only allocates device memory and supplies the stream."""
+import os
+
 import numpy as np
 import torch
 
@@ -69,7 +71,9 @@ class Ragged:
 
 
 STFT_COMPLEX, STFT_TF, STFT_LOG = 1, 2, 4
-STFT_DFT256 = True   # 256/64 magnitude features on the tensor cores (csrc/stft_mma.cu); False = FFT kernel
+# 256/64 magnitude features on the tensor cores (csrc/stft_mma.cu) instead of the FFT kernel.  Parity-green, but
+# measured slower on configs[1] (16.4 vs 13.4 ms, profiles/r01_summary.md section K), so it is opt-in.
+STFT_DFT256 = os.environ.get("SSB_STFT_DFT256", "0") == "1"
 ISTFT_TF, ISTFT_F32 = 1, 2
 
 
@@ -87,7 +91,7 @@ def stft(sig, rag, complex_out=False, layout_tf=False, log=False, out=None):
         call("stft_dft256", sig, tiles, int(tiles.shape[0]), out, stream_ptr())
         return out
     if rag.align != 1:
-        raise ValueError("an aligned Ragged layout is only read by the 256/64 magnitude path")
+        raise ValueError("an aligned Ragged layout is only read by the tensor-core 256/64 magnitude path (STFT_DFT256)")
     call("stft", sig, rag.d_sig_off, rag.d_frame_off, rag.d_stft_tiles, rag.n_utts, int(rag.stft_tiles[-1]),
          rag.n_fft, rag.hop, flags, out, stream_ptr())
     return out

@@ -53,6 +53,7 @@ def test_stft_dft256_matches_oracle_and_fft_kernel(align, monkeypatch):
     # tensor-core path (csrc/stft_mma.cu): tile boundaries (127/128/129 frames), the shortest legal utterance, lengths
     # that are not multiples of the hop, 16-byte aligned (fast loads) and back-to-back (scalar loads) layouts
     lens = [129, 127 * 64, 128 * 64 - 1, 128 * 64, 129 * 64 + 5, 300, 64 * 3 + 1, 40000, 12345, 257 * 64 + 63]
+    monkeypatch.setattr(ops, "STFT_DFT256", True)
     sigs = _corpus(11, lens)
     rag = ops.Ragged(lens, 256, 64, DEV, align=align)
     host = np.full(int(rag.sig_off[-1]), np.nan, dtype=np.float32)      # gaps must never be read
@@ -78,7 +79,8 @@ def test_stft_dft256_matches_oracle_and_fft_kernel(align, monkeypatch):
             assert mx2 <= 3e-5, (u, mx2)
 
 
-def test_stft_dft256_full_size_properties():
+def test_stft_dft256_full_size_properties(monkeypatch):
+    monkeypatch.setattr(ops, "STFT_DFT256", True)
     # BASELINE-sized shard: homogeneity |STFT(a x)| == a |STFT(x)|, agreement with the FFT kernel, and Parseval per
     # frame against the windowed samples of interior frames
     rng = np.random.default_rng(2)
