@@ -124,6 +124,18 @@ int ss_bias_prep(const float* b_ih, const float* b_hh, int n, int hidden, float*
 int ss_unpack(const float* packed, const long long* toff, int T, int B, int C, int c_src, int c_off, float* out,
               void* stream);
 
+/* On-device hand-offs (no .npz round trip between the stages).
+ * ss_ragged_to_padded: the (T_u, F) blocks ss_stft(LAYOUT_TF) writes -> the model's time-major padded input
+ * [T][B][F] (zeros past T_u); is_complex takes |X| of complex64 blocks on the way (np.abs, archs/uPIT.py:91).
+ * Utterance u of the ragged corpus becomes batch column u, so the corpus must be sorted by descending length
+ * like the collator's batches (archs/uPIT.py:40).
+ * ss_masks_to_ragged: head pre-activations z [T*B][ldz] -> sigmoid (archs/uPIT.py:144) -> the per-utterance,
+ * per-speaker (T_u, F) mask blocks ss_istft_masked(LAYOUT_TF) reads (archs/uPIT.py:220-225 without the files). */
+int ss_ragged_to_padded(const void* in, int is_complex, const long long* frame_off, int T, int B, int F, float* out,
+                        void* stream);
+int ss_masks_to_ragged(const float* z, long long ldz, const long long* frame_off, int T, int B, int F, int n_src,
+                       float* out, void* stream);
+
 /* ---- K2b/K2c: persistent bidirectional LSTM recurrence.  Replaces the sequential part of the cuDNN LSTM
  * behind nn.LSTM(..., bidirectional=True) at archs/uPIT.py:115,132 / archs/RSH.py:155,172 (PackedSequence
  * semantics via lens[], descending) and of its backward (steps/train_qsub.py:120) ----

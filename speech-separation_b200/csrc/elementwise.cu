@@ -275,3 +275,75 @@ extern "C" int ss_rsh_residual_bwd(const float* dx, const float* carry_in, const
       dx, carry_in, next_in, R, F, carry_out, dmask);
   return check_launch("ss_rsh_residual_bwd");
 }
+
+// ---- on-device hand-offs between the STFT / model / iSTFT stages ----
+namespace ssb {
+
+// Ragged (T_u, F) blocks -> time-major padded rows t*B + u, zeros past T_u.  COMPLEX input takes |X| on the way
+// (np.abs of the test-branch features, archs/uPIT.py:91), so the complex STFT is written once and read twice.
+template <bool COMPLEX>
+__global__ void __launch_bounds__(256) ragged_to_padded_kernel(const float* __restrict__ in,
+                                                               const long long* __restrict__ frame_off, int T, int B,
+                                                               int F, float* __restrict__ out) {
+  const long long n = (long long)T * B * F;
+  for (long long e = (long long)blockIdx.x * 256 + threadIdx.x; e < n; e += (long long)gridDim.x * 256) {
+    const long long r = e / F;
+    const int f = (int)(e - r * F);
+    const int t = (int)(r / B), u = (int)(r - (long long)t * B);
+    const long long fo = frame_off[u];
+    float v = 0.0f;
+    if (t < (int)(frame_off[u + 1] - fo)) {
+      const long long i = (fo + t) * F + f;
+      if (COMPLEX) {
+        const float2 z = reinterpret_cast<const float2*>(in)[i];
+        v = sqrtf(z.x * z.x + z.y * z.y);
+      } else {
+        v = in[i];
+      }
+    }
+    out[e] = v;
+  }
+}
+
+// Head pre-activations z [T*B][ldz] (speaker s in columns [s*F, (s+1)*F)) -> sigmoid -> the mask blocks
+// ss_istft_masked(LAYOUT_TF) reads: for utterance u, n_src blocks (T_u, F) starting at element frame_off[u]*n_src*F.
+__global__ void __launch_bounds__(256) masks_to_ragged_kernel(const float* __restrict__ z, long long ldz,
+                                                              const long long* __restrict__ frame_off, int T, int B,
+                                                              int F, int S, float* __restrict__ out) {
+  const long long n = (long long)T * B * S * F;
+  for (long long e = (long long)blockIdx.x * 256 + threadIdx.x; e < n; e += (long long)gridDim.x * 256) {
+    const long long r = e / (S * F);
+    const int c = (int)(e - r * (S * F));
+    const int t = (int)(r / B), u = (int)(r - (long long)t * B);
+    const long long fo = frame_off[u];
+    const int Tu = (int)(frame_off[u + 1] - fo);
+    if (t >= Tu) continue;
+    const int s = c / F, f = c - s * F;
+    out[(fo * S + (long long)s * Tu + t) * F + f] = sigmoidf_(z[r * ldz + c]);
+  }
+}
+
+}  // namespace ssb
+
+extern "C" int ss_ragged_to_padded(const void* in, int is_complex, const long long* frame_off, int T, int B, int F,
+                                   float* out, void* stream) {
+  using namespace ssb;
+  SS_REQUIRE(T > 0 && B > 0 && F > 0, "ss_ragged_to_padded: bad shape %d x %d x %d", T, B, F);
+  const long long n = (long long)T * B * F;
+  const int grid = (int)min((long long)148 * 8, (n + 255) / 256);
+  if (is_complex)
+    ragged_to_padded_kernel<true><<<grid, 256, 0, (cudaStream_t)stream>>>((const float*)in, frame_off, T, B, F, out);
+  else
+    ragged_to_padded_kernel<false><<<grid, 256, 0, (cudaStream_t)stream>>>((const float*)in, frame_off, T, B, F, out);
+  return check_launch("ss_ragged_to_padded");
+}
+
+extern "C" int ss_masks_to_ragged(const float* z, long long ldz, const long long* frame_off, int T, int B, int F,
+                                  int n_src, float* out, void* stream) {
+  using namespace ssb;
+  SS_REQUIRE(T > 0 && B > 0 && F > 0 && n_src > 0 && ldz >= (long long)n_src * F, "ss_masks_to_ragged: bad shape");
+  const long long n = (long long)T * B * n_src * F;
+  masks_to_ragged_kernel<<<(int)min((long long)148 * 8, (n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
+      z, ldz, frame_off, T, B, F, n_src, out);
+  return check_launch("ss_masks_to_ragged");
+}

@@ -121,6 +121,24 @@ def istft_masked(spec, mask, rag, n_src, layout_tf=False, out_f32=False, out=Non
     return out, wav_off
 
 
+def ragged_to_padded(flat, rag, T=None, out=None):
+    """(T_u, F) blocks (ss_stft LAYOUT_TF; float32 or complex64 -> |X|) -> time-major padded [T*B][F] model input."""
+    T = int(rag.T.max()) if T is None else int(T)
+    if out is None:
+        out = torch.empty(T * rag.n_utts, rag.F, dtype=torch.float32, device=flat.device)
+    call("ragged_to_padded", flat, int(flat.dtype == torch.complex64), rag.d_frame_off, T, rag.n_utts, rag.F, out,
+         stream_ptr())
+    return out
+
+
+def masks_to_ragged(z, ldz, rag, T, n_src, out=None):
+    """sigmoid of the head pre-activations [T*B][ldz] -> the (T_u, F) mask blocks istft_masked(layout_tf=True) reads."""
+    if out is None:
+        out = torch.empty(rag.total_frames * n_src * rag.F, dtype=torch.float32, device=z.device)
+    call("masks_to_ragged", z, LL(ldz), rag.d_frame_off, int(T), rag.n_utts, rag.F, int(n_src), out, stream_ptr())
+    return out
+
+
 class SB16:
     """Split-bf16 matrix [rows][cols] with pitch `ld` (elements): planes hi, lo in one bf16 buffer."""
 

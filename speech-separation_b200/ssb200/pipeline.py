@@ -1,0 +1,75 @@
+"""On-device pipelines around the model: waveforms in, loss or separated
+waveforms out, with no .npz round trip between the stages.
+
+The reference hands data from stage to stage through files: steps/extract_feats.py:86-90 writes (F, T) arrays,
+archs/uPIT.py:66-79 re-reads and transposes them, compute_masks (archs/uPIT.py:209-225) copies every utterance's
+mask to the host and compresses it, steps/reconstruct_sources.py:32-42 re-reads masks and complex features.  Here the
+same arithmetic runs back to back on the device: ss_stft(LAYOUT_TF) -> ss_ragged_to_padded -> BLSTM engine ->
+ss_masks_to_ragged -> ss_istft_masked, one host->device copy of the samples and one device->host copy of the int16
+audio.  The file-based CLIs (ssb200.extract_feats / reconstruct_sources) remain the drop-in for run_train.sh /
+run_eval.sh; tests check that both routes give the same numbers.
+"""
+import numpy as np
+import torch
+
+from . import ops
+from .uPIT import _to_device_async, run_forward
+
+
+def _order(wavs, hop):
+    """Collator order (archs/uPIT.py:40, ssb200/uPIT.py:Collator): descending number of frames."""
+    return [int(i) for i in np.argsort(np.array([1 + len(w) // hop for w in wavs]))[::-1]]
+
+
+def _upload(wavs, order, device):
+    flat = np.concatenate([np.asarray(wavs[i], dtype=np.float32) for i in order])
+    return torch.from_numpy(flat).pin_memory().to(device, non_blocking=True)
+
+
+def _batch(rag, mix_padded, device):
+    lens = rag.T.astype(np.int32)
+    return {"device_batch": True, "T": int(rag.T.max()), "B": rag.n_utts, "lens": lens,
+            "lens_dev": _to_device_async(lens, np.int32, device), "mix": mix_padded}
+
+
+def train_batch(mix_wavs, src_wavs, n_fft=512, hop=128, device="cuda"):
+    """f2: mixture and source waveforms -> the padded device batch compute_loss / loss_and_grads / Trainer.step take
+    in place of the collator's PackedSequences.  src_wavs[i][s] is source s of mixture i.
+    Returns (batch, order): batch column b holds mixture order[b]."""
+    order = _order(mix_wavs, hop)
+    rag = ops.Ragged([len(mix_wavs[i]) for i in order], n_fft, hop, device)
+    T, S = int(rag.T.max()), len(src_wavs[0])
+    mix = ops.stft(_upload(mix_wavs, order, device), rag, layout_tf=True)
+    batch = _batch(rag, ops.ragged_to_padded(mix, rag, T), device)
+    src = torch.empty(S, T * rag.n_utts, rag.F, dtype=torch.float32, device=device)
+    for s in range(S):
+        for i in order:
+            assert len(src_wavs[i][s]) == len(mix_wavs[i])
+        spec = ops.stft(_upload([w[s] for w in src_wavs], order, device), rag, layout_tf=True, out=mix)
+        ops.ragged_to_padded(spec, rag, T, out=src[s])
+    batch["src"] = src
+    return batch, order
+
+
+def separate(model, wavs, n_fft=512, hop=128, device=None):
+    """f3: list of mixture waveforms -> list of [n_spk] int16 waveforms (what run_eval.sh's feature extraction,
+    compute_masks and reconstruct_sources.py produce through files), uPIT-style models (mask columns [s*F, (s+1)*F))."""
+    device = model.lin.weight.device if device is None else device
+    S, F = model.num_spk, n_fft // 2 + 1
+    assert F == model.feat_dim and model.out_dim == S * F
+    order = _order(wavs, hop)
+    rag = ops.Ragged([len(wavs[i]) for i in order], n_fft, hop, device)
+    spec = ops.stft(_upload(wavs, order, device), rag, complex_out=True, layout_tf=True)
+    batch = _batch(rag, ops.ragged_to_padded(spec, rag), device)
+    model.hidden = model.init_hidden(batch["B"])
+    with torch.no_grad():
+        run_forward(model, batch, model.hidden, save=False)
+        ws = batch["ws"]
+        mask = ops.masks_to_ragged(ws.z, ws.ldz, rag, batch["T"], S)
+        wav, off = ops.istft_masked(spec, mask, rag, S, layout_tf=True)
+    host = wav.cpu().numpy()                                   # the only device->host copy
+    out = [None] * len(wavs)
+    for u, i in enumerate(order):
+        L = int(rag.L[u])
+        out[i] = [host[off[u] + s * L: off[u] + (s + 1) * L] for s in range(S)]
+    return out

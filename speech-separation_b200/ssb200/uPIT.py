@@ -159,6 +159,8 @@ def _to_device_async(arr, dtype, device):
 def unpack_batch(batch_sample, keys, device, src_keys=()):
     """PackedSequences -> time-major padded device tensors (rows t*B+b) + lengths.  `src_keys` are unpacked side by
     side into one (len(src_keys), T*B, F) tensor returned under 'src'."""
+    if isinstance(batch_sample, dict) and batch_sample.get("device_batch"):
+        return batch_sample               # already padded on the device (ssb200/pipeline.py: no PackedSequence hop)
     mix = batch_sample[keys[0]]
     assert isinstance(mix, PackedSequence)
     bs = mix.batch_sizes.numpy().astype(np.int64)

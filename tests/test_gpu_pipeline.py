@@ -1,0 +1,89 @@
+"""On-device pipelines (ssb200/pipeline.py) against the file-format route they
+short-cut: same loss / gradients as compute_loss on collated PackedSequences of oracle features, same int16 audio
+(+-1 LSB) as compute_masks -> oracle mask x mixture-phase iSTFT (steps/reconstruct_sources.py:35-42)."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import stft_oracle as so
+from ssb200 import pipeline, synth
+from ssb200 import uPIT as arch
+
+pytestmark = pytest.mark.gpu
+
+
+def _waves(seed, lens, S):
+    mixes, srcs = [], []
+    for b, n in enumerate(lens):
+        m, ss = synth.mixture(seed * 1000 + b, n, S)
+        mixes.append(m)
+        srcs.append(ss)
+    return mixes, srcs
+
+
+def _model(F, S, seed):
+    torch.manual_seed(seed)
+    return arch.SepDNN(0, feat_dim=str(F), num_spk=str(S)).cuda()
+
+
+@pytest.mark.parametrize("n_fft,hop,S", [(256, 64, 2), (512, 128, 3)])
+def test_train_batch_matches_collated_features(n_fft, hop, S):
+    F = n_fft // 2 + 1
+    lens = [9000, 12000, 7777, 12000 - 3 * hop, 5000]        # unsorted on purpose: the pipeline applies the collator order
+    mixes, srcs = _waves(5, lens, S)
+    model = _model(F, S, 1)
+    model.train()
+    # file-format route: oracle features -> dataset items -> Collator -> compute_loss
+    items = []
+    for m, ss in zip(mixes, srcs):
+        it = {"mix": so.stft_mag(m, n_fft, hop).T.copy()}
+        for s in range(S):
+            it["source%d" % (s + 1)] = so.stft_mag(ss[s], n_fft, hop).T.copy()
+        items.append(it)
+    packed = arch.Collator("mix")(items)
+    torch.manual_seed(77)
+    loss_a, norm_a = arch.compute_loss(model, 0, packed)
+    loss_a.backward()
+    grads_a = {k: v.grad.detach().clone() for k, v in model.named_parameters()}
+    idx_a = model.last["indices"].clone()
+    # device route
+    batch, order = pipeline.train_batch(mixes, srcs, n_fft, hop)
+    assert [1 + lens[i] // hop for i in order] == sorted((1 + n // hop for n in lens), reverse=True)
+    torch.manual_seed(77)
+    loss_b, norm_b = arch.compute_loss(model, 0, batch)
+    loss_b.backward()
+    assert torch.equal(model.last["indices"], idx_a)            # permutation choices bit-exact
+    assert float(norm_a) == float(norm_b)
+    assert abs(float(loss_a) - float(loss_b)) <= 1e-4 * abs(float(loss_a))
+    for k, v in model.named_parameters():
+        d = float((v.grad - grads_a[k]).norm() / (grads_a[k].norm() + 1e-30))
+        assert d <= 1e-3, (k, d)
+
+
+def test_separate_matches_file_route():
+    n_fft, hop, S = 512, 128, 2
+    F = n_fft // 2 + 1
+    lens = [16000, 9000, 12345, 16000 - 5 * hop]
+    mixes, _ = _waves(9, lens, S)
+    model = _model(F, S, 2)
+    model.eval()
+    torch.manual_seed(123)
+    got = pipeline.separate(model, mixes, n_fft, hop)
+    # file-format route with the same (h0, c0) draw: TestSet items -> Collator -> compute_masks -> oracle iSTFT
+    import tempfile
+    specs = [so.stft(m, n_fft, hop) for m in mixes]
+    items = [{"mix": np.abs(sp).T.copy(), "name": "u%d" % i} for i, sp in enumerate(specs)]
+    packed = arch.Collator("mix")(items)
+    with tempfile.TemporaryDirectory() as d:
+        torch.manual_seed(123)
+        arch.compute_masks(model, packed, d)
+        for i, sp in enumerate(specs):
+            z = np.load("%s/u%d.npz" % (d, i))
+            for s in range(S):
+                ref = so.masked_istft_int16(sp, z["s%d" % (s + 1)], hop)
+                g = got[i][s]
+                assert g.dtype == np.int16 and g.shape == ref.shape
+                diff = np.abs(g.astype(np.int64) - ref.astype(np.int64))
+                # masks differ by ~1e-6 between the routes (oracle vs CUDA STFT input), so a handful of samples sit on
+                # a truncation boundary
+                assert diff.max() <= 1 and (diff > 0).mean() < 0.02, (i, s, diff.max(), (diff > 0).mean())
