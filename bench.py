@@ -484,6 +484,39 @@ def run_istft(args, rank, local, world, n_utts=3000, n_src=2):
                          "algorithmic_bytes_per_frame_source": byts, "kernel_ms": round(kms, 3)}}
 
 
+def run_separate(args, rank, local, world):
+    """Evaluation end to end on the device (SURVEY 8 f3, ssb200/pipeline.py:separate): host waveforms -> STFT ->
+    BLSTM masks -> mask x mixture-phase iSTFT -> int16 audio on the host; what run_eval.sh does through three
+    programs and two sets of .npz files (steps/extract_feats.py test branch, compute_masks, reconstruct_sources.py)."""
+    import torch
+    from ssb200 import pipeline, uPIT
+    K, W = args.steps, args.warmup
+    torch.manual_seed(0)
+    model = uPIT.SepDNN(local, feat_dim=str(F), num_spk=str(S)).cuda()
+    model.eval()
+    rng = np.random.default_rng(11 + rank)
+    batches = []
+    for i in range(N_BATCHES):
+        lens = train_lengths(5000 + 1000 * rank + i, B_PER_GPU)
+        batches.append([rng.uniform(-0.3, 0.3, size=n).astype(np.float32) for n in lens])
+    audio = [sum(len(w) for w in b) / SR for b in batches]
+    sink = {}
+
+    def step(i):
+        sink["wav"] = pipeline.separate(model, batches[i % N_BATCHES], N_FFT, HOP)
+
+    ms, _ = timed_region(step, K, W, world)
+    tot = sum(audio[(W + i) % N_BATCHES] for i in range(K)) * world
+    nbytes = int(np.mean([sum(len(w) for w in b) for b in batches]))
+    return {"metric": "uPIT separation audio-sec/sec (waveform in, %d int16 waveforms out)" % S,
+            "value": round(tot / (ms / 1e3), 1), "unit": "audio-sec/sec", "n_gpus": world, "steps": K, "warmup": W,
+            "ms_per_step": round(ms / K, 3),
+            "config": {"workload": "eval of configs[2] shapes: %d utterances U[4,8] s per step, STFT %d/%d, S=%d, "
+                                   "h0/c0 random per batch like the reference" % (B_PER_GPU, N_FFT, HOP, S)},
+            "e2e": {"value": round(tot / (ms / 1e3), 1), "unit": "audio-sec/sec", "h2d_bytes_per_step": nbytes * 4,
+                    "d2h_bytes_per_step": nbytes * 2 * S}}
+
+
 # ---------------------------------------------------------------- reference arm (CPU, rank 0 only)
 def run_reference(args, rank, world):
     """`--impl reference`: the reference's CPU implementation of the path, on the host cores.  /root/reference is
@@ -519,7 +552,7 @@ def main():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--workload", default="train", choices=["train", "stft", "istft"])
+    ap.add_argument("--workload", default="train", choices=["train", "stft", "istft", "separate"])
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-extras", action="store_true", help="skip the stft/istft/cpu_baseline legs of the train line")
     args = ap.parse_args()
@@ -546,6 +579,8 @@ def main():
         line = run_stft(args, rank, local, world)
     elif args.workload == "istft":
         line = run_istft(args, rank, local, world)
+    elif args.workload == "separate":
+        line = run_separate(args, rank, local, world)
     else:
         line = run_train(args, rank, local, world)
         if not args.no_extras:
@@ -554,6 +589,8 @@ def main():
             line["stft"] = run_stft(sub, rank, local, world)
             torch.cuda.empty_cache()
             line["istft"] = run_istft(sub, rank, local, world)
+            torch.cuda.empty_cache()
+            line["separate"] = run_separate(sub, rank, local, world)
     if rank == 0 and world == 1 and not args.no_extras:
         if args.workload == "train":
             # 4 utterances per CPU step like the --impl reference arm (larger CPU batches run SLOWER per audio-second on
