@@ -97,6 +97,66 @@ def stft(sig, rag, complex_out=False, layout_tf=False, log=False, out=None):
     return out
 
 
+class _HostStream:
+    """Cached plan of stft_host: utterance chunks, their sub-corpora and two device buffers of each kind."""
+
+    def __init__(self, rag, chunks, complex_out):
+        tot = rag.total_frames
+        cuts = np.searchsorted(rag.frame_off, np.arange(1, chunks) * (tot / chunks))
+        self.bounds = np.unique(np.concatenate([[0], cuts, [rag.n_utts]])).astype(np.int64)
+        self.subs = [Ragged(rag.n_samples[a:b], rag.n_fft, rag.hop, rag.device, align=rag.align)
+                     for a, b in zip(self.bounds[:-1], self.bounds[1:])]
+        n_in = max(int(r.sig_off[-1]) for r in self.subs)
+        n_out = max(r.total_frames for r in self.subs) * rag.F
+        odt = torch.complex64 if complex_out else torch.float32
+        self.d_in = [torch.empty(n_in, dtype=torch.float32, device=rag.device) for _ in range(2)]
+        self.d_out = [torch.empty(n_out, dtype=odt, device=rag.device) for _ in range(2)]
+        self.streams = [torch.cuda.Stream(device=rag.device) for _ in range(3)]
+
+
+def stft_host(h_sig, rag, h_out, chunks=8, complex_out=False, layout_tf=False):
+    """Pinned host samples -> pinned host features (the whole job of steps/extract_feats.py:85-90 minus the file
+    IO): the corpus is cut into `chunks` runs of utterances and host->device copy, kernel and device->host copy of
+    consecutive runs overlap on three streams (PCIe is full duplex; the copies dominate end to end).  Returns after
+    the last copy has landed."""
+    assert h_sig.is_pinned() and h_out.is_pinned() and h_sig.numel() == int(rag.sig_off[-1])
+    key = (int(chunks), bool(complex_out))
+    plans = rag.__dict__.setdefault("_host_plans", {})
+    if key not in plans:
+        plans[key] = _HostStream(rag, chunks, complex_out)
+    pl = plans[key]
+    s_in, s_cmp, s_out = pl.streams
+    cur = torch.cuda.current_stream()
+    for st in pl.streams:
+        st.wait_stream(cur)
+    ev_cmp, ev_out = {}, {}
+    for c, sub in enumerate(pl.subs):
+        b = c & 1
+        a0, a1 = int(rag.sig_off[pl.bounds[c]]), int(rag.sig_off[pl.bounds[c + 1]])
+        f0, f1 = int(rag.frame_off[pl.bounds[c]]) * rag.F, int(rag.frame_off[pl.bounds[c + 1]]) * rag.F
+        d_in, d_out = pl.d_in[b][:a1 - a0], pl.d_out[b][:f1 - f0]
+        with torch.cuda.stream(s_in):
+            if c >= 2:
+                s_in.wait_event(ev_cmp[c - 2])                 # the kernel that read this buffer is done
+            d_in.copy_(h_sig[a0:a1], non_blocking=True)
+            ev_in = torch.cuda.Event()
+            ev_in.record(s_in)
+        with torch.cuda.stream(s_cmp):
+            s_cmp.wait_event(ev_in)
+            if c >= 2:
+                s_cmp.wait_event(ev_out[c - 2])                # the copy that read this output buffer is done
+            stft(d_in, sub, complex_out=complex_out, layout_tf=layout_tf, out=d_out)
+            ev_cmp[c] = torch.cuda.Event()
+            ev_cmp[c].record(s_cmp)
+        with torch.cuda.stream(s_out):
+            s_out.wait_event(ev_cmp[c])
+            h_out[f0:f1].copy_(d_out, non_blocking=True)
+            ev_out[c] = torch.cuda.Event()
+            ev_out[c].record(s_out)
+    s_out.synchronize()
+    return h_out
+
+
 def stft_views(flat, rag, layout_tf=False):
     """Per-utterance views of a flat STFT buffer."""
     F = rag.F

@@ -165,3 +165,18 @@ def test_stft_istft_roundtrip_full_size():
         a = x[int(rag.sig_off[u]):int(rag.sig_off[u]) + L]
         b = y[int(off[u]):int(off[u]) + L]
         assert float((a - b).abs().max()) <= 5e-6
+
+
+@pytest.mark.parametrize("chunks", [1, 3, 8])
+def test_stft_host_streaming_equals_single_launch(chunks):
+    # host -> host streaming over three streams gives bit-identical features to one launch over the whole corpus
+    rng = np.random.default_rng(8)
+    lens = rng.integers(3000, 20000, size=23)
+    rag = ops.Ragged(lens, 256, 64, DEV)
+    h_sig = (torch.rand(int(rag.sig_off[-1])) - 0.5).pin_memory()
+    h_out = torch.empty(rag.total_frames * rag.F, dtype=torch.float32).pin_memory()
+    for _ in range(2):                                       # second call reuses the cached plan and buffers
+        h_out.zero_()
+        ops.stft_host(h_sig, rag, h_out, chunks=chunks)
+        ref = ops.stft(h_sig.to(DEV), rag).cpu()
+        assert torch.equal(h_out, ref)
