@@ -21,9 +21,28 @@ def _order(wavs, hop):
     return [int(i) for i in np.argsort(np.array([1 + len(w) // hop for w in wavs]))[::-1]]
 
 
-def _upload(wavs, order, device):
-    flat = np.concatenate([np.asarray(wavs[i], dtype=np.float32) for i in order])
-    return torch.from_numpy(flat).pin_memory().to(device, non_blocking=True)
+_PINNED, _IN_FLIGHT = {}, {}
+
+
+def _pinned(tag, n, dtype):
+    """Grow-only pinned staging buffers: cudaHostAlloc per call costs more than the copies it feeds."""
+    buf = _PINNED.get(tag)
+    if buf is None or buf.numel() < n or buf.dtype != dtype:
+        buf = torch.empty(max(n, 1 << 16), dtype=dtype).pin_memory()
+        _PINNED[tag] = buf
+    return buf[:n]
+
+
+def _upload(wavs, order, device, tag="in"):
+    n = sum(len(wavs[i]) for i in order)
+    if tag in _IN_FLIGHT:
+        _IN_FLIGHT[tag].synchronize()                          # the last copy out of this staging buffer has finished
+    stage = _pinned(tag, n, torch.float32)
+    np.concatenate([np.asarray(wavs[i], dtype=np.float32) for i in order], out=stage.numpy())
+    dev = stage.to(device, non_blocking=True)
+    _IN_FLIGHT[tag] = torch.cuda.Event()
+    _IN_FLIGHT[tag].record()
+    return dev
 
 
 def _batch(rag, mix_padded, device):
@@ -45,7 +64,8 @@ def train_batch(mix_wavs, src_wavs, n_fft=512, hop=128, device="cuda"):
     for s in range(S):
         for i in order:
             assert len(src_wavs[i][s]) == len(mix_wavs[i])
-        spec = ops.stft(_upload([w[s] for w in src_wavs], order, device), rag, layout_tf=True, out=mix)
+        # (a second staging buffer: the previous upload may still be in flight)
+        spec = ops.stft(_upload([w[s] for w in src_wavs], order, device, tag="in%d" % (s & 1)), rag, layout_tf=True, out=mix)
         ops.ragged_to_padded(spec, rag, T, out=src[s])
     batch["src"] = src
     return batch, order
@@ -67,7 +87,10 @@ def separate(model, wavs, n_fft=512, hop=128, device=None):
         ws = batch["ws"]
         mask = ops.masks_to_ragged(ws.z, ws.ldz, rag, batch["T"], S)
         wav, off = ops.istft_masked(spec, mask, rag, S, layout_tf=True)
-    host = wav.cpu().numpy()                                   # the only device->host copy
+    stage = _pinned("out", wav.numel(), wav.dtype)
+    stage.copy_(wav, non_blocking=True)                        # the only device->host copy
+    torch.cuda.current_stream().synchronize()
+    host = stage.numpy().copy()
     out = [None] * len(wavs)
     for u, i in enumerate(order):
         L = int(rag.L[u])
