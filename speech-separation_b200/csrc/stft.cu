@@ -34,6 +34,10 @@ __device__ __forceinline__ float sqrt_approx(float x) {
   return r;
 }
 
+#ifndef SSB_STFT_SHFL
+#define SSB_STFT_SHFL 1   // partner bins by warp shuffle (0: through the shared-memory exchange buffer)
+#endif
+
 template <int P>
 __device__ __forceinline__ void fft_p(c2* v) {
   if (P == 8) fft8(v); else fft16(v);
@@ -179,6 +183,7 @@ __global__ void __launch_bounds__(StftCfg<NFFT>::THREADS, StftCfg<NFFT>::CTAS)
       // so each thread finishes the pairs of its own bins below M/2 (k2 < P/2) and only the upper bins travel
       // through the exchange buffer (natural order, re in [0, M/2), im in [M/2, M)).  The window table carries the
       // 1/2 of E and D.
+#if !SSB_STFT_SHFL
 #pragma unroll
       for (int a = 0; a < NA; ++a)
 #pragma unroll
@@ -187,6 +192,12 @@ __global__ void __launch_bounds__(StftCfg<NFFT>::THREADS, StftCfg<NFFT>::CTAS)
           scr[j + P * a + 16 * k2] = z[a][k2].im;
         }
       __syncwarp();
+#else
+      // The partner bin M - k of k = j + P a + 16 k2 lives in lane P - j of the same group as z[NA-1-a][P-1-k2]
+      // (j != 0), or in lane 0 itself as z[a][P - k2 - a] (j == 0): two 64-bit shuffles replace the trip through
+      // the exchange buffer (8 of the kernel's 63 shared-memory wavefronts per frame).
+      const int src_lane = (lane & ~(P - 1)) | ((P - j) & (P - 1));
+#endif
       const bool liveA = g < nt, liveB = STFT_HALF + g < nt;
       const int fa = g, fb = STFT_HALF + g;
       // one output bin of both frames
@@ -225,7 +236,13 @@ __global__ void __launch_bounds__(StftCfg<NFFT>::THREADS, StftCfg<NFFT>::CTAS)
 #pragma unroll
         for (int k2 = 0; k2 < P / 2; ++k2) {
           const int k = j + P * a + 16 * k2;                   // 0 <= k < M/2; the partner bin is M - k
+#if !SSB_STFT_SHFL
           const p2 bx = scr[(M / 2 - k) & (M / 2 - 1)], by = scr[M / 2 + ((M / 2 - k) & (M / 2 - 1))];
+#else
+          const c2 zo = z[NA - 1 - a][P - 1 - k2], zz = z[a][(P - k2 - a) & (P - 1)];   // (k = 0 reads junk, unused)
+          const p2 bx = __shfl_sync(0xffffffffu, j == 0 ? zz.re : zo.re, src_lane);
+          const p2 by = __shfl_sync(0xffffffffu, j == 0 ? zz.im : zo.im, src_lane);
+#endif
           const p2 zx = z[a][k2].re, zy = z[a][k2].im;
           const p2 ex = add2(zx, bx), dx = sub2(zx, bx), ey = sub2(zy, by), dy = add2(zy, by);
           const float2 w = ptw[k];
