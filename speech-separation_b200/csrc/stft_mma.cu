@@ -5,21 +5,26 @@
 // Algebra.  With the periodic Hann window w[n] = w[256-n], w[0] = 0 and a real frame x[0..255]:
 //   Re X[k] =  sum_{n=1..128} (w[n] cos(2 pi k n/256)) e[n],   e[n] = x[n] + x[256-n] (n < 128), e[128] = x[128]
 //   Im X[k] = -sum_{n=1..127} (w[n] sin(2 pi k n/256)) o[n],   o[n] = x[n] - x[256-n]
-// so a tile of 128 frames is  E[128 x 128] * C^T[128 x 129]  and  O[128 x 128] * S^T[128 x 128]  (K = n-1).  The
+// so a tile of 128 frames is  E[128 x 128] * C^T[128 x 128]  and  O[128 x 128] * S^T[128 x 128]  (K = n-1, bins 0..127;
+// the Nyquist bin X[128] = sum_n (-1)^n w[n] e[n] is real and summed outside the GEMMs).  The
 // window lives inside the basis (a diagonal scaling along K), the fold halves the flops of a plain 256-point DFT
 // matrix, and every operand is split-bf16 (hi + lo) with the three products hi*hi + hi*lo + lo*hi accumulated in
 // fp32 in TMEM (error ~2^-16, inside the 1e-4 feature bar).
 //
-// One persistent CTA per SM, 17 warps:
-//   warps 0..7   producers: half a warp per frame and K block; two LDG.128 (x[n..n+3] and the mirrored quad) per
-//                lane, fold, split into hi/lo bf16 and 8-byte stores into the 128B-swizzled K-major A stage.  The odd
-//                part o stays packed in registers until its stage is free, so every sample is loaded once per frame.
-//   warp 8       one thread issues the MMAs (M=128, N=144 cos / N=128 sin, K=16; 48 per tile) and the commits
-//   warps 9..16  epilogue: TMEM -> sqrt(re^2 + im^2) -> (F, T_u) rows of the utterance; a warp stores 32 consecutive
-//                frames of one bin (128 contiguous bytes)
-// Shared memory: the 132 KB basis image (loaded once per CTA by bulk copies), two 32 KB A stages cycling through
-// (E, kb0), (O, kb0), (E, kb1), (O, kb1).  TMEM: three 144-column accumulator slots; tile i uses slots 2i%3 (cos)
-// and (2i+1)%3 (sin), so the cos GEMM of tile i+1 runs while the epilogue drains tile i.
+// One persistent CTA per SM, 21 warps:
+//   warps 0..15  producers: half a warp per frame and 64-wide K block; two LDG.128 (x[n..n+3] and the mirrored quad)
+//                per lane, fold, split into hi/lo bf16, 8-byte stores into a 128B-swizzled K-major A stage.  The odd
+//                part o stays packed in registers until the next ring slot is free, so every sample is loaded once
+//                per frame.  The same warps sum the Nyquist bin, sum_n (-1)^n w[n] e[n], on the FMA pipe (16-lane
+//                shuffle reduction per frame) so that both GEMMs are N = 128 and TMEM holds two full accumulator sets.
+//   warp 16      one thread issues the MMAs (M=128, N=128, K=16; 48 per tile) and the commits
+//   warps 17..20 epilogue: pipelined tcgen05.ld -> sqrt(re^2 + im^2) -> (F, T_u) rows of the utterance; a warp
+//                stores 32 consecutive frames of one bin (128 contiguous bytes)
+// Shared memory: the 128 KB basis image (cos hi | cos lo | sin hi | sin lo, bins 0..127, loaded once per CTA by bulk
+// copies) and a ring of three 32 KB A stages that the fills E(kb0), O(kb0), E(kb1), O(kb1), ... go round.
+// TMEM: 2 x (128 cos + 128 sin) columns; the epilogue drains tile i while the MMAs of tile i+1 run.
+// Measured (profiles/r01_summary.md section K): parity <= 3e-5 against the oracle, 16.4 ms on configs[1] against the
+// FFT kernel's 13.4 ms -- the MMAs take 5.8 ms alone, the producers 10.3 ms alone -- hence opt-in.
 #include "../../include/ssb200.h"
 #include "common.cuh"
 
