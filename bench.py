@@ -379,6 +379,35 @@ def cpu_stft_sample(budget_s=8.0):
     return frames / (time.perf_counter() - t0), n, 1
 
 
+def _cpu_stft_worker(args):
+    seed, budget_s = args
+    from oracle import stft_oracle
+    lens = stft_corpus_lengths(64, seed=seed)
+    rng = np.random.default_rng(seed)
+    sigs = [rng.standard_normal(int(n)).astype(np.float32) * 0.1 for n in lens[:16]]
+    stft_oracle.stft_mag(sigs[0], STFT_NFFT, STFT_HOP)
+    t0 = time.perf_counter()
+    frames = n = 0
+    while time.perf_counter() - t0 < budget_s:
+        frames += stft_oracle.stft_mag(sigs[n % len(sigs)], STFT_NFFT, STFT_HOP).shape[1]
+        n += 1
+    return frames, time.perf_counter() - t0
+
+
+def cpu_stft_pool_sample(budget_s=4.0):
+    """The same per-utterance loop in os.cpu_count() worker processes, the way steps/extract_feats.sh:41-48 fans the
+    reference out over --nj SGE tasks.  Returns (aggregate frames/sec, workers)."""
+    import multiprocessing as mp
+    n = os.cpu_count() or 1
+    try:
+        with mp.get_context("spawn").Pool(n) as pool:
+            res = pool.map_async(_cpu_stft_worker, [(100 + i, budget_s) for i in range(n)]).get(timeout=budget_s + 90)
+    except Exception as e:                                     # a reported baseline must never take the bench line down
+        sys.stderr.write("cpu_stft_pool_sample failed: %r\n" % (e,))
+        return None, n
+    return sum(f / t for f, t in res), n
+
+
 def run_stft(args, rank, local, world, n_mix=20000, e2e_mix=2000):
     """value: the WHOLE corpus (n_mix x 3 signals / world per rank) resident in HBM, one launch per step.
     e2e: a shard of e2e_mix mixtures through pinned host buffers (H2D of the audio + D2H of the features inside
@@ -596,10 +625,18 @@ def main():
             fps, n, c1 = cpu_stft_sample(5.0)
             line["stft"]["cpu_baseline"] = {"value": round(fps, 0), "unit": "frames/sec", "cores": c1, "kind": "port",
                                             "sample": "%d utterances, single process" % n}
+            pfps, pw = cpu_stft_pool_sample(3.0)
+            if pfps is not None:
+                line["stft"]["cpu_baseline_pool"] = {"value": round(pfps, 0), "unit": "frames/sec", "cores": pw, "kind": "port",
+                                                 "sample": "%d worker processes x 3 s, one utterance at a time each" % pw}
         elif args.workload == "stft":
             fps, n, c1 = cpu_stft_sample(10.0)
             line["cpu_baseline"] = {"value": round(fps, 0), "unit": "frames/sec", "cores": c1, "kind": "port",
                                     "sample": "%d utterances, single process" % n}
+            pfps, pw = cpu_stft_pool_sample(5.0)
+            if pfps is not None:
+                line["cpu_baseline_pool"] = {"value": round(pfps, 0), "unit": "frames/sec", "cores": pw, "kind": "port",
+                                         "sample": "%d worker processes x 5 s, one utterance at a time each" % pw}
     if rank == 0:
         sys.stdout.flush()
         emit(line)
