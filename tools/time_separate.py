@@ -9,10 +9,14 @@ sys.path.insert(0, "speech-separation_b200")
 from ssb200 import ops, pipeline, uPIT  # noqa: E402
 from ssb200.uPIT import run_forward  # noqa: E402
 
+import os  # noqa: E402
+
+LOCAL = int(os.environ.get("LOCAL_RANK", "0"))             # under torchrun: one process per GPU, all timing at once
+torch.cuda.set_device(LOCAL)
 N_FFT, HOP, S, B = 512, 128, 2, 64
 F = N_FFT // 2 + 1
 torch.manual_seed(0)
-model = uPIT.SepDNN(0, feat_dim=str(F), num_spk=str(S)).cuda().eval()
+model = uPIT.SepDNN(LOCAL, feat_dim=str(F), num_spk=str(S)).cuda().eval()
 rng = np.random.default_rng(0)
 wavs = [rng.uniform(-0.3, 0.3, size=int(n)).astype(np.float32) for n in rng.integers(32000, 64001, size=B)]
 for _ in range(3):
@@ -53,4 +57,5 @@ for _ in range(R):
     t = lap("D2H", t)
     out = [[host[off[u] + s * int(rag.L[u]): off[u] + (s + 1) * int(rag.L[u])] for s in range(S)] for u in range(B)]
     t = lap("slices", t)
-print({k: round(v / R, 3) for k, v in acc.items()}, "total", round(sum(acc.values()) / R, 3))
+print("rank", LOCAL, "threads", torch.get_num_threads(), {k: round(v / R, 3) for k, v in acc.items()}, "total",
+      round(sum(acc.values()) / R, 3), flush=True)
