@@ -17,7 +17,8 @@ __global__ void __launch_bounds__(256) bn_partial_kernel(const __nv_bfloat16* __
   if (c >= C) return;
   const int r0 = blockIdx.y * BN_ROWS, r1 = min(R, r0 + BN_ROWS);
   float a = 0.0f, b = 0.0f;
-  for (int r = r0; r < r1; ++r) {
+#pragma unroll 8
+  for (int r = r0; r < r1; ++r) {                              // 8 rows of loads in flight per thread
     const long long o = (long long)r * ld + c;
     const float v = join_bf16(x[o], x[o + plane]);
     if (dy) {
@@ -120,6 +121,32 @@ __global__ void __launch_bounds__(256) bn_bwd_apply_kernel(float* __restrict__ d
 }
 
 // dW[o][c] = s_c * (G[o][c] - mean_c * dsum[o]) + beta_c * dsum[o]   with G = dz^T x
+// the same on four consecutive columns per thread (C, ld, plane multiples of 4): 16-byte dy accesses, 8-byte bf16 loads
+__global__ void __launch_bounds__(256) bn_bwd_apply4_kernel(float* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
+                                                            long long ld, long long plane, unsigned int nq, int C4,
+                                                            const float* __restrict__ coef,
+                                                            const float* __restrict__ bwd) {
+  const int C = 4 * C4;
+  for (unsigned int q = blockIdx.x * 256u + threadIdx.x; q < nq; q += gridDim.x * 256u) {
+    const unsigned int r = q / (unsigned int)C4;
+    const int c = 4 * (int)(q - r * (unsigned int)C4);
+    const long long o = (long long)r * ld + c;
+    const uint2 h = *reinterpret_cast<const uint2*>(x + o), l = *reinterpret_cast<const uint2*>(x + o + plane);
+    float4 g = reinterpret_cast<float4*>(dy)[q];
+    const float4 s = *reinterpret_cast<const float4*>(coef + c), m = *reinterpret_cast<const float4*>(coef + 2 * C + c);
+    const float4 b0 = *reinterpret_cast<const float4*>(bwd + c), b1 = *reinterpret_cast<const float4*>(bwd + C + c);
+    const float v0 = __uint_as_float(h.x << 16) + __uint_as_float(l.x << 16);
+    const float v1 = __uint_as_float(h.x & 0xffff0000u) + __uint_as_float(l.x & 0xffff0000u);
+    const float v2 = __uint_as_float(h.y << 16) + __uint_as_float(l.y << 16);
+    const float v3 = __uint_as_float(h.y & 0xffff0000u) + __uint_as_float(l.y & 0xffff0000u);
+    g.x = s.x * g.x + b0.x * (v0 - m.x) + b1.x;
+    g.y = s.y * g.y + b0.y * (v1 - m.y) + b1.y;
+    g.z = s.z * g.z + b0.z * (v2 - m.z) + b1.z;
+    g.w = s.w * g.w + b0.w * (v3 - m.w) + b1.w;
+    reinterpret_cast<float4*>(dy)[q] = g;
+  }
+}
+
 __global__ void __launch_bounds__(256) head_dw_fix_kernel(const float* __restrict__ G, const float* __restrict__ dsum,
                                                           const float* __restrict__ coef,
                                                           const float* __restrict__ beta, int O, int C,
@@ -163,8 +190,15 @@ extern "C" int ss_bn_bwd(float* dy, const void* x, long long ld, long long plane
   bn_partial_kernel<<<dim3(cdiv(C, 256), parts), 256, 0, st>>>((const __nv_bfloat16*)x, ld, plane, dy, R, C, partial);
   bn_bwd_final_kernel<<<cdiv(C, 256), 256, 0, st>>>(partial, parts, R, C, coef, training, dgamma, dbeta, bwd);
   const long long n = (long long)R * C;
-  bn_bwd_apply_kernel<<<(int)min((long long)148 * 8, (n + 255) / 256), 256, 0, st>>>(dy, (const __nv_bfloat16*)x, ld, plane,
-                                                                                    n, C, coef, bwd);
+  const bool vec4 = C % 4 == 0 && ld % 4 == 0 && plane % 4 == 0 && n / 4 < 0xffffffffll &&
+                    ((reinterpret_cast<uintptr_t>(dy) | reinterpret_cast<uintptr_t>(coef) | reinterpret_cast<uintptr_t>(bwd)) & 15) == 0 &&
+                    (reinterpret_cast<uintptr_t>(x) & 7) == 0;
+  if (vec4)
+    bn_bwd_apply4_kernel<<<(int)min((long long)148 * 8, (n / 4 + 255) / 256), 256, 0, st>>>(
+        dy, (const __nv_bfloat16*)x, ld, plane, (unsigned int)(n / 4), C / 4, coef, bwd);
+  else
+    bn_bwd_apply_kernel<<<(int)min((long long)148 * 8, (n + 255) / 256), 256, 0, st>>>(dy, (const __nv_bfloat16*)x, ld,
+                                                                                      plane, n, C, coef, bwd);
   return check_launch("ss_bn_bwd");
 }
 
