@@ -8,12 +8,21 @@ import torch
 from ._lib import LL, call, lib, stream_ptr
 
 
+def _small(a, dtype, device):
+    """Offset tables -> device through pinned memory: a pageable host->device copy makes the driver wait for everything
+    already queued on the stream, which would serialise the host side of batch i+1 behind the kernels of batch i."""
+    t = torch.from_numpy(np.ascontiguousarray(np.asarray(a, dtype=dtype)))
+    if torch.device(device).type != "cuda":
+        return t
+    return t.pin_memory().to(device, non_blocking=True)
+
+
 def _i64(a, device):
-    return torch.as_tensor(np.asarray(a, dtype=np.int64), device=device)
+    return _small(a, np.int64, device)
 
 
 def _i32(a, device):
-    return torch.as_tensor(np.asarray(a, dtype=np.int32), device=device)
+    return _small(a, np.int32, device)
 
 
 def up8(n):

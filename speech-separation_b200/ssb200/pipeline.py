@@ -71,28 +71,53 @@ def train_batch(mix_wavs, src_wavs, n_fft=512, hop=128, device="cuda"):
     return batch, order
 
 
-def separate(model, wavs, n_fft=512, hop=128, device=None):
-    """f3: list of mixture waveforms -> list of [n_spk] int16 waveforms (what run_eval.sh's feature extraction,
-    compute_masks and reconstruct_sources.py produce through files), uPIT-style models (mask columns [s*F, (s+1)*F))."""
+_PENDING = {}
+
+
+def submit(model, wavs, n_fft=512, hop=128, device=None, slot=0):
+    """First half of `separate`: uploads the waveforms and enqueues STFT, model, masks, iSTFT and the copy of the int16
+    audio into pinned memory on the current stream, without waiting.  Returns a handle for `collect`.  Two slots used
+    alternately let the host side of batch i+1 (ordering, concatenation, h0/c0 draw, launches) run while the device
+    works on batch i -- the evaluation counterpart of Trainer.prefetch."""
+    if slot in _PENDING:
+        raise RuntimeError("pipeline.submit: slot %d still holds a batch that was not collected" % slot)
     device = model.lin.weight.device if device is None else device
     S, F = model.num_spk, n_fft // 2 + 1
     assert F == model.feat_dim and model.out_dim == S * F
     order = _order(wavs, hop)
     rag = ops.Ragged([len(wavs[i]) for i in order], n_fft, hop, device)
-    spec = ops.stft(_upload(wavs, order, device), rag, complex_out=True, layout_tf=True)
+    spec = ops.stft(_upload(wavs, order, device, tag="in%d" % slot), rag, complex_out=True, layout_tf=True)
     batch = _batch(rag, ops.ragged_to_padded(spec, rag), device)
     model.hidden = model.init_hidden(batch["B"])
     with torch.no_grad():
-        run_forward(model, batch, model.hidden, save=False)
+        run_forward(model, batch, model.hidden, save=False)     # one workspace: the stream orders the batches
         ws = batch["ws"]
         mask = ops.masks_to_ragged(ws.z, ws.ldz, rag, batch["T"], S)
         wav, off = ops.istft_masked(spec, mask, rag, S, layout_tf=True)
-    stage = _pinned("out", wav.numel(), wav.dtype)
+    stage = _pinned("out%d" % slot, wav.numel(), wav.dtype)
     stage.copy_(wav, non_blocking=True)                        # the only device->host copy
-    torch.cuda.current_stream().synchronize()
-    host = stage.numpy().copy()
-    out = [None] * len(wavs)
-    for u, i in enumerate(order):
-        L = int(rag.L[u])
+    done = torch.cuda.Event()
+    done.record()
+    h = {"slot": slot, "done": done, "stage": stage, "off": off, "order": order, "L": rag.L, "S": S, "n": len(wavs),
+         "keep": (spec, mask, wav)}                            # device buffers stay referenced until the copy is done
+    _PENDING[slot] = h
+    return h
+
+
+def collect(h):
+    """Second half of `separate`: waits for the batch of `h` and returns its waveforms in the caller's order."""
+    h["done"].synchronize()
+    host = h["stage"].numpy().copy()
+    _PENDING.pop(h["slot"], None)
+    h["keep"] = None
+    out, off, S = [None] * h["n"], h["off"], h["S"]
+    for u, i in enumerate(h["order"]):
+        L = int(h["L"][u])
         out[i] = [host[off[u] + s * L: off[u] + (s + 1) * L] for s in range(S)]
     return out
+
+
+def separate(model, wavs, n_fft=512, hop=128, device=None):
+    """f3: list of mixture waveforms -> list of [n_spk] int16 waveforms (what run_eval.sh's feature extraction,
+    compute_masks and reconstruct_sources.py produce through files), uPIT-style models (mask columns [s*F, (s+1)*F))."""
+    return collect(submit(model, wavs, n_fft, hop, device))

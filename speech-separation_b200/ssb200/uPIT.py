@@ -108,7 +108,10 @@ class SepDNN(nn.Module):
         h = torch.randn(2 * 2, batch_size, HID)
         c = torch.randn(2 * 2, batch_size, HID)
         dev = self.lin.weight.device
-        return h.to(dev), c.to(dev)
+        if dev.type != "cuda":
+            return h.to(dev), c.to(dev)
+        # through pinned memory: a pageable copy would wait for everything already queued on the stream
+        return h.pin_memory().to(dev, non_blocking=True), c.pin_memory().to(dev, non_blocking=True)
 
     # ---- engine plumbing ----
     def param_dict(self):

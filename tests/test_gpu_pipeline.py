@@ -87,3 +87,29 @@ def test_separate_matches_file_route():
                 # masks differ by ~1e-6 between the routes (oracle vs CUDA STFT input), so a handful of samples sit on
                 # a truncation boundary
                 assert diff.max() <= 1 and (diff > 0).mean() < 0.02, (i, s, diff.max(), (diff > 0).mean())
+
+
+def test_submit_collect_two_slots_equal_separate():
+    # batch i+1 submitted before batch i is collected: same audio as the blocking call with the same (h0, c0) draws
+    n_fft, hop, S = 256, 64, 2
+    model = _model(n_fft // 2 + 1, S, 4)
+    model.eval()
+    sets = [_waves(20 + k, [7000 + 500 * k, 9000, 6100], S)[0] for k in range(3)]
+    torch.manual_seed(5)
+    ref = [pipeline.separate(model, w, n_fft, hop) for w in sets]
+    torch.manual_seed(5)
+    got, pending = [], None
+    for k, w in enumerate(sets):
+        h = pipeline.submit(model, w, n_fft, hop, slot=k & 1)
+        if pending is not None:
+            got.append(pipeline.collect(pending))
+        pending = h
+    got.append(pipeline.collect(pending))
+    for a, b in zip(ref, got):
+        for ua, ub in zip(a, b):
+            for sa, sb in zip(ua, ub):
+                assert np.array_equal(sa, sb)
+    h = pipeline.submit(model, sets[0], n_fft, hop, slot=0)
+    with pytest.raises(RuntimeError):
+        pipeline.submit(model, sets[1], n_fft, hop, slot=0)
+    pipeline.collect(h)
