@@ -106,7 +106,7 @@ class ClockSampler:
 # kernels launched per C-ABI call (memsets not counted); default 1
 KERNELS_PER_CALL = {"colsum_sb16": 2, "bn_stats": 2, "bn_bwd": 3, "grad_norm": 2,
                     # host-side knobs / stream ops of the C ABI: no kernel
-                    "lstm_bwd_start_flag": 0, "stream_wait_value32": 0, "gemm_sm_limit": 0}
+                    "stream_wait_value32": 0}
 
 
 class CallMeter:
@@ -250,7 +250,6 @@ def run_train(args, rank, local, world):
     hbm, tf_burst, tf_sus, peak_src = peaks()
     torch.manual_seed(0)
     model = uPIT.SepDNN(local, feat_dim=str(F), num_spk=str(S)).cuda()
-    model.max_workspaces = N_BATCHES
     trainer = train.Trainer(model, uPIT)
     meter = CallMeter()
     coll = uPIT.Collator("mix")
@@ -302,10 +301,11 @@ def run_train(args, rank, local, world):
     fr = float(np.mean(frames[:PROF]))
     gemm_fl, rec_fl = train_flops_per_frame()
     rl = {}
-    if "gemm_sb16_x2" in prof:           # the batched weight-gradient launches belong to the same kernel
-        g, x = prof.setdefault("gemm_sb16", {"calls_per_step": 0, "ms_per_step": 0.0, "ms_per_call": 0.0}), prof.pop("gemm_sb16_x2")
-        g["calls_per_step"] += x["calls_per_step"]
-        g["ms_per_step"] += x["ms_per_step"]
+    for other in ("gemm_sb16_x2", "gemm_sb16_tn"):   # the batched / weight-gradient launches are the same kernel template
+        if other in prof:
+            g, x = prof.setdefault("gemm_sb16", {"calls_per_step": 0, "ms_per_step": 0.0, "ms_per_call": 0.0}), prof.pop(other)
+            g["calls_per_step"] += x["calls_per_step"]
+            g["ms_per_step"] += x["ms_per_step"]
     for name, fl in (("gemm_sb16", gemm_fl), ("lstm_fwd", rec_fl / 3), ("lstm_bwd", rec_fl / 3)):
         if name in prof:
             a = fl * fr / (prof[name]["ms_per_step"] * 1e-3) / 1e12
@@ -518,7 +518,6 @@ def run_separate(args, rank, local, world):
     torch.manual_seed(0)
     model = uPIT.SepDNN(local, feat_dim=str(F), num_spk=str(S)).cuda()
     model.eval()
-    model.max_workspaces = N_BATCHES     # one workspace per distinct (T, B): no device allocation inside the timed region
     rng = np.random.default_rng(11 + rank)
     batches = []
     for i in range(N_BATCHES):

@@ -20,7 +20,7 @@
 extern "C" {
 #endif
 
-#define SSB200_VERSION 1
+#define SSB200_VERSION 2
 
 /* ---- library ---- */
 const char* ss_last_error(void);
@@ -70,13 +70,34 @@ int ss_istft_masked(const void* spec, const float* mask, const long long* frame_
 #define SS_ROWMAP_UNIT4 1 /* m = 4*u + gate  ->  output row gate*hidden + u (undo the gate interleave) */
 int ss_gemm_sb16(const void* A, long long lda, long long a_plane, const void* B, long long ldb, long long b_plane,
                  float* C, long long ldc, int M, int N, int K, const float* bias, float alpha, float beta, int rowmap,
-                 int hidden, void* stream);
+                 int hidden, int sm_limit, void* stream);
 
-/* Two problems of the same shape in one launch (the two LSTM directions' weight gradients): entry z in {0,1} reads
- * A rows [z*a_batch_rows, +M) and B rows [z*b_batch_rows, +N) of the same sb16 matrices and writes Cz. */
+/* Two problems of the same shape in one launch: entry z in {0,1} reads A rows [z*a_batch_rows, +M) and B rows
+ * [z*b_batch_rows, +N) of the same sb16 matrices and writes Cz (bias[n] is shared).
+ * sm_limit > 0 (all ss_gemm_* entry points) caps the grid to that many CTAs: the GEMM then runs beside a resident
+ * recurrence kernel on the SMs that kernel leaves idle; 0 = every SM. */
 int ss_gemm_sb16_x2(const void* A, long long lda, long long a_plane, int a_batch_rows, const void* B, long long ldb,
                     long long b_plane, int b_batch_rows, float* C0, float* C1, long long ldc, int M, int N, int K,
-                    float alpha, float beta, int rowmap, int hidden, void* stream);
+                    const float* bias, float alpha, float beta, int rowmap, int hidden, int sm_limit, void* stream);
+
+/* Weight-gradient form ("TN"): both operands are stored with the REDUCTION index r = t*B + b as their row, exactly as
+ * the forward / backward kernels write activations and gate gradients -- no transposed copy exists anywhere.
+ *   Cz[rowmap(m)][n] = alpha * sum_r A[r][a_col0 + z*a_col_batch + m] * B[r + b_shift_z][b_col0 + z*b_col_batch + n]
+ *                      + beta * Cz[..][n]
+ * with r running over the n_blk blocks of 64 rows that start at block blk0_z (per entry z; batch = 1 or 2), so a sum
+ * over all R rows can be accumulated chunk by chunk (beta = 1) while a recurrence kernel is still producing rows.
+ * A: sb16 [R][a_cols] (pitch lda), B: sb16 [R][b_cols] (pitch ldb); rows outside [0, R) read as zero, which is
+ * what makes b_shift = -/+B express h_prev[t] = out[t -/+ 1] for dW_hh (the h0 term: ss_dwhh_edge).
+ * Replaces the autograd backward GEMMs of nn.LSTM / nn.Linear weights (steps/train_qsub.py:120). */
+int ss_gemm_sb16_tn(const void* A, long long lda, long long a_plane, int a_cols, int a_col0, int a_col_batch,
+                    const void* B, long long ldb, long long b_plane, int b_cols, int b_col0, int b_col_batch, int R,
+                    int blk0_z0, int blk0_z1, int n_blk, int b_shift_z0, int b_shift_z1, int batch, float* C0, float* C1,
+                    long long ldc, int M, int N, float alpha, float beta, int rowmap, int hidden, int sm_limit,
+                    void* stream);
+/* dW_hh[z][gate*H+u][j] += sum_b dG[row_z(b)][z*4H + 4u+gate] * h0[z][b][j], row_0(b) = b, row_1(b) = (len_b-1)*B + b:
+ * the first frame each direction processes carries h0, which no row of `out` holds. */
+int ss_dwhh_edge(const void* dG, long long ld, long long plane, const int* lens, const float* h0, int B, int H,
+                 float* dW0, float* dW1, long long ldw, void* stream);
 
 /* ---- layout / precision conversion kernels (plumbing around the GEMMs) ----
  * ss_split: fp32 in[R][C] (pitch ld_in) -> sb16 out[rp(r)][C] (pitch ld_out, plane out_plane) and/or the
@@ -99,7 +120,7 @@ int ss_colsum_sb16(const void* in, long long ld, long long plane, int R, int C, 
  * bitmask used[B], idx = argmin, used updated.  stats[4] = {sum_b min/S, sum_b len_b*F, loss = [0]/[1], 1/(S*[1])},
  * accumulated over calls when accumulate != 0 (RSH.py:240-241).
  * bwd (gout NULL = 1): dz = (2*(m*x - src[assign])*x*stats[3]*gout[0] + dmask_extra) * m*(1-m), as sb16 [T*B][ld_dz] and
- * transposed sb16 [n_out*F][ld_dzT]; rows with t >= len_b are zero. */
+ * (dzT != NULL) transposed sb16 [n_out*F][ld_dzT]; rows with t >= len_b are zero. */
 int ss_pit_chunks(int T);
 int ss_pit_loss_fwd(const float* z, long long ldz, const float* mix, const float* src, const int* lens, int T, int B,
                     int F, int n_out, int n_src, float* mask_out, float* partial, void* stream);
@@ -142,33 +163,34 @@ int ss_masks_to_ragged(const float* z, long long ldz, const long long* frame_off
  * Gate columns are interleaved: column dir*4H + 4*u + gate (gate order i,f,g,o as torch).
  * fwd: gx [T*B][8H] = x W_ih^T + b_ih + b_hh (both directions) is overwritten with the activated gates;
  *      whh_r sb16 [8H][H] (rows dir*4H+4u+gate); h0,c0,hn,cn [2][B][H]; out sb16 [T*B][2H] (zero at t>=len_b);
- *      training extras (all or none): outT, hprevT sb16 [2H][ldT] (transposed outputs / pre-step states), cs.
- *      ws: ss_lstm_ws_bytes(B,H) bytes.
+ *      cs [T*B][2H] cell states (training; may be NULL).  ws: ss_lstm_ws_bytes(B,H) bytes.
  * bwd: dout [T*B][2H] gradient wrt out; whhT sb16 [2H][4H] (row dir*H+j, column 4u+gate);
- *      dG sb16 [T*B][8H] and dGT sb16 [8H][ldT] gate pre-activation gradients (zero at t>=len_b);
- *      dhn,dcn (optional) gradient wrt (hn,cn); dh0,dc0 (optional) gradient wrt (h0,c0). */
+ *      dG sb16 [T*B][8H] gate pre-activation gradients (zero at t>=len_b);
+ *      dhn,dcn (optional) gradient wrt (hn,cn); dh0,dc0 (optional) gradient wrt (h0,c0).
+ * progress (optional, both): two counters, one per direction; while it runs the kernel stores
+ *      progress[d] = prog_base + (number of steps of direction d whose out / dG rows are globally visible), every few
+ *      steps (never the last ones: kernel completion covers those).  Direction 0 forward and direction 1 backward walk
+ *      t = 0..T-1, the other two T-1..0.  Work on another stream gated with ss_stream_wait_value32 (cyclic >=, so
+ *      prog_base may grow from launch to launch without ever being reset) can consume finished frames while the
+ *      recurrence is still running: engine.py streams the next GEMM through the SMs the recurrence leaves idle. */
 long long ss_lstm_ws_bytes(int B, int H);
 int ss_lstm_fwd(float* gx, const void* whh_r, long long whh_ld, long long whh_plane, const float* h0, const float* c0,
-                const int* lens, void* out, long long out_plane, void* outT, void* hprevT, long long ldT,
-                long long outT_plane, float* cs, float* hn, float* cn, void* ws, int T, int B, int H, void* stream);
-/* The transposed sb16 copies the weight-gradient GEMMs read, as separate calls (ss_lstm_fwd with outT = hprevT = NULL
- * and ss_lstm_bwd with dGT = NULL skip them): out[c][r] = in[r][c] for both planes; hprevT[d*H+j][t*B+b] = the state
- * direction d carried INTO frame t of row b (h0 at the row's first processed frame, zero at t >= len_b). */
+                const int* lens, void* out, long long out_plane, float* cs, float* hn, float* cn, void* ws,
+                unsigned int* progress, unsigned int prog_base, int T, int B, int H, void* stream);
+int ss_lstm_bwd(const float* gates, const float* cs, const float* c0, const float* dout, const float* dhn,
+                const float* dcn, const int* lens, const void* whhT, long long whhT_ld, long long whhT_plane, void* dG,
+                long long dG_plane, float* dh0, float* dc0, void* ws, unsigned int* progress, unsigned int prog_base,
+                int T, int B, int H, void* stream);
+/* Stream-ordered wait until (int)(*addr - value) >= 0 (cuStreamWaitValue32, GEQ): no SM is occupied while waiting. */
+int ss_stream_wait_value32(void* stream, unsigned int* addr, unsigned int value);
+/* Transposed sb16 copies (K = T*B contiguous) for the K-major form of the weight-gradient GEMMs; superseded by
+ * ss_gemm_sb16_tn and kept only as the cross-check path of tests/test_gpu_gemm.py:
+ * out[c][r] = in[r][c] for both planes; hprevT[d*H+j][t*B+b] = the state direction d carried INTO frame t of row b
+ * (h0 at the row's first processed frame, zero at t >= len_b). */
 int ss_transpose_sb16(const void* in, long long ld, long long plane, int R, int C, void* out, long long ldT,
                       long long planeT, void* stream);
 int ss_hprev_transpose(const void* out_sb, long long ld, long long plane, int T, int B, int H, const int* lens,
                        const float* h0, void* hprevT, long long ldT, long long planeT, void* stream);
-/* Overlap aids (engine.py runs the upper layer's weight-gradient GEMMs beside the lower layer's backward recurrence):
- * ss_lstm_bwd_start_flag: the NEXT ss_lstm_bwd launch stores `value` to *flag once its grid is resident;
- * ss_stream_wait_value32: stream-ordered wait until *addr >= value (no SM occupied while waiting);
- * ss_gemm_sm_limit: grid cap of the following ss_gemm_* launches from this host thread (0 = all SMs). */
-int ss_lstm_bwd_start_flag(unsigned int* flag, unsigned int value);
-int ss_stream_wait_value32(void* stream, unsigned int* addr, unsigned int value);
-int ss_gemm_sm_limit(int n);
-int ss_lstm_bwd(const float* gates, const float* cs, const float* c0, const float* dout, const float* dhn,
-                const float* dcn, const int* lens, const void* whhT, long long whhT_ld, long long whhT_plane, void* dG,
-                long long dG_plane, void* dGT, long long ldT, long long dGT_plane, float* dh0, float* dc0, void* ws,
-                int T, int B, int H, void* stream);
 
 /* ---- K3/K4 glue: BatchNorm1d(2H) over all T*B rows (padding included, archs/uPIT.py:119,138) folded into the
  * head Linear (archs/uPIT.py:117,141), and its backward ----

@@ -194,10 +194,10 @@ extern "C" int ss_bn_bwd(float* dy, const void* x, long long ld, long long plane
                     ((reinterpret_cast<uintptr_t>(dy) | reinterpret_cast<uintptr_t>(coef) | reinterpret_cast<uintptr_t>(bwd)) & 15) == 0 &&
                     (reinterpret_cast<uintptr_t>(x) & 7) == 0;
   if (vec4)
-    bn_bwd_apply4_kernel<<<(int)min((long long)148 * 8, (n / 4 + 255) / 256), 256, 0, st>>>(
+    bn_bwd_apply4_kernel<<<(int)min((long long)ssb::sm_count() * 8, (n / 4 + 255) / 256), 256, 0, st>>>(
         dy, (const __nv_bfloat16*)x, ld, plane, (unsigned int)(n / 4), C / 4, coef, bwd);
   else
-    bn_bwd_apply_kernel<<<(int)min((long long)148 * 8, (n + 255) / 256), 256, 0, st>>>(dy, (const __nv_bfloat16*)x, ld,
+    bn_bwd_apply_kernel<<<(int)min((long long)ssb::sm_count() * 8, (n + 255) / 256), 256, 0, st>>>(dy, (const __nv_bfloat16*)x, ld,
                                                                                       plane, n, C, coef, bwd);
   return check_launch("ss_bn_bwd");
 }
@@ -206,7 +206,7 @@ extern "C" int ss_head_dw_fix(const float* G, const float* dsum, const float* co
                               float* dW, void* stream) {
   using namespace ssb;
   const long long n = (long long)O * C;
-  head_dw_fix_kernel<<<(int)min((long long)148 * 8, (n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(G, dsum, coef, beta,
+  head_dw_fix_kernel<<<(int)min((long long)ssb::sm_count() * 8, (n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(G, dsum, coef, beta,
                                                                                                    O, C, dW);
   return check_launch("ss_head_dw_fix");
 }

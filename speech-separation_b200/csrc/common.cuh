@@ -11,6 +11,7 @@ namespace ssb {
 // ---- error reporting (C-ABI: 0 = ok, negative = error, text in ss_last_error()) ----
 void set_error(const char* fmt, ...);
 int check_launch(const char* what);            // cudaGetLastError -> 0 / -2
+int sm_count();                                // SMs of the current device (cached per device)
 
 #define SS_REQUIRE(cond, ...)                   \
   do {                                          \

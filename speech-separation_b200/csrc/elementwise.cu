@@ -149,7 +149,7 @@ extern "C" int ss_sigmoid(const float* z, long long ldz, int R, int C, float* ou
   using namespace ssb;
   const long long n = (long long)R * C;
   if (n == 0) return 0;
-  sigmoid_kernel<<<(int)min((long long)148 * 8, (n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(z, ldz, R, C, out);
+  sigmoid_kernel<<<(int)min((long long)ssb::sm_count() * 8, (n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(z, ldz, R, C, out);
   return check_launch("ss_sigmoid");
 }
 
@@ -157,7 +157,7 @@ extern "C" int ss_sigmoid(const float* z, long long ldz, int R, int C, float* ou
 extern "C" int ss_axpby(const float* x, float* y, long long n, float a, float b, void* stream) {
   using namespace ssb;
   if (n == 0) return 0;
-  axpy_kernel<<<(int)min((long long)148 * 8, (n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(x, y, n, a, b);
+  axpy_kernel<<<(int)min((long long)ssb::sm_count() * 8, (n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(x, y, n, a, b);
   return check_launch("ss_axpby");
 }
 
@@ -173,7 +173,7 @@ extern "C" int ss_unpack(const float* packed, const long long* toff, int T, int 
   using namespace ssb;
   const long long n = (long long)T * B * C;
   if (n == 0) return 0;
-  unpack_kernel<<<(int)min((long long)148 * 8, (n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(packed, toff, T, B, C, c_src,
+  unpack_kernel<<<(int)min((long long)ssb::sm_count() * 8, (n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(packed, toff, T, B, C, c_src,
                                                                                               c_off, out);
   return check_launch("ss_unpack");
 }
@@ -261,7 +261,7 @@ extern "C" int ss_rsh_residual(const float* cur, const float* z, long long ldz, 
   using namespace ssb;
   const long long n = (long long)T * B * 2 * F;
   if (n == 0) return 0;
-  rsh_residual_kernel<<<(int)min((long long)148 * 8, (n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(cur, z, ldz, lens, T, B,
+  rsh_residual_kernel<<<(int)min((long long)ssb::sm_count() * 8, (n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(cur, z, ldz, lens, T, B,
                                                                                                     F, relu, next);
   return check_launch("ss_rsh_residual");
 }
@@ -271,7 +271,7 @@ extern "C" int ss_rsh_residual_bwd(const float* dx, const float* carry_in, const
   using namespace ssb;
   const long long n = R * F;
   if (n == 0) return 0;
-  rsh_residual_bwd_kernel<<<(int)min((long long)148 * 8, (n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
+  rsh_residual_bwd_kernel<<<(int)min((long long)ssb::sm_count() * 8, (n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
       dx, carry_in, next_in, R, F, carry_out, dmask);
   return check_launch("ss_rsh_residual_bwd");
 }
@@ -330,7 +330,7 @@ extern "C" int ss_ragged_to_padded(const void* in, int is_complex, const long lo
   using namespace ssb;
   SS_REQUIRE(T > 0 && B > 0 && F > 0, "ss_ragged_to_padded: bad shape %d x %d x %d", T, B, F);
   const long long n = (long long)T * B * F;
-  const int grid = (int)min((long long)148 * 8, (n + 255) / 256);
+  const int grid = (int)min((long long)ssb::sm_count() * 8, (n + 255) / 256);
   if (is_complex)
     ragged_to_padded_kernel<true><<<grid, 256, 0, (cudaStream_t)stream>>>((const float*)in, frame_off, T, B, F, out);
   else
@@ -343,7 +343,58 @@ extern "C" int ss_masks_to_ragged(const float* z, long long ldz, const long long
   using namespace ssb;
   SS_REQUIRE(T > 0 && B > 0 && F > 0 && n_src > 0 && ldz >= (long long)n_src * F, "ss_masks_to_ragged: bad shape");
   const long long n = (long long)T * B * n_src * F;
-  masks_to_ragged_kernel<<<(int)min((long long)148 * 8, (n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
+  masks_to_ragged_kernel<<<(int)min((long long)ssb::sm_count() * 8, (n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
       z, ldz, frame_off, T, B, F, n_src, out);
   return check_launch("ss_masks_to_ragged");
+}
+
+// ---- dW_hh edge term.  The weight-gradient GEMM reads the carried state h_prev[t] as out[t -/+ 1] (row-shifted
+// operand, gemm.cu TN form); the first frame a direction processes carries h0 instead, which no row of `out` holds:
+//   dW_hh[z][gate*H + u][j] += sum_b dG[row_z(b)][z*4H + 4u + gate] * h0[z][b][j],  row_0(b) = b,  row_1(b) = (len_b-1)*B + b
+namespace ssb {
+constexpr int EDGE_N = 8;   // gate rows per block
+__global__ void __launch_bounds__(128)
+dwhh_edge_kernel(const __nv_bfloat16* __restrict__ dG, long long ld, long long plane, const int* __restrict__ lens,
+                 const float* __restrict__ h0, int B, int H, float* __restrict__ dW0, float* __restrict__ dW1,
+                 long long ldw) {
+  __shared__ float a[EDGE_N][128];
+  const int z = blockIdx.z, n0 = blockIdx.y * EDGE_N, j = blockIdx.x * 128 + threadIdx.x;
+  for (int e = threadIdx.x; e < EDGE_N * B; e += 128) {
+    const int i = e / B, b = e - i * B;
+    const int len = lens[b];
+    float v = 0.0f;
+    if (len > 0) {
+      const long long row = z ? (long long)(len - 1) * B + b : b;
+      const long long o = row * ld + (long long)z * 4 * H + n0 + i;
+      v = join_bf16(dG[o], dG[o + plane]);
+    }
+    a[i][b] = v;
+  }
+  __syncthreads();
+  if (j >= H) return;
+  float acc[EDGE_N];
+#pragma unroll
+  for (int i = 0; i < EDGE_N; ++i) acc[i] = 0.0f;
+  const float* hp = h0 + (long long)z * B * H + j;
+  for (int b = 0; b < B; ++b) {
+    const float h = hp[(long long)b * H];
+#pragma unroll
+    for (int i = 0; i < EDGE_N; ++i) acc[i] = fmaf(a[i][b], h, acc[i]);
+  }
+  float* dW = z ? dW1 : dW0;
+#pragma unroll
+  for (int i = 0; i < EDGE_N; ++i) {
+    const int n = n0 + i;                                      // interleaved 4u + gate -> natural row gate*H + u
+    dW[((long long)(n & 3) * H + (n >> 2)) * ldw + j] += acc[i];
+  }
+}
+}  // namespace ssb
+
+extern "C" int ss_dwhh_edge(const void* dG, long long ld, long long plane, const int* lens, const float* h0, int B, int H,
+                            float* dW0, float* dW1, long long ldw, void* stream) {
+  using namespace ssb;
+  SS_REQUIRE(B > 0 && B <= 128 && H > 0 && (4 * H) % EDGE_N == 0, "ss_dwhh_edge: need 1 <= B <= 128 (got %d)", B);
+  dwhh_edge_kernel<<<dim3(cdiv(H, 128), 4 * H / EDGE_N, 2), 128, 0, (cudaStream_t)stream>>>(
+      (const __nv_bfloat16*)dG, ld, plane, lens, h0, B, H, dW0, dW1, ldw);
+  return check_launch("ss_dwhh_edge");
 }

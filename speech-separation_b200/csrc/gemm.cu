@@ -1,9 +1,19 @@
 // tcgen05 GEMM on split-bf16 operands:  C[m][n] = alpha * sum_k A[m][k] * B[n][k] (+ bias[n]) (+ beta * C[m][n])
 // A, B are "sb16" matrices (two bf16 planes hi, lo; x ~= hi + lo) and the product is evaluated as
 // hi*hi + hi*lo + lo*hi with fp32 accumulation in TMEM (error ~2^-16, i.e. fp32-class results from the bf16 pipe).
-// One 128x128 output tile per CTA; warp 0 = TMA producer, warp 1 = MMA issuer, warps 2..5 = epilogue.
+// Persistent CTAs over 128x128 output tiles; warp 0 = TMA producer, warp 1 = MMA issuer, warps 2..5 = epilogue.
 // Stands in for every cuBLAS call the reference makes through torch (nn.LSTM input projections,
 // nn.Linear: archs/uPIT.py:115-117,132,141) and for their autograd backward GEMMs.
+//
+// Two operand forms share the kernel:
+//   NT (TN = false): A[M][K], B[N][K], both K-major (the reduction index is the contiguous one);
+//   TN (TN = true):  C[m][n] = sum_r A[r][m] * B[r + shift][n] -- both operands are stored with the REDUCTION index
+//       as their row ("MN-major" for the tensor core).  This is the weight-gradient form dW = dG^T X with r = t*B + b:
+//       the activations and gate gradients are read exactly as the forward / backward kernels wrote them, so no
+//       transposed copy of anything exists.  TMA brings 64-row x 64-column boxes (128-byte rows, SWIZZLE_128B), the
+//       shared-memory descriptors declare MN-major atoms (8 reduction rows x 64 columns, LBO = distance between
+//       64-column blocks, SBO = 1024 B between 8-row groups) and the instruction descriptor sets a_major = b_major = 1.
+//       `shift` rows (per batch entry) realise h_prev[t] = out[t -/+ 1] for dW_hh; TMA zero-fills rows outside [0, R).
 #include "../../include/ssb200.h"
 #include "common.cuh"
 
@@ -24,9 +34,24 @@ struct GemmParams {
   float alpha, beta;
   int M, N, K, rowmap, hidden;
   int batch, a_batch_rows, b_batch_rows;   // batch entry z reads A rows [z*a_batch_rows, +M), B rows [z*b_batch_rows, +N)
+  // TN form only: A columns [a_col0 + z*a_batch_rows, +M), B columns [b_col0 + z*b_batch_rows, +N); reduction over the
+  // 64-row blocks [kb0[z], kb0[z] + nkb) of both operands, B rows shifted by b_shift[z]
+  int a_col0, b_col0, nkb, kb0[2], b_shift[2];
 };
 
+// MN-major, SWIZZLE_128B shared-memory matrix descriptor: 64-column blocks `lbo` bytes apart, 8-row groups 1024 B apart.
+__device__ __forceinline__ uint64_t umma_desc_sw128_mn(uint32_t saddr, uint32_t lbo) {
+  uint64_t d = 0;
+  d |= (uint64_t)((saddr >> 4) & 0x3FFF);
+  d |= (uint64_t)((lbo >> 4) & 0x3FFF) << 16;
+  d |= (uint64_t)(1024 >> 4) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)2 << 61;
+  return d;
+}
+
 // Persistent: CTA c works on tiles c, c + gridDim.x, ... (n fastest, then m, then batch).
+template <bool TN>
 __global__ void __launch_bounds__(G_THREADS, 1)
 gemm_sb16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, GemmParams p) {
   extern __shared__ unsigned char smem_raw[];
@@ -39,7 +64,7 @@ gemm_sb16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int nkb = (p.K + GB_K - 1) / GB_K;
+  const int nkb = TN ? p.nkb : (p.K + GB_K - 1) / GB_K;
   const int mt = (p.M + GB_M - 1) / GB_M, nt = (p.N + GB_N - 1) / GB_N;
   const int tiles = p.batch * mt * nt;
 
@@ -73,15 +98,27 @@ gemm_sb16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           mbar_wait(&empty[s], ph ^ 1);
           unsigned char* st = smem + s * G_STAGE_BYTES;
           mbar_arrive_expect_tx(&full[s], G_STAGE_BYTES);
-          tma_load_3d(st, &tmA, &full[s], kb * GB_K, m0, 0);               // [plane][128 rows][64 k]
-          tma_load_3d(st + 2 * G_PLANE, &tmB, &full[s], kb * GB_K, n0, 0);
+          if (TN) {
+            // four boxes of [plane][64 rows][64 columns]: A columns m0.., m0+64.., B columns n0.., n0+64..
+            const int r = (p.kb0[z] + kb) * GB_K;
+            tma_load_3d(st, &tmA, &full[s], p.a_col0 + m0, r, 0);
+            tma_load_3d(st + G_PLANE, &tmA, &full[s], p.a_col0 + m0 + 64, r, 0);
+            tma_load_3d(st + 2 * G_PLANE, &tmB, &full[s], p.b_col0 + n0, r + p.b_shift[z], 0);
+            tma_load_3d(st + 3 * G_PLANE, &tmB, &full[s], p.b_col0 + n0 + 64, r + p.b_shift[z], 0);
+          } else {
+            tma_load_3d(st, &tmA, &full[s], kb * GB_K, m0, 0);               // [plane][128 rows][64 k]
+            tma_load_3d(st + 2 * G_PLANE, &tmB, &full[s], kb * GB_K, n0, 0);
+          }
         }
       }
     }
   } else if (warp == 1) {
     if (lane == 0) {
-      constexpr uint32_t idesc = umma_idesc_bf16(GB_M, GB_N);
-      const uint64_t base = umma_desc_sw128(smem_u32(smem));
+      constexpr uint32_t idesc = umma_idesc_bf16(GB_M, GB_N) | (TN ? (1u << 15) | (1u << 16) : 0u);
+      const uint64_t base = TN ? umma_desc_sw128_mn(smem_u32(smem), G_PLANE) : umma_desc_sw128(smem_u32(smem));
+      // NT: planes 16 KB apart, a k-step is 32 bytes inside the 128-byte row.  TN: a box is [hi 8 KB | lo 8 KB], the two
+      // 64-column blocks of an operand are G_PLANE apart (= LBO), a k-step is two 8-row groups = 2048 bytes.
+      constexpr uint32_t lo_off = (TN ? G_PLANE / 2 : G_PLANE) >> 4, kstep = (TN ? 2048 : 32) >> 4;
       int it = 0, lt = 0;
       for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x, ++lt) {
         const int acc = lt & 1;
@@ -92,13 +129,13 @@ gemm_sb16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           const int s = it % G_STAGES, ph = (it / G_STAGES) & 1;
           mbar_wait(&full[s], ph);
           tc_fence_after();
-          const uint64_t dah = base + (uint32_t)(s * (G_STAGE_BYTES >> 4)), dal = dah + (G_PLANE >> 4);
-          const uint64_t dbh = dah + (2 * G_PLANE >> 4), dbl = dbh + (G_PLANE >> 4);
+          const uint64_t dah = base + (uint32_t)(s * (G_STAGE_BYTES >> 4)), dal = dah + lo_off;
+          const uint64_t dbh = dah + (2 * G_PLANE >> 4), dbl = dbh + lo_off;
 #pragma unroll
-          for (int k = 0; k < GB_K / 16; ++k) {                            // 16 bf16 = 32 bytes inside the 128B row
-            umma_bf16(tmem_d, dal + 2 * k, dbh + 2 * k, idesc, (kb | k) ? 1u : 0u);   // small terms first
-            umma_bf16(tmem_d, dah + 2 * k, dbl + 2 * k, idesc, 1u);
-            umma_bf16(tmem_d, dah + 2 * k, dbh + 2 * k, idesc, 1u);
+          for (int k = 0; k < GB_K / 16; ++k) {
+            umma_bf16(tmem_d, dal + kstep * k, dbh + kstep * k, idesc, (kb | k) ? 1u : 0u);   // small terms first
+            umma_bf16(tmem_d, dah + kstep * k, dbl + kstep * k, idesc, 1u);
+            umma_bf16(tmem_d, dah + kstep * k, dbh + kstep * k, idesc, 1u);
           }
           umma_commit(&empty[s]);
         }
@@ -188,16 +225,22 @@ static int sb16_tmap(CUtensorMap* tm, const void* base, long long rows, long lon
 
 }  // namespace ssb
 
-// Grid cap for the following launches of this host thread (0 = all SMs): lets a GEMM run beside a resident
-// recurrence kernel on the SMs that kernel leaves idle (engine.py, backward of the upper layer's weights).
-static int g_sm_limit = 0;
-extern "C" int ss_gemm_sm_limit(int n) {
-  g_sm_limit = n > 0 ? n : 0;
-  return 0;
+static int gemm_grid(int tiles, int sm_limit) {
+  static int n_sm = 0;
+  if (!n_sm) {
+    cudaFuncSetAttribute(ssb::gemm_sb16_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, ssb::G_SMEM);
+    cudaFuncSetAttribute(ssb::gemm_sb16_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, ssb::G_SMEM);
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev);
+  }
+  int grid = tiles < n_sm ? tiles : n_sm;
+  if (sm_limit > 0 && grid > sm_limit) grid = sm_limit;      // run beside a resident recurrence kernel on its idle SMs
+  return grid;
 }
 
 static int gemm_launch(const void* A, long long lda, long long a_plane, int a_rows, const void* B, long long ldb,
-                       long long b_plane, int b_rows, ssb::GemmParams p, void* stream) {
+                       long long b_plane, int b_rows, ssb::GemmParams p, int sm_limit, void* stream) {
   using namespace ssb;
   SS_REQUIRE(p.M > 0 && p.N > 0 && p.K > 0, "ss_gemm_sb16: empty problem %dx%dx%d", p.M, p.N, p.K);
   SS_REQUIRE(lda % 8 == 0 && ldb % 8 == 0 && a_plane % 8 == 0 && b_plane % 8 == 0,
@@ -210,33 +253,67 @@ static int gemm_launch(const void* A, long long lda, long long a_plane, int a_ro
   if (rc) return rc;
   rc = sb16_tmap(&tmB, B, b_rows, p.K, ldb, b_plane, GB_N);
   if (rc) return rc;
-  static bool attr_set = false;
-  static int n_sm = 148;
-  if (!attr_set) {
-    cudaFuncSetAttribute(gemm_sb16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, G_SMEM);
-    int dev = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev);
-    attr_set = true;
-  }
   const int tiles = p.batch * cdiv(p.N, GB_N) * cdiv(p.M, GB_M);
-  int grid = tiles < n_sm ? tiles : n_sm;
-  if (g_sm_limit > 0 && grid > g_sm_limit) grid = g_sm_limit;
-  gemm_sb16_kernel<<<grid, G_THREADS, G_SMEM, (cudaStream_t)stream>>>(tmA, tmB, p);
+  gemm_sb16_kernel<false><<<gemm_grid(tiles, sm_limit), G_THREADS, G_SMEM, (cudaStream_t)stream>>>(tmA, tmB, p);
   return check_launch("ss_gemm_sb16");
 }
 
 extern "C" int ss_gemm_sb16(const void* A, long long lda, long long a_plane, const void* B, long long ldb,
                             long long b_plane, float* C, long long ldc, int M, int N, int K, const float* bias,
-                            float alpha, float beta, int rowmap, int hidden, void* stream) {
+                            float alpha, float beta, int rowmap, int hidden, int sm_limit, void* stream) {
   ssb::GemmParams p{{C, nullptr}, ldc, bias, alpha, beta, M, N, K, rowmap, hidden, 1, 0, 0};
-  return gemm_launch(A, lda, a_plane, M, B, ldb, b_plane, N, p, stream);
+  return gemm_launch(A, lda, a_plane, M, B, ldb, b_plane, N, p, sm_limit, stream);
 }
 
 extern "C" int ss_gemm_sb16_x2(const void* A, long long lda, long long a_plane, int a_batch_rows, const void* B,
                                long long ldb, long long b_plane, int b_batch_rows, float* C0, float* C1,
-                               long long ldc, int M, int N, int K, float alpha, float beta, int rowmap, int hidden,
-                               void* stream) {
-  ssb::GemmParams p{{C0, C1}, ldc, nullptr, alpha, beta, M, N, K, rowmap, hidden, 2, a_batch_rows, b_batch_rows};
-  return gemm_launch(A, lda, a_plane, a_batch_rows + M, B, ldb, b_plane, b_batch_rows + N, p, stream);
+                               long long ldc, int M, int N, int K, const float* bias, float alpha, float beta,
+                               int rowmap, int hidden, int sm_limit, void* stream) {
+  ssb::GemmParams p{{C0, C1}, ldc, bias, alpha, beta, M, N, K, rowmap, hidden, 2, a_batch_rows, b_batch_rows};
+  return gemm_launch(A, lda, a_plane, a_batch_rows + M, B, ldb, b_plane, b_batch_rows + N, p, sm_limit, stream);
+}
+
+extern "C" int ss_gemm_sb16_tn(const void* A, long long lda, long long a_plane, int a_cols, int a_col0, int a_col_batch,
+                               const void* B, long long ldb, long long b_plane, int b_cols, int b_col0, int b_col_batch,
+                               int R, int blk0_z0, int blk0_z1, int n_blk, int b_shift_z0, int b_shift_z1, int batch,
+                               float* C0, float* C1, long long ldc, int M, int N, float alpha, float beta, int rowmap,
+                               int hidden, int sm_limit, void* stream) {
+  using namespace ssb;
+  SS_REQUIRE(M > 0 && N > 0 && R > 0 && n_blk > 0 && (batch == 1 || batch == 2), "ss_gemm_sb16_tn: empty problem");
+  SS_REQUIRE(lda % 8 == 0 && ldb % 8 == 0 && a_plane % 8 == 0 && b_plane % 8 == 0 && a_col0 % 8 == 0 && b_col0 % 8 == 0 &&
+                 a_col_batch % 8 == 0 && b_col_batch % 8 == 0,
+             "ss_gemm_sb16_tn: pitches, plane strides and column offsets must be multiples of 8 elements (16 bytes)");
+  SS_REQUIRE(((uintptr_t)A & 15) == 0 && ((uintptr_t)B & 15) == 0, "ss_gemm_sb16_tn: operands must be 16-byte aligned");
+  SS_REQUIRE(rowmap == SS_ROWMAP_NONE || (rowmap == SS_ROWMAP_UNIT4 && hidden > 0 && M == 4 * hidden),
+             "ss_gemm_sb16_tn: bad rowmap");
+  SS_REQUIRE(blk0_z0 >= 0 && blk0_z1 >= 0 && (long long)(blk0_z0 + n_blk - 1) * GB_K < R &&
+                 (long long)(blk0_z1 + n_blk - 1) * GB_K < R,
+             "ss_gemm_sb16_tn: row blocks outside the %d reduction rows", R);
+  CUtensorMap tmA, tmB;
+  {  // (columns, reduction rows, plane), box 64 x 64 x 2; rows outside [0, R) and columns outside the matrix read as zero
+    uint64_t dims[3] = {(uint64_t)a_cols, (uint64_t)R, 2};
+    uint64_t str[2] = {(uint64_t)lda * 2, (uint64_t)a_plane * 2};
+    uint32_t box[3] = {64, 64, 2};
+    int rc = make_tmap_bf16(&tmA, A, 3, dims, str, box);
+    if (rc) return rc;
+  }
+  {
+    uint64_t dims[3] = {(uint64_t)b_cols, (uint64_t)R, 2};
+    uint64_t str[2] = {(uint64_t)ldb * 2, (uint64_t)b_plane * 2};
+    uint32_t box[3] = {64, 64, 2};
+    int rc = make_tmap_bf16(&tmB, B, 3, dims, str, box);
+    if (rc) return rc;
+  }
+  GemmParams p{{C0, batch == 2 ? C1 : nullptr}, ldc, nullptr, alpha, beta, M, N, n_blk * GB_K, rowmap, hidden, batch,
+               a_col_batch, b_col_batch};
+  p.a_col0 = a_col0;
+  p.b_col0 = b_col0;
+  p.nkb = n_blk;
+  p.kb0[0] = blk0_z0;
+  p.kb0[1] = blk0_z1;
+  p.b_shift[0] = b_shift_z0;
+  p.b_shift[1] = b_shift_z1;
+  const int tiles = batch * cdiv(N, GB_N) * cdiv(M, GB_M);
+  gemm_sb16_kernel<true><<<gemm_grid(tiles, sm_limit), G_THREADS, G_SMEM, (cudaStream_t)stream>>>(tmA, tmB, p);
+  return check_launch("ss_gemm_sb16_tn");
 }

@@ -303,7 +303,7 @@ static int launch_istft(const float2* spec, const float* mask, const long long* 
   auto kern = istft_kernel<NFFT, TF, F32>;
   cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   const long long n_work = (long long)total_tiles * n_src;
-  const int resident = 148 * C::CTAS;
+  const int resident = ssb::sm_count() * C::CTAS;
   const int grid = n_work < resident ? (int)n_work : resident;
   kern<<<grid, C::THREADS, smem, st>>>(spec, mask, frame_off, wav_off, tile_off, n_utts, n_src, total_tiles, hop, out);
   return check_launch("ss_istft_masked");

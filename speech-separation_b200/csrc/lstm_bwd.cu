@@ -36,7 +36,6 @@ lstm_bwd_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
   uint64_t* wfull = accum_full + 1;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(wfull + 1);
 
-  if (p.start_flag && blockIdx.x == 0 && threadIdx.x == 0) *reinterpret_cast<volatile unsigned int*>(p.start_flag) = p.start_value;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int dir = blockIdx.x / p.NC, cta = blockIdx.x % p.NC;
   const int j0 = cta * LB_U;
@@ -80,6 +79,12 @@ lstm_bwd_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
           mbar_wait(&empty[st], ph ^ 1);
           mbar_arrive_expect_tx(&full[st], stage_bytes);
           tma_load_3d(ring + st * stage_bytes, &tmG, &full[st], dir * 4 * H + kc * 64, tp * B, 0);
+        }
+        // progress for stream-ordered consumers (ss_stream_wait_value32): the counter just observed covers the dG rows of
+        // steps 0..s-1 of this direction; one CTA per direction reports every 4th step, after its copies are in flight
+        if (p.progress && cta == 0 && (s & 3) == 0) {
+          __threadfence_system();
+          *reinterpret_cast<volatile unsigned int*>(p.progress + dir) = p.prog_base + (unsigned int)s;
         }
       }
     }
@@ -233,20 +238,10 @@ lstm_bwd_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
 
 }  // namespace ssb
 
-// The NEXT ss_lstm_bwd launch writes `value` to *flag as soon as its grid is resident (both kernels are cooperative
-// launches): stream-ordered work gated on it with ss_stream_wait_value32 then runs on the SMs the recurrence leaves idle.
-static unsigned int* g_start_flag = nullptr;
-static unsigned int g_start_value = 0;
-extern "C" int ss_lstm_bwd_start_flag(unsigned int* flag, unsigned int value) {
-  g_start_flag = flag;
-  g_start_value = value;
-  return 0;
-}
-
 extern "C" int ss_lstm_bwd(const float* gates, const float* cs, const float* c0, const float* dout, const float* dhn,
                            const float* dcn, const int* lens, const void* whhT, long long whhT_ld,
-                           long long whhT_plane, void* dG, long long dG_plane, void* dGT, long long ldT,
-                           long long dGT_plane, float* dh0, float* dc0, void* ws, int T, int B, int H, void* stream) {
+                           long long whhT_plane, void* dG, long long dG_plane, float* dh0, float* dc0, void* ws,
+                           unsigned int* progress, unsigned int prog_base, int T, int B, int H, void* stream) {
   using namespace ssb;
   SS_REQUIRE(T > 0 && B > 0 && B <= 128, "ss_lstm_bwd: need 1 <= B <= 128 (got %d) and T > 0", B);
   SS_REQUIRE(H % 8 == 0 && 4 * H <= 64 * LB_MAXKC, "ss_lstm_bwd: unsupported hidden size %d", H);
@@ -254,7 +249,6 @@ extern "C" int ss_lstm_bwd(const float* gates, const float* cs, const float* c0,
   LstmBwdParams p;
   p.gates = gates; p.cs = cs; p.c0 = c0; p.dout = dout; p.dhn = dhn; p.dcn = dcn; p.lens = lens;
   p.dG = (__nv_bfloat16*)dG; p.dG_plane = dG_plane;
-  p.dGT = (__nv_bfloat16*)dGT; p.ldT = ldT; p.dGT_plane = dGT_plane;
   p.dh0 = dh0; p.dc0 = dc0;
   p.T = T; p.B = B; p.H = H;
   p.R = B <= 64 ? 64 : 128;
@@ -263,17 +257,12 @@ extern "C" int ss_lstm_bwd(const float* gates, const float* cs, const float* c0,
   p.NS = p.R == 64 ? 4 : 2;
   p.want_d0 = dh0 != nullptr;
   p.dbg = g_lstm_dbg;
-  p.ROT = getenv("SSB_ROT") ? atoi(getenv("SSB_ROT")) : 1;
+  p.ROT = 1;
   p.sync = (unsigned int*)ws;
-  p.start_flag = g_start_flag;                                 // one-shot, see ss_lstm_bwd_start_flag
-  p.start_value = g_start_value;
-  g_start_flag = nullptr;
+  p.progress = progress;
+  p.prog_base = prog_base;
   cudaMemsetAsync(ws, 0, 256, st);
-  if (H == 600 && B <= 64 && !getenv("SSB_BWD_V1")) {
-    int rc = launch_lstm_bwd_ks(p, whhT, whhT_ld, whhT_plane, st);
-    if (rc) return rc;
-    return dGT ? launch_transpose_sb16(dG, 8LL * H, dG_plane, T * B, 8 * H, dGT, ldT, dGT_plane, st) : 0;
-  }
+  if (H == 600 && B <= 64) return launch_lstm_bwd_ks(p, whhT, whhT_ld, whhT_plane, st);
 
   CUtensorMap tmW, tmG;
   {
@@ -298,5 +287,5 @@ extern "C" int ss_lstm_bwd(const float* gates, const float* cs, const float* c0,
     set_error("ss_lstm_bwd: cooperative launch failed: %s", cudaGetErrorString(e));
     return -2;
   }
-  return dGT ? launch_transpose_sb16(dG, 8LL * H, dG_plane, T * B, 8 * H, dGT, ldT, dGT_plane, st) : 0;
+  return 0;
 }

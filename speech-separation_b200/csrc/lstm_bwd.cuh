@@ -14,13 +14,11 @@ struct LstmBwdParams {
   const int* lens;
   __nv_bfloat16* dG;         // sb16 [T*B][8H]
   long long dG_plane;
-  __nv_bfloat16* dGT;        // sb16 [8H][ldT]
-  long long ldT, dGT_plane;
   float* dh0;                // [2][B][H] or null
   float* dc0;
   unsigned int* sync;
-  unsigned int* start_flag;  // optional: *start_flag = start_value once the kernel is resident (ss_lstm_bwd_start_flag)
-  unsigned int start_value;
+  unsigned int* progress;    // [2] or null: prog_base + number of steps whose dG rows are globally visible, per direction
+  unsigned int prog_base;
   int T, B, H, R, NC, KC, NS, want_d0, ROT;
   long long* dbg;            // optional clock64 trace of CTA 0: [step][32]
 };

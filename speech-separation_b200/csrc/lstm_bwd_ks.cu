@@ -99,8 +99,6 @@ lstm_bwd_ks_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int rank = (int)cluster_rank();
-  // cooperative launch: block 0 running means the whole grid is resident -> work waiting on the flag may start
-  if (p.start_flag && blockIdx.x == 0 && threadIdx.x == 0) *reinterpret_cast<volatile unsigned int*>(p.start_flag) = p.start_value;
   const int cl = blockIdx.x / KS_CL;
   const int dir = cl / KS_NCL, c = cl % KS_NCL;
   const int T = p.T, B = p.B;
@@ -149,6 +147,12 @@ lstm_bwd_ks_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
             mbar_arrive_expect_tx(&full[st], KS_CHUNK);
             tma_load_3d(ring + st * KS_CHUNK, &tmG, &full[st], dir * 4 * H + (ch0 + i) * 64, 0, tp * B);
           }
+        }
+        // progress for stream-ordered consumers (ss_stream_wait_value32): the counter just observed covers the dG rows of
+        // steps 0..s-1 of this direction; one CTA per direction reports every 4th step, after its copies are in flight
+        if (p.progress && c == 0 && rank == 0 && (s & 3) == 0) {
+          __threadfence_system();
+          *reinterpret_cast<volatile unsigned int*>(p.progress + dir) = p.prog_base + (unsigned int)s;
         }
         KS_STAMP(2);
       }
@@ -350,17 +354,28 @@ int launch_lstm_bwd_ks(const LstmBwdParams& p, const void* whhT, long long whhT_
   cfg.blockDim = dim3(KS_THREADS);
   cfg.dynamicSmemBytes = KS_SMEM;
   cfg.stream = st;
-  cudaLaunchAttribute attr[2];
+  cudaLaunchAttribute attr[1];
   attr[0].id = cudaLaunchAttributeClusterDimension;
   attr[0].val.clusterDim.x = KS_CL;
   attr[0].val.clusterDim.y = 1;
   attr[0].val.clusterDim.z = 1;
-  attr[1].id = cudaLaunchAttributeCooperative;
-  attr[1].val.cooperative = 1;
   cfg.attrs = attr;
-  // SSB_NO_COOP=1 drops the co-residency guarantee: Nsight Compute 2025.x cannot replay a launch that is both
-  // cooperative and clustered; on an otherwise idle GPU the 80 CTAs are co-resident anyway.  Profiling aid only.
-  cfg.numAttrs = getenv("SSB_NO_COOP") ? 1 : 2;
+  cfg.numAttrs = 1;
+  // The CTAs spin on each other (per-step counter), so all 20 clusters must be able to run at once.  This is checked
+  // here instead of asking for a cooperative launch: Nsight Compute cannot replay a launch that is both cooperative
+  // and clustered, and work that already occupies SMs (the flag-gated GEMMs of the side stream) always finishes on
+  // its own, so late CTAs only wait.
+  static int max_clusters[2] = {-1, -1};
+  if (max_clusters[p.dbg ? 1 : 0] < 0) {
+    int n = 0;
+    if (cudaOccupancyMaxActiveClusters(&n, kern, &cfg) != cudaSuccess) n = 0;
+    max_clusters[p.dbg ? 1 : 0] = n;
+  }
+  if (max_clusters[p.dbg ? 1 : 0] < 2 * KS_NCL) {
+    set_error("ss_lstm_bwd (K-split clusters): only %d of the %d clusters can be co-resident on this device",
+              max_clusters[p.dbg ? 1 : 0], 2 * KS_NCL);
+    return -2;
+  }
   cudaError_t e = cudaLaunchKernelEx(&cfg, kern, tmW, tmG, p);
   if (e != cudaSuccess) {
     set_error("ss_lstm_bwd (K-split clusters): launch failed: %s", cudaGetErrorString(e));

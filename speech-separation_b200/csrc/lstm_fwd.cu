@@ -25,7 +25,7 @@ namespace ssb {
     if (!FAST && p.dbg && blockIdx.x == 0) p.dbg[s * 32 + (slot)] = clock64(); \
   } while (0)
 
-// FAST: H = 600, B <= 64 (R = 64), no rotation, no trace -- the reference's shape; every loop bound is a constant so
+// FAST: H = 600, B <= 64 (R = 64), no trace -- the reference's shape; every loop bound is a constant so
 // the single MMA-issuing thread runs a fully unrolled instruction stream (its scalar overhead, not the tensor
 // pipe, paced the generic loop: tools/microbench/bulk_rate.cu).
 template <bool FAST>
@@ -50,7 +50,6 @@ lstm_fwd_kernel(const __grid_constant__ CUtensorMap tmW, LstmFwdParams p) {
   const int u0 = cta * LF_U;
   const int T = p.T, B = p.B, H = FAST ? 600 : p.H;
   unsigned int* counter = p.sync + dir;
-  const int kc0 = (!FAST && p.ROT) ? (cta * p.ROT) % p.KC : 0;
 
   if (threadIdx.x == 0) {
     tma_prefetch_desc(&tmW);
@@ -84,14 +83,22 @@ lstm_fwd_kernel(const __grid_constant__ CUtensorMap tmW, LstmFwdParams p) {
         LF_STAMP(1);
         // (the generic->async proxy fence sits on the writer side, in publish(): there it overlaps the other
         // threads' stores instead of adding ~1000 cycles between the acquire and the first copy)
-        const __nv_bfloat16* src = p.hbuf + (((long long)(cta % p.REP) * 2 + (s & 1)) * 2 + dir) * PKC * blk;
+        const __nv_bfloat16* src = p.hbuf + ((long long)(s & 1) * 2 + dir) * PKC * blk;
 #pragma unroll
         for (int i = 0; i < PKC; ++i, ++it) {
-          const int kc = FAST ? i : (kc0 + i) % PKC;     // (generic path: optional per-CTA chunk rotation)
+          const int kc = i;
           const int st = FAST ? i % 5 : it % PNS, ph = FAST ? (i / 5) & 1 : (it / PNS) & 1;
           mbar_wait(&empty[st], ph ^ 1);
           mbar_arrive_expect_tx(&full[st], stage_bytes);
           bulk_load(ring + st * stage_bytes, src + kc * blk, stage_bytes, &full[st]);
+        }
+        // Progress for stream-ordered consumers (ss_stream_wait_value32): the `out` stores of step j precede, in every
+        // CTA, the release of step j+1's publish, i.e. counter >= NC*(j+3); the counter observed at the top of step s therefore
+        // covers the outputs of steps 0..s-2.  One CTA per direction reports, every 4th step, after its copies are
+        // in flight (the fence then overlaps the MMAs instead of delaying them).
+        if (p.progress && cta == 0 && s >= 2 && (s & 3) == 0) {
+          __threadfence_system();
+          *reinterpret_cast<volatile unsigned int*>(p.progress + dir) = p.prog_base + (unsigned int)(s - 1);
         }
         LF_STAMP(2);
       }
@@ -106,7 +113,7 @@ lstm_fwd_kernel(const __grid_constant__ CUtensorMap tmW, LstmFwdParams p) {
       for (int s = 0; s < T; ++s) {
 #pragma unroll
         for (int i = 0; i < PKC; ++i, ++it) {
-          const int kc = FAST ? i : (kc0 + i) % PKC;
+          const int kc = i;
           const int st = FAST ? i % 5 : it % PNS, ph = FAST ? (i / 5) & 1 : (it / PNS) & 1;
           mbar_wait(&full[st], ph);
           LF_STAMP(i == 0 ? 3 : 10 + i);
@@ -154,11 +161,9 @@ lstm_fwd_kernel(const __grid_constant__ CUtensorMap tmW, LstmFwdParams p) {
         __nv_bfloat16 hi[4], lo[4];
 #pragma unroll
         for (int j = 0; j < 4; ++j) split_bf16(h[j], hi[j], lo[j]);
-        for (int r = 0; r < p.REP; ++r) {
-          __nv_bfloat16* dst = p.hbuf + ((((long long)r * 2 + slot) * 2 + dir) * PKC + kc_w) * blk + row_off;
-          *reinterpret_cast<uint2*>(dst) = *reinterpret_cast<uint2*>(hi);
-          *reinterpret_cast<uint2*>(dst + PR * 64) = *reinterpret_cast<uint2*>(lo);
-        }
+        __nv_bfloat16* dst = p.hbuf + (((long long)slot * 2 + dir) * PKC + kc_w) * blk + row_off;
+        *reinterpret_cast<uint2*>(dst) = *reinterpret_cast<uint2*>(hi);
+        *reinterpret_cast<uint2*>(dst + PR * 64) = *reinterpret_cast<uint2*>(lo);
       }
       // CTA barrier, then ONE thread releases at gpu scope (cumulative over the other threads' stores, the
       // cooperative-groups grid.sync pattern) and orders them against the consumers' async-proxy reads.
@@ -226,7 +231,7 @@ lstm_fwd_kernel(const __grid_constant__ CUtensorMap tmW, LstmFwdParams p) {
       dbg_s = s;
       publish((s + 1) & 1);                                    // carried state for the next step (critical path first)
       if (threadIdx.x == 0) LF_STAMP(7);
-      if (row_ok && !(p.EXP & 4)) {
+      if (row_ok) {
         if (active) {
 #pragma unroll
           for (int j = 0; j < 4; ++j) __stcs(gptr + j, g4[j]);
@@ -266,30 +271,22 @@ extern "C" int ss_lstm_debug(long long* buf) {   // development aid: clock64 tra
   return 0;
 }
 
-static int lstm_rep() {
-  const char* e = getenv("SSB_HREP");
-  int r = e ? atoi(e) : 1;
-  return r < 1 ? 1 : (r > 8 ? 8 : r);
-}
-
 extern "C" long long ss_lstm_ws_bytes(int B, int H) {
   const long long R = B <= 64 ? 64 : 128;
-  return 8LL * 2 * 2 * ssb::cdiv(H, 64) * 2 * R * 64 * 2 + 256;       // hbuf (up to 8 replicas) + sync counters
+  return 2LL * 2 * ssb::cdiv(H, 64) * 2 * R * 64 * 2 + 1024;          // h ping-pong buffer + sync counters
 }
 
 extern "C" int ss_lstm_fwd(float* gx, const void* whh_r, long long whh_ld, long long whh_plane, const float* h0,
-                           const float* c0, const int* lens, void* out, long long out_plane, void* outT, void* hprevT,
-                           long long ldT, long long outT_plane, float* cs, float* hn, float* cn, void* ws, int T, int B,
-                           int H, void* stream) {
+                           const float* c0, const int* lens, void* out, long long out_plane, float* cs, float* hn,
+                           float* cn, void* ws, unsigned int* progress, unsigned int prog_base, int T, int B, int H,
+                           void* stream) {
   using namespace ssb;
   SS_REQUIRE(T > 0 && B > 0 && B <= 128, "ss_lstm_fwd: need 1 <= B <= 128 (got %d) and T > 0", B);
-  SS_REQUIRE((outT == nullptr) == (hprevT == nullptr), "ss_lstm_fwd: outT and hprevT go together");
   SS_REQUIRE(H % LF_U == 0 && H % 8 == 0 && H <= 64 * LF_MAXKC, "ss_lstm_fwd: unsupported hidden size %d", H);
   cudaStream_t st = (cudaStream_t)stream;
   LstmFwdParams p;
   p.gx = gx; p.h0 = h0; p.c0 = c0; p.lens = lens;
   p.out = (__nv_bfloat16*)out; p.out_plane = out_plane;
-  p.outT = (__nv_bfloat16*)outT; p.hprevT = (__nv_bfloat16*)hprevT; p.ldT = ldT; p.outT_plane = outT_plane;
   p.cs = cs; p.hn = hn; p.cn = cn;
   p.T = T; p.B = B; p.H = H;
   p.dbg = g_lstm_dbg;
@@ -297,10 +294,9 @@ extern "C" int ss_lstm_fwd(float* gx, const void* whh_r, long long whh_ld, long 
   p.NC = H / LF_U;
   p.KC = cdiv(H, 64);
   p.NS = p.R == 64 ? 5 : 2;
-  p.REP = lstm_rep();
-  p.EXP = getenv("SSB_EXP") ? atoi(getenv("SSB_EXP")) : 0;
-  p.ROT = getenv("SSB_ROT") ? atoi(getenv("SSB_ROT")) : 0;
-  const long long hbuf_bytes = (long long)p.REP * 2 * 2 * p.KC * 2 * p.R * 64 * 2;
+  p.progress = progress;
+  p.prog_base = prog_base;
+  const long long hbuf_bytes = 2LL * 2 * p.KC * 2 * p.R * 64 * 2;
   p.hbuf = (__nv_bfloat16*)ws;
   p.sync = (unsigned int*)((char*)ws + hbuf_bytes);
   cudaMemsetAsync(ws, 0, hbuf_bytes + 1024, st);
@@ -313,14 +309,8 @@ extern "C" int ss_lstm_fwd(float* gx, const void* whh_r, long long whh_ld, long 
     int rc = make_tmap_bf16(&tmW, whh_r, 3, dims, str, box);
     if (rc) return rc;
   }
-  const bool dual = H == 600 && B > 32 && B <= 64 && p.REP == 1 && p.ROT == 0 &&
-                    !getenv("SSB_GENERIC") && getenv("SSB_FWD_DUAL");
-  if (dual) {   // experimental: two batch halves interleaved per CTA (lstm_fwd_dual.cu); slower today, see its header
-    int rc = launch_lstm_fwd_dual(tmW, p, st);
-    if (rc) return rc;
-  } else {
   const int smem = p.NS * 2 * p.R * 128 + p.KC * LF_WCHUNK + 64 * LF_XPITCH * 4 + 1024 + 256;
-  const bool fast = H == 600 && p.R == 64 && p.ROT == 0 && p.dbg == nullptr && !getenv("SSB_GENERIC");
+  const bool fast = H == 600 && p.R == 64 && p.dbg == nullptr;
   void* kern = fast ? (void*)lstm_fwd_kernel<true> : (void*)lstm_fwd_kernel<false>;
   cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
   void* args[] = {(void*)&tmW, (void*)&p};
@@ -328,13 +318,6 @@ extern "C" int ss_lstm_fwd(float* gx, const void* whh_r, long long whh_ld, long 
   if (e != cudaSuccess) {
     set_error("ss_lstm_fwd: cooperative launch failed: %s", cudaGetErrorString(e));
     return -2;
-  }
-  }
-  if (outT) {   // transposed copies for the dW GEMMs, one HBM-bound pass each instead of scattered stores per step
-    int rc = launch_transpose_sb16(out, 2LL * H, out_plane, T * B, 2 * H, outT, ldT, outT_plane, st);
-    if (rc) return rc;
-    rc = launch_hprev_transpose(out, 2LL * H, out_plane, T, B, H, lens, h0, hprevT, ldT, outT_plane, st);
-    if (rc) return rc;
   }
   return 0;
 }

@@ -1,5 +1,4 @@
-// Shared declarations of the forward recurrence kernels (lstm_fwd.cu: generic + single-context fast path,
-// lstm_fwd_dual.cu: two batch halves interleaved per CTA).
+// Declarations of the forward recurrence kernel (lstm_fwd.cu: generic + constant-shape fast path).
 #pragma once
 #include "common.cuh"
 
@@ -21,19 +20,15 @@ struct LstmFwdParams {
   const int* lens;           // [B]
   __nv_bfloat16* out;        // sb16 [T*B][2H]
   long long out_plane;
-  __nv_bfloat16* outT;       // sb16 [2H][ldT] or null: transposed outputs (X^T of the next layer's dW GEMM)
-  __nv_bfloat16* hprevT;     // sb16 [2H][ldT] or null: transposed carried state BEFORE each step (dW_hh GEMM)
-  long long ldT, outT_plane;
   float* cs;                 // [T*B][2H] or null
   float* hn;                 // [2][B][H]
   float* cn;
-  __nv_bfloat16* hbuf;       // [rep][slot 2][dir 2][kc][plane 2][R][64], rows pre-swizzled (SWIZZLE_128B)
-  int REP, EXP, ROT;
+  __nv_bfloat16* hbuf;       // [slot 2][dir 2][kc][plane 2][R][64], rows pre-swizzled (SWIZZLE_128B)
   unsigned int* sync;        // [2]
+  unsigned int* progress;    // [2] or null: prog_base + number of steps whose `out` rows are globally visible, per direction
+  unsigned int prog_base;
   int T, B, H, R, NC, KC, NS;
   long long* dbg;            // optional clock64 trace of CTA 0: [step][32]
 };
-
-int launch_lstm_fwd_dual(const CUtensorMap& tmW, LstmFwdParams p, cudaStream_t st);
 
 }  // namespace ssb

@@ -109,7 +109,7 @@ extern "C" int ss_clip_adam(float* p, const float* g, float* m, float* v, long l
   a.gscale = gscale, a.max_norm = max_norm, a.lr = lr, a.beta1 = beta1, a.beta2 = beta2, a.eps = eps;
   a.bc1 = (float)(1.0 - pow((double)beta1, step));
   a.bc2_sqrt = (float)sqrt(1.0 - pow((double)beta2, step));
-  const int blocks = (int)min((long long)148 * 8, (n / 4 + OPT_THREADS - 1) / OPT_THREADS + 1);
+  const int blocks = (int)min((long long)ssb::sm_count() * 8, (n / 4 + OPT_THREADS - 1) / OPT_THREADS + 1);
   clip_adam_kernel<<<blocks, OPT_THREADS, 0, (cudaStream_t)stream>>>(p, g, m, v, n, norm, a);
   return check_launch("ss_clip_adam");
 }

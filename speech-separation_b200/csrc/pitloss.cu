@@ -168,6 +168,7 @@ pit_bwd_kernel(const float* __restrict__ z, long long ldz, const float* __restri
     }
     tile[ty + 8 * i][tx] = v;
   }
+  if (!dzT) return;                                            // (block-uniform) only the transposed-copy form wants it
   __syncthreads();
 #pragma unroll
   for (int i = 0; i < 4; ++i) {

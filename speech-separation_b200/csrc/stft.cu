@@ -298,7 +298,7 @@ static int launch_stft(const float* sig, const long long* sig_off, const long lo
                 (size_t)C::F * C::PITCH * (COMPLEX ? 8 : 4);
   auto kern = stft_kernel<NFFT, COMPLEX, TF, LOGMAG>;
   cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-  const int resident = 148 * C::CTAS;                                  // persistent: every SM full
+  const int resident = ssb::sm_count() * C::CTAS;                                  // persistent: every SM full
   const int grid = total_tiles < resident ? total_tiles : resident;
   kern<<<grid, C::THREADS, smem, st>>>(sig, sig_off, frame_off, tile_off, n_utts, total_tiles, hop, out);
   return check_launch("ss_stft");

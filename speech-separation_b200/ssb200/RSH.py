@@ -115,17 +115,16 @@ class SepDNN(uPIT.SepDNN):
         self.gpuid = gpuid
         self.feat_dim = int(kwargs.get("feat_dim", 257))
         self.num_spk = 1                                  # one mask per pass
-        self.num_layers = 2
+        self.num_layers = int(kwargs.get("num_layers", 2))    # reference: 2 (archs/RSH.py:155)
         for key in kwargs:
             print("modelparam:", key, kwargs[key])
-        self.blstm = nn.LSTM(self.feat_dim * 2, HID, num_layers=2, bidirectional=True)
+        self.blstm = nn.LSTM(self.feat_dim * 2, HID, num_layers=self.num_layers, bidirectional=True)
         self.lin = nn.Linear(HID * 2, self.feat_dim)
         self.bn = nn.BatchNorm1d(HID * 2)
         self.in_dim, self.out_dim = 2 * self.feat_dim, self.feat_dim
         self._wt = None
         self._wt_versions = None
         self._ws = {}
-        self.max_workspaces = 8
         self.last = None
 
     def forward(self, x):
@@ -148,42 +147,85 @@ def _unpack_sub(model, sub, n_spk, dev):
     return batch
 
 
+def _forward_passes(model, batch_sample, save, hidden_fn=None):
+    """All sub-batches and passes of archs/RSH.py:205-257.  Returns (subs, stats, last_n): stats = the device accumulator
+    {sum of min losses / S, norm, loss, 1/(S_last * norm)}, subs = what the backward pass needs."""
+    dev = model.lin.weight.device
+    F = model.feat_dim
+    stats = torch.zeros(4, dtype=torch.float32, device=dev)
+    subs, first, last_n, hidden = [], True, 1, None
+    for n in range(batch_sample.max_spk):
+        B = batch_sample.sub_batch_lens[n]
+        if B == 0:
+            continue
+        hidden = model.init_hidden(B) if hidden_fn is None else hidden_fn(B)   # drawn even when n == 0, like the reference (H1)
+        if n == 0:
+            continue
+        batch = _unpack_sub(model, batch_sample[n], n, dev)
+        used = torch.zeros(B, dtype=torch.int32, device=dev)
+        x, passes = batch["combo"], []
+        for k in range(n):
+            run_forward(model, batch, hidden, save, slot=(n, k), x=x)
+            ws = batch["ws"]
+            engine.pit_loss(ws, batch["mix"], batch["src"], batch["lens_dev"], F, 1, n, mode=1,
+                            accumulate=not first, used=used, stats=stats)
+            first = False
+            nxt = torch.empty_like(x)
+            call("rsh_residual", x, ws.z, LL(ws.ldz), batch["lens_dev"], ws.T, ws.B, F, 1, nxt, stream_ptr())
+            passes.append({"ws": ws, "x": x, "h0": hidden[0].contiguous(), "c0": hidden[1].contiguous(),
+                           "losses": ws.losses[:n], "idx": ws.idx, "T": ws.T, "B": ws.B})
+            hidden = (ws.hn, ws.cn)                       # state carried into the next pass (H5)
+            x = nxt
+        subs.append({"n": n, "batch": batch, "passes": passes})
+        last_n = n
+    model.hidden = hidden if subs else None
+    model.last = {"subs": subs, "stats": stats}
+    return subs, stats, last_n
+
+
+def _backward_passes(model, subs, stats, last_n, grads, gloss, hook=None):
+    """Backward through every pass in reverse, accumulating the weight gradients into `grads` (written, not added to, by
+    the first pass processed).  gloss: None (= 1) or a 1-element device tensor; hook: bucket callback of the last pass."""
+    F = model.feat_dim
+    p = {k: v.detach() for k, v in model.param_dict().items()}
+    acc = False
+    todo = sum(s["n"] for s in subs)
+    for sub in reversed(subs):
+        n, batch = sub["n"], sub["batch"]
+        wt = batch["wt"]
+        # stats[3] = 1/(S_last * norm): rescale to this sub-batch's 1/(n * norm)
+        scale = float(last_n) / n
+        if gloss is None:
+            gout = None if scale == 1.0 else torch.full((1,), scale, dtype=torch.float32, device=stats.device)
+        else:
+            gout = (gloss.detach().to(torch.float32) * scale).reshape(1).contiguous()
+        carry = dmask = dhn = dcn = None
+        for k in reversed(range(n)):
+            ps = sub["passes"][k]
+            more = k > 0
+            todo -= 1
+            ps["ws"].bind(ps["T"], ps["B"])
+            dx, dh0, dc0 = engine.backward(ps["ws"], wt, p, grads, batch["mix"], batch["src"], batch["lens_dev"],
+                                           ps["h0"], ps["c0"], F, 1, gout, dmask_extra=dmask, dhn=dhn, dcn=dcn,
+                                           want_dx=more, want_d0=more, training=model.training, accumulate=acc,
+                                           stats=stats, hook=hook if todo == 0 else None)
+            acc = True
+            if more:
+                TB = ps["ws"].TB
+                new_carry = torch.empty(TB, F, dtype=torch.float32, device=dx.device)
+                dmask = torch.empty(TB, F, dtype=torch.float32, device=dx.device)
+                call("rsh_residual_bwd", dx, carry, ps["x"], LL(TB), F, new_carry, dmask, stream_ptr())
+                carry, dhn, dcn = new_carry, dh0, dc0
+
+
 class _RSHLoss(torch.autograd.Function):
     """loss over all sub-batches and passes; backward = the hand-written kernels, passes in reverse."""
 
     @staticmethod
     def forward(ctx, model, batch_sample, save, *params):
-        dev = model.lin.weight.device
-        F = model.feat_dim
-        stats = torch.zeros(4, dtype=torch.float32, device=dev)
-        subs, first, last_n = [], True, 1
-        for n in range(batch_sample.max_spk):
-            B = batch_sample.sub_batch_lens[n]
-            if B == 0:
-                continue
-            hidden = model.init_hidden(B)                     # drawn even when n == 0, like the reference (H1)
-            if n == 0:
-                continue
-            batch = _unpack_sub(model, batch_sample[n], n, dev)
-            used = torch.zeros(B, dtype=torch.int32, device=dev)
-            x, passes = batch["combo"], []
-            for k in range(n):
-                run_forward(model, batch, hidden, save, slot=(n, k), x=x)
-                ws = batch["ws"]
-                engine.pit_loss(ws, batch["mix"], batch["src"], batch["lens_dev"], F, 1, n, mode=1,
-                                accumulate=not first, used=used, stats=stats)
-                first = False
-                nxt = torch.empty_like(x)
-                call("rsh_residual", x, ws.z, LL(ws.ldz), batch["lens_dev"], ws.T, ws.B, F, 1, nxt, stream_ptr())
-                passes.append({"ws": ws, "x": x, "c0": hidden[1].contiguous(), "losses": ws.losses[:n], "idx": ws.idx})
-                hidden = (ws.hn, ws.cn)                       # state carried into the next pass (H5)
-                x = nxt
-            subs.append({"n": n, "batch": batch, "passes": passes})
-            last_n = n
+        subs, stats, last_n = _forward_passes(model, batch_sample, save)
         ctx.model, ctx.subs, ctx.saved, ctx.stats, ctx.last_n = model, subs, save, stats, last_n
         ctx.names = [k for k, _ in model.named_parameters()]
-        model.hidden = hidden if subs else None
-        model.last = {"subs": subs, "stats": stats}
         loss, norm = stats[2].clone(), stats[1].clone()
         ctx.mark_non_differentiable(norm)
         return loss, norm
@@ -193,30 +235,9 @@ class _RSHLoss(torch.autograd.Function):
         if not ctx.saved:
             raise RuntimeError("RSH loss was computed without saving activations (no_grad / eval)")
         model = ctx.model
-        F = model.feat_dim
-        p = {k: v.detach() for k, v in model.param_dict().items()}
+        p = model.param_dict()
         grads = {k: torch.zeros_like(p[k]) for k in ctx.names}
-        acc = False
-        for sub in reversed(ctx.subs):
-            n, batch = sub["n"], sub["batch"]
-            wt = batch["wt"]
-            # stats[3] = 1/(S_last * norm): rescale to this sub-batch's 1/(n * norm)
-            gout = (gloss.detach().to(torch.float32) * (float(ctx.last_n) / n)).reshape(1).contiguous()
-            carry = dmask = dhn = dcn = None
-            for k in reversed(range(n)):
-                ps = sub["passes"][k]
-                more = k > 0
-                dx, dh0, dc0 = engine.backward(ps["ws"], wt, p, grads, batch["mix"], batch["src"], batch["lens_dev"],
-                                               ps["c0"], F, 1, gout, dmask_extra=dmask, dhn=dhn, dcn=dcn,
-                                               want_dx=more, want_d0=more, training=model.training, accumulate=acc,
-                                               stats=ctx.stats)
-                acc = True
-                if more:
-                    TB = ps["ws"].TB
-                    new_carry = torch.empty(TB, F, dtype=torch.float32, device=dx.device)
-                    dmask = torch.empty(TB, F, dtype=torch.float32, device=dx.device)
-                    call("rsh_residual_bwd", dx, carry, ps["x"], LL(TB), F, new_carry, dmask, stream_ptr())
-                    carry, dhn, dcn = new_carry, dh0, dc0
+        _backward_passes(model, ctx.subs, ctx.stats, ctx.last_n, grads, gloss)
         return (None, None, None) + tuple(grads[k] for k in ctx.names)
 
 
@@ -227,6 +248,18 @@ def compute_loss(model, epoch, batch_sample, plotdir=""):
     save = torch.is_grad_enabled() and any(q.requires_grad for q in params)
     loss, norm = _RSHLoss.apply(model, batch_sample, save, *params)
     return loss, norm.detach()
+
+
+def loss_and_grads(model, batch_sample, grads, hook=None, hidden=None):
+    """compute_loss + loss.backward() without the autograd tape (same contract as ssb200.uPIT.loss_and_grads): every
+    parameter gradient is written straight into grads[name] (e.g. views of ssb200.train.Trainer's flat bucket);
+    `hook(tag)` fires for each gradient bucket once the LAST pass has enqueued it.  Returns device scalars (loss, norm)."""
+    with torch.no_grad():
+        subs, stats, last_n = _forward_passes(model, batch_sample, True, hidden_fn=hidden)
+        if not subs:
+            raise ValueError("RSH.loss_and_grads: the batch holds no utterance with at least one speaker")
+        _backward_passes(model, subs, stats, last_n, grads, None, hook=hook)
+    return stats[2], stats[1]
 
 
 def compute_cv_loss(model, epoch, batch_sample, plotdir=""):

@@ -1,11 +1,26 @@
-"""Host orchestration of the BLSTM mask estimator step: which kernel runs on which buffer.
+"""Host orchestration of the BLSTM mask estimator step: which kernel runs on which buffer, on which stream.
 
 Mirrors what `SepDNN.forward` + `compute_loss` + `loss.backward()` do in the reference
 (archs/uPIT.py:129-147,157-206; archs/RSH.py:169-187,197-259; steps/train_qsub.py:120), but every
-arithmetic step is a libssb200 kernel; torch only owns the device buffers.
+arithmetic step is a libssb200 kernel; torch only owns the device buffers and the streams.
 
 Layouts: activations time-major padded, row = t*B + b.  LSTM gate columns interleaved (dir*4H + 4u + gate).
+
+Streaming.  A recurrence kernel occupies 100 (forward) / 80 (backward, K-split) of the 148 SMs for milliseconds and
+reports per direction how many frames are finished (`progress`, include/ssb200.h).  The GEMM that consumes its output
+does not wait for the kernel to end: it is cut into time chunks x direction halves, each launched on a side stream
+behind a stream-ordered wait on the progress counter and capped to the idle SMs --
+
+  forward   x-projection of layer l+1:  gx[l+1][rows] (+)= out[l][rows, dir half] . W_ih[l+1][:, dir half]^T
+  backward  dX of layer l:              dout[l-1][rows] (+)= dG[l][rows, dir half] . W_ih[l][dir half, :]
+            dW_hh[l], (l = 0: dW_ih[0]) accumulated over row blocks as the gate gradients appear;
+            dW_ih[l >= 1] and the head's weight gradients ride under the NEXT recurrence
+
+-- so that only the chunk the recurrence finishes last is left for the main stream.  Weight gradients use the "TN"
+GEMM form (ss_gemm_sb16_tn): activations and gate gradients are read as they were written, no transposed copies.
 """
+import ctypes
+
 import torch
 
 from . import ops
@@ -14,13 +29,18 @@ from .ops import SB16, up8
 
 H = 600          # archs/uPIT.py:115, archs/RSH.py:155 (hard-coded in the reference)
 UNIT4 = 1
+STREAM = True    # stream GEMMs under the recurrences (module switch for A/B tests; results are identical either way)
+N_CHUNKS = 8     # time chunks of a streamed GEMM
+MIN_STREAM_T = 48
 
 
-def _sb_view(sb, row0, rows):
-    """Rows [row0,row0+rows) of an SB16 as a new SB16 sharing storage (plane stride unchanged)."""
+def _sb_view(sb, row0=0, rows=None, col0=0, cols=None):
+    """Rows [row0, +rows) x columns [col0, +cols) of an SB16 as a new SB16 sharing storage (pitch and plane stride kept)."""
     v = SB16.__new__(SB16)
-    v.rows, v.cols, v.ld, v.plane = rows, sb.cols, sb.ld, sb.plane
-    v.buf = sb.buf[row0 * sb.ld:]
+    v.rows = sb.rows - row0 if rows is None else rows
+    v.cols = sb.cols - col0 if cols is None else cols
+    v.ld, v.plane = sb.ld, sb.plane
+    v.buf = sb.buf[row0 * sb.ld + col0:]
     return v
 
 
@@ -68,56 +88,175 @@ class Weights:
             _split_into(p["lin.weight"], None, outT=self.linT)
 
 
-class Workspace:
-    """All activation / gradient buffers for one (T, B) shape."""
+def _ws_bytes(B):
+    fn = lib().ss_lstm_ws_bytes
+    fn.restype = ctypes.c_longlong
+    return int(fn(int(B), H))
 
-    def __init__(self, T, B, in_dim, out_dim, n_src, num_layers, device, training=True):
-        self.T, self.B, self.in_dim, self.out_dim, self.L = T, B, in_dim, out_dim, num_layers
-        TB = T * B
-        self.TB = TB
+
+class Workspace:
+    """All activation / gradient buffers of one model step, sized by CAPACITY (rows = T*B, batch B): a shuffled loader
+    yields a new T_max almost every batch (steps/train_qsub.py:81), so `bind(T, B)` only re-points the views; nothing is
+    allocated or cleared unless a batch exceeds the capacity (SepDNN.workspace then grows it)."""
+
+    def __init__(self, cap_rows, cap_B, in_dim, out_dim, n_src, num_layers, device, training=True):
+        self.cap_rows, self.cap_B = int(cap_rows), int(cap_B)
+        self.in_dim, self.out_dim, self.L, self.device = in_dim, out_dim, num_layers, device
+        R, Bc = self.cap_rows, self.cap_B
         f32 = dict(dtype=torch.float32, device=device)
-        self.x0 = SB16(TB, in_dim, device)
-        self.gx = [torch.empty(TB, 8 * H, **f32) for _ in range(num_layers)]
-        self.out = [SB16(TB, 2 * H, device) for _ in range(num_layers)]
-        self.hn = torch.empty(2 * num_layers, B, H, **f32)
-        self.cn = torch.empty(2 * num_layers, B, H, **f32)
-        lib().ss_lstm_ws_bytes.restype = __import__("ctypes").c_longlong
-        self.lstm_ws = torch.empty(int(lib().ss_lstm_ws_bytes(B, H)), dtype=torch.uint8, device=device)
+        self.x0 = SB16(R, in_dim, device)
+        self.gx = [torch.empty(R, 8 * H, **f32) for _ in range(num_layers)]
+        self.out = [SB16(R, 2 * H, device) for _ in range(num_layers)]
+        self._hn = torch.empty(2 * num_layers * Bc * H, **f32)
+        self._cn = torch.empty(2 * num_layers * Bc * H, **f32)
+        self.lstm_ws = torch.empty(max(_ws_bytes(Bc), _ws_bytes(min(Bc, 64))), dtype=torch.uint8, device=device)
         self.coef = torch.empty(5, 2 * H, **f32)
-        self.bn_partial = torch.empty(2 * max(1, lib().ss_bn_parts(TB)) * 2 * H, **f32)
+        self.bn_partial = torch.empty(2 * max(1, lib().ss_bn_parts(R)) * 2 * H, **f32)
         self.ldz = (out_dim + 3) // 4 * 4
-        self.z = torch.empty(TB, self.ldz, **f32)
-        self.pit_partial = torch.empty(max(1, lib().ss_pit_chunks(T)) * B * 16, **f32)
-        self.losses = torch.empty(24, B, **f32)
-        self.idx = torch.empty(B, dtype=torch.int32, device=device)
-        self.assign = torch.empty(B, 4, dtype=torch.int32, device=device)
-        self.used = torch.zeros(B, dtype=torch.int32, device=device)
+        self.z = torch.empty(R, self.ldz, **f32)
+        # ss_pit_chunks(T) * B * 16 floats, and chunks(T) * B <= chunks(T * B) + B
+        self.pit_partial = torch.empty((lib().ss_pit_chunks(R) + Bc + 1) * 16, **f32)
+        self._losses = torch.empty(24 * Bc, **f32)
+        self._idx = torch.empty(Bc, dtype=torch.int32, device=device)
+        self._assign = torch.empty(Bc * 4, dtype=torch.int32, device=device)
+        self._used = torch.zeros(Bc, dtype=torch.int32, device=device)
         self.stats = torch.zeros(4, **f32)
+        # progress counters of the recurrence kernels: [fwd dir0, fwd dir1, bwd dir0, bwd dir1]; values only grow
+        self.progress = torch.zeros(4, dtype=torch.int32, device=device)
+        self.prog_base = 0
         self.training = training
         if training:
-            self.x0T = SB16(in_dim, TB, device)
-            self.outT = [SB16(2 * H, TB, device) for _ in range(num_layers)]
-            self.hprevT = [SB16(2 * H, TB, device) for _ in range(num_layers)]
-            self.cs = [torch.empty(TB, 2 * H, **f32) for _ in range(num_layers)]
-            self.dz = SB16(TB, out_dim, device)
-            self.dzT = SB16(out_dim, TB, device)
-            self.dy = torch.empty(TB, 2 * H, **f32)           # dY -> dout of the top layer (in place)
-            self.dout = torch.empty(TB, 2 * H, **f32)         # dout of lower layers
+            self.cs = [torch.empty(R, 2 * H, **f32) for _ in range(num_layers)]
+            self.dz = SB16(R, out_dim, device)
+            self.dy = torch.empty(R, 2 * H, **f32)            # dY -> dout of the top layer (in place)
+            self.dout = torch.empty(R, 2 * H, **f32)          # dout of lower layers
             # one gradient buffer per layer: the upper layer's weight-gradient GEMMs still read theirs while the lower
             # layer's recurrence writes its own (see backward())
-            self.dG = [SB16(TB, 8 * H, device) for _ in range(num_layers)]
-            self.dGT = [SB16(8 * H, TB, device) for _ in range(num_layers)]
+            self.dG = [SB16(R, 8 * H, device) for _ in range(num_layers)]
             self.G = torch.empty(out_dim, 2 * H, **f32)
             self.bn_bwd = torch.empty(2, 2 * H, **f32)
-            self.cs_partial = [torch.empty(max(1, lib().ss_colsum_parts(TB)) * 8 * H, **f32) for _ in range(num_layers + 1)]
+            self.cs_partial = [torch.empty(max(1, lib().ss_colsum_parts(R)) * 8 * H, **f32) for _ in range(num_layers + 1)]
             self.db_l = [torch.empty(8 * H, **f32) for _ in range(num_layers)]
-            self.start_flag = torch.zeros(1, dtype=torch.int32, device=device)
-            self.start_seq = 0
             self.bwd_sync = torch.empty(256, dtype=torch.uint8, device=device)
+            self.dsum = torch.empty(out_dim, **f32)
+            self.dlinW = torch.empty(out_dim, 2 * H, **f32)
+            self.dgamma = torch.empty(2 * H, **f32)
+            self.dbeta = torch.empty(2 * H, **f32)
+        self.T = self.B = self.TB = 0
+
+    def fits(self, T, B):
+        return T * B <= self.cap_rows and B <= self.cap_B
+
+    def bind(self, T, B):
+        assert self.fits(T, B)
+        self.T, self.B, self.TB = int(T), int(B), int(T) * int(B)
+        L2 = 2 * self.L
+        self.hn = self._hn[:L2 * B * H].view(L2, B, H)
+        self.cn = self._cn[:L2 * B * H].view(L2, B, H)
+        self.losses = self._losses[:24 * B].view(24, B)
+        self.idx = self._idx[:B]
+        self.assign = self._assign[:4 * B].view(B, 4)
+        self.used = self._used[:B]
+        return self
+
+    def next_base(self):
+        """A fresh base for a recurrence launch's progress values (cyclic 32-bit comparison on the waiting side)."""
+        self.prog_base = (self.prog_base + self.T + 8) & 0xFFFFFFFF
+        return self.prog_base
 
 
-def _gemm(a, b, out, bias=None, alpha=1.0, beta=0.0, rowmap=0, hidden=0, M=None, N=None, K=None):
-    return ops.gemm(a, b, out=out, bias=bias, alpha=alpha, beta=beta, rowmap=rowmap, hidden=hidden, M=M, N=N, K=K)
+def _gemm(a, b, out, bias=None, alpha=1.0, beta=0.0, rowmap=0, hidden=0, M=None, N=None, K=None, sm_limit=0):
+    return ops.gemm(a, b, out=out, bias=bias, alpha=alpha, beta=beta, rowmap=rowmap, hidden=hidden, M=M, N=N, K=K,
+                    sm_limit=sm_limit)
+
+
+_SIDE, _SMS = {}, {}
+
+
+def _dev_index(device):
+    d = torch.device(device)
+    return d.index if d.index is not None else torch.cuda.current_device()
+
+
+def _side_stream(device):
+    key = _dev_index(device)
+    if key not in _SIDE:
+        _SIDE[key] = torch.cuda.Stream(device=device)
+    return _SIDE[key]
+
+
+def idle_sms(device, backward, B):
+    """SMs a recurrence kernel leaves free: it runs 100 CTAs forward (2 x 50), 80 backward in the K-split form
+    (B <= 64), 76 in the generic backward form, one per SM."""
+    key = _dev_index(device)
+    if key not in _SMS:
+        _SMS[key] = torch.cuda.get_device_properties(key).multi_processor_count
+    used = (80 if B <= 64 else 76) if backward else 100
+    return max(8, _SMS[key] - used)
+
+
+def _chunks(T, n):
+    """Frame ranges [(a, b)] of n nearly equal time chunks."""
+    n = max(1, min(n, T))
+    cuts = [round(i * T / n) for i in range(n + 1)]
+    return [(cuts[i], cuts[i + 1]) for i in range(n) if cuts[i + 1] > cuts[i]]
+
+
+class _Streamer:
+    """Side-stream jobs gated on the progress counters of the recurrence kernel that is running on the main stream."""
+
+    def __init__(self, ws, device, backward, nsteps):
+        self.ws, self.device = ws, device
+        self.side = _side_stream(device)
+        self.flag0 = 2 if backward else 0
+        # largest value the kernel is certain to report (include/ssb200.h: every 4th step, never the last ones)
+        if backward:
+            self.max_reported = 4 * ((nsteps - 1) // 4) if nsteps - 1 >= 4 else -1
+        else:
+            self.max_reported = 4 * ((nsteps - 1) // 4) - 1 if nsteps - 1 >= 4 else -1
+        self.sm_limit = idle_sms(device, backward, ws.B)
+        self.jobs, self.late = [], []
+        self.base = ws.next_base()
+
+    def add(self, waits, fn, order=0):
+        """fn(sm_limit) may run once, for every (direction, steps) in `waits`, that many steps of the direction are
+        finished; waits = () means as soon as the kernel is up.  Jobs the counters cannot announce run after the
+        kernel (run_late)."""
+        waits = tuple(waits) or ((0, 1),)
+        ready = max(r for _, r in waits)
+        if ready <= self.max_reported:
+            self.jobs.append((ready, order, waits, fn))
+        else:
+            self.late.append((ready, order, fn))
+
+    def launch(self):
+        """Enqueue the gated jobs on the side stream (call right AFTER the recurrence launch has succeeded)."""
+        if not self.jobs:
+            return
+        ev = torch.cuda.Event()
+        ev.record()
+        self.side.wait_event(ev)                               # inputs that precede the recurrence on the main stream
+        with torch.cuda.stream(self.side):
+            for ready, _, waits, fn in sorted(self.jobs, key=lambda j: (j[0], j[1])):
+                for direction, steps in waits:
+                    call("stream_wait_value32", stream_ptr(), self.ws.progress[self.flag0 + direction:],
+                         ctypes.c_uint((self.base + steps) & 0xFFFFFFFF))
+                fn(self.sm_limit)
+
+    def run_late(self):
+        """After the recurrence, on the main stream: join the side stream, then the jobs the kernel finished last."""
+        if self.jobs:
+            torch.cuda.current_stream().wait_stream(self.side)
+        for _, _, fn in sorted(self.late, key=lambda j: (j[0], j[1])):
+            fn(0)
+
+
+def _lstm_fwd(ws, wt, l, h0, c0, lens_dev, training, sj):
+    o = ws.out[l]
+    call("lstm_fwd", ws.gx[l], wt.whh_r[l].buf, LL(wt.whh_r[l].ld), LL(wt.whh_r[l].plane),
+         h0[2 * l:2 * l + 2], c0[2 * l:2 * l + 2], lens_dev, o.buf, LL(o.plane), ws.cs[l] if training else None,
+         ws.hn[2 * l:2 * l + 2], ws.cn[2 * l:2 * l + 2], ws.lstm_ws, ws.progress if sj else None,
+         ctypes.c_uint(sj.base if sj else 0), ws.T, ws.B, H, stream_ptr())
 
 
 def forward(ws, wt, p, x, lens_dev, h0, c0, bn_train, save=True, bn_momentum=0.1, bn_eps=1e-5):
@@ -127,35 +266,39 @@ def forward(ws, wt, p, x, lens_dev, h0, c0, bn_train, save=True, bn_momentum=0.1
     training = save
     T, B, TB = ws.T, ws.B, ws.TB
     st = stream_ptr()
-    _split_into(x, ws.x0, outT=ws.x0T if training else None)
-    inp = ws.x0
+    _split_into(x, ws.x0)
+    _gemm(ws.x0, wt.wih[0], ws.gx[0], bias=wt.bias[0], M=TB)
+    stream = STREAM and T >= MIN_STREAM_T
     for l in range(ws.L):
-        _gemm(inp, wt.wih[l], ws.gx[l], bias=wt.bias[l])
-        o = ws.out[l]
-        inline_T = training and not OVERLAP                    # transposed copies inside the call, on this stream
-        call("lstm_fwd", ws.gx[l], wt.whh_r[l].buf, LL(wt.whh_r[l].ld), LL(wt.whh_r[l].plane),
-             h0[2 * l:2 * l + 2], c0[2 * l:2 * l + 2], lens_dev, o.buf, LL(o.plane),
-             ws.outT[l].buf if inline_T else None, ws.hprevT[l].buf if inline_T else None,
-             LL(ws.outT[l].ld if inline_T else 0), LL(ws.outT[l].plane if inline_T else 0),
-             ws.cs[l] if training else None, ws.hn[2 * l:2 * l + 2], ws.cn[2 * l:2 * l + 2], ws.lstm_ws, T, B, H, st)
-        if training and OVERLAP:
-            # only the backward pass reads outT / hprevT: the side stream makes them while the next GEMM and
-            # recurrence run (backward() joins the side stream before it needs them)
-            side, ev = _side_stream(x.device), torch.cuda.Event()
-            ev.record()
-            side.wait_event(ev)
-            with torch.cuda.stream(side):
-                oT, hT = ws.outT[l], ws.hprevT[l]
-                call("transpose_sb16", o.buf, LL(o.ld), LL(o.plane), TB, 2 * H, oT.buf, LL(oT.ld), LL(oT.plane), stream_ptr())
-                call("hprev_transpose", o.buf, LL(o.ld), LL(o.plane), T, B, H, lens_dev, h0[2 * l:2 * l + 2], hT.buf,
-                     LL(hT.ld), LL(hT.plane), stream_ptr())
-        inp = o
+        nxt = l + 1 < ws.L
+        sj = _Streamer(ws, x.device, False, T) if (stream and nxt) else None
+        _lstm_fwd(ws, wt, l, h0, c0, lens_dev, training, sj)
+        if not nxt:
+            break
+        if sj is None:
+            _gemm(ws.out[l], wt.wih[l + 1], ws.gx[l + 1], bias=wt.bias[l + 1], M=TB)
+            continue
+        # x-projection of layer l+1, streamed: direction d's half of out[l] for frames [a, b) is final after b steps of
+        # direction 0 (t = 0..) / T - a steps of direction 1 (t = T-1..); whichever half of a chunk comes first writes
+        # (beta = 0, + bias), the other accumulates
+        o, w, gx, bias = ws.out[l], wt.wih[l + 1], ws.gx[l + 1], wt.bias[l + 1]
+        for (a, b) in _chunks(T, N_CHUNKS):
+            r0, rows = a * B, (b - a) * B
+            ready = (b, T - a)
+            first = 0 if ready[0] <= ready[1] else 1
+            for d in (0, 1):
+                def job(sm_limit, d=d, r0=r0, rows=rows, acc=(d != first)):
+                    _gemm(_sb_view(o, r0, rows, d * H, H), _sb_view(w, 0, 8 * H, d * H, H), gx[r0:], bias=None if acc else bias,
+                          beta=1.0 if acc else 0.0, M=rows, N=8 * H, K=H, sm_limit=sm_limit)
+                sj.add(((d, ready[d]),), job, order=0 if d == first else 1)
+        sj.launch()
+        sj.run_late()
     top = ws.out[-1]
     call("bn_stats", top.buf, LL(top.ld), LL(top.plane), TB, 2 * H, p["bn.weight"], p["bn.bias"], float(bn_eps),
          float(bn_momentum), int(bn_train), p["bn.running_mean"], p["bn.running_var"], ws.bn_partial, ws.coef, st)
     _split_into(p["lin.weight"], wt.lin_folded, col_scale=ws.coef[0])
     call("head_fold_bias", p["lin.weight"], p["lin.bias"], ws.coef, ws.out_dim, 2 * H, wt.bias_folded, st)
-    _gemm(top, wt.lin_folded, ws.z, bias=wt.bias_folded)
+    _gemm(top, wt.lin_folded, ws.z, bias=wt.bias_folded, M=TB)
     return ws.z
 
 
@@ -169,60 +312,79 @@ def pit_loss(ws, mix, src, lens_dev, F, n_out, n_src, mode=0, accumulate=False, 
          ws.stats if stats is None else stats, st)
 
 
-def backward(ws, wt, p, grads, mix, src, lens_dev, c0, F, n_out, gout, dmask_extra=None, dhn=None, dcn=None,
+def _gemm_tn(a, a_col0, a_col_batch, b, b_col0, b_col_batch, R, blk0, n_blk, shifts, batch, c0, c1, ldc, M, N, beta,
+             rowmap, hidden, sm_limit):
+    call("gemm_sb16_tn", a.buf, LL(a.ld), LL(a.plane), a.cols, a_col0, a_col_batch,
+         b.buf, LL(b.ld), LL(b.plane), b.cols, b_col0, b_col_batch, R, blk0[0], blk0[1], n_blk, shifts[0], shifts[1],
+         batch, c0, c1, LL(ldc), M, N, 1.0, float(beta), rowmap, hidden, sm_limit, stream_ptr())
+
+
+def _block_chunks(nblk, n):
+    """Sizes of n nearly equal runs of 64-row blocks."""
+    n = max(1, min(n, nblk))
+    cuts = [round(i * nblk / n) for i in range(n + 1)]
+    return [cuts[i + 1] - cuts[i] for i in range(n) if cuts[i + 1] > cuts[i]]
+
+
+def backward(ws, wt, p, grads, mix, src, lens_dev, h0, c0, F, n_out, gout, dmask_extra=None, dhn=None, dcn=None,
              want_dx=False, want_d0=False, training=True, accumulate=False, hook=None, stats=None):
     """Backward of loss -> every parameter gradient in `grads` (dict name -> fp32 tensor, natural layouts).
     Returns (dx or None, dh0 or None, dc0 or None)."""
     T, B, TB = ws.T, ws.B, ws.TB
-    st = stream_ptr()
+    dev = mix.device
     O = ws.out_dim
-    beta = 1.0 if accumulate else 0.0
+    beta0 = 1.0 if accumulate else 0.0
+    nblk = (TB + 63) // 64
     call("pit_loss_bwd", ws.z, LL(ws.ldz), mix, src, lens_dev, ws.assign, T, B, F, n_out,
          ws.stats if stats is None else stats, gout, dmask_extra,
-         ws.dz.buf, LL(ws.dz.ld), LL(ws.dz.plane), ws.dzT.buf, LL(ws.dzT.ld), LL(ws.dzT.plane), st)
-    top, topT = ws.out[-1], ws.outT[-1]
-    # head: dlin.bias = colsum(dz); G = dz^T x; dW = s*(G - mean*dsum) + beta*dsum; dY = dz W
-    dsum = ws.dsum if hasattr(ws, "dsum") else None
-    if dsum is None:
-        dsum = ws.dsum = torch.empty(O, dtype=torch.float32, device=mix.device)
-        ws.dlinW = torch.empty(O, 2 * H, dtype=torch.float32, device=mix.device)
-        ws.dgamma = torch.empty(2 * H, dtype=torch.float32, device=mix.device)
-        ws.dbeta = torch.empty(2 * H, dtype=torch.float32, device=mix.device)
-        ws.db = torch.empty(8 * H, dtype=torch.float32, device=mix.device)
-    def head_weight_grads():
-        """dlin.weight, dlin.bias (needs dz only: off the critical path), then the bucket hook."""
+         ws.dz.buf, LL(ws.dz.ld), LL(ws.dz.plane), None, LL(0), LL(0), stream_ptr())
+    top = ws.out[-1]
+
+    def head_weight_grads(sm_limit):
+        """dlin.bias = colsum(dz); G = dz^T top; dlin.weight = s*(G - mean*dsum) + beta*dsum (needs dz only: off the
+        critical path), then the bucket hook."""
         s = stream_ptr()
-        call("colsum_sb16", ws.dz.buf, LL(ws.dz.ld), LL(ws.dz.plane), TB, O, ws.cs_partial[-1], dsum, 0, 0, s)
-        _gemm(ws.dzT, topT, ws.G, K=TB)
-        call("head_dw_fix", ws.G, dsum, ws.coef, p["bn.bias"], O, 2 * H, ws.dlinW, s)
+        call("colsum_sb16", ws.dz.buf, LL(ws.dz.ld), LL(ws.dz.plane), TB, O, ws.cs_partial[-1], ws.dsum, 0, 0, s)
+        _gemm_tn(ws.dz, 0, 0, top, 0, 0, TB, (0, 0), nblk, (0, 0), 1, ws.G, None, 2 * H, O, 2 * H, 0.0, 0, 0, sm_limit)
+        call("head_dw_fix", ws.G, ws.dsum, ws.coef, p["bn.bias"], O, 2 * H, ws.dlinW, s)
         _acc(grads, "lin.weight", ws.dlinW, accumulate)
-        _acc(grads, "lin.bias", dsum, accumulate)
+        _acc(grads, "lin.bias", ws.dsum, accumulate)
         if hook is not None:
             hook("head")
 
-    _gemm(ws.dz, wt.linT, ws.dy, K=O)
+    _gemm(ws.dz, wt.linT, ws.dy, M=TB, K=O)
     call("bn_bwd", ws.dy, top.buf, LL(top.ld), LL(top.plane), TB, 2 * H, ws.coef, int(training), ws.bn_partial,
-         ws.dgamma, ws.dbeta, ws.bn_bwd, st)
+         ws.dgamma, ws.dbeta, ws.bn_bwd, stream_ptr())
     _acc(grads, "bn.weight", ws.dgamma, accumulate)
     _acc(grads, "bn.bias", ws.dbeta, accumulate)
     dout = ws.dy
     dx = dh0 = dc0 = None
     if want_d0:
-        dh0 = torch.zeros(2 * ws.L, B, H, dtype=torch.float32, device=mix.device)
-        dc0 = torch.zeros(2 * ws.L, B, H, dtype=torch.float32, device=mix.device)
+        dh0 = torch.zeros(2 * ws.L, B, H, dtype=torch.float32, device=dev)
+        dc0 = torch.zeros(2 * ws.L, B, H, dtype=torch.float32, device=dev)
 
-    def weight_grads(l):
-        """dW_ih, dW_hh (both directions per launch: rows d*4H.. of dGT; d*H.. of hprevT), biases; then the bucket hook."""
+    def g_pair(kind, l):
+        g0, g1 = grads["blstm.weight_%s_l%d" % (kind, l)], grads["blstm.weight_%s_l%d_reverse" % (kind, l)]
+        assert g0.stride(0) == g1.stride(0) and g0.stride(1) == 1
+        return g0, g1
+
+    def dw_chunk(l, kind, blk0, n_blk, beta, sm_limit):
+        """Rows of 64-row blocks [blk0[z], +n_blk) of direction z's weight gradient: dW[z] (+)= dG[l][:, z]^T . X."""
+        g0, g1 = g_pair(kind, l)
+        if kind == "ih":
+            xin = ws.x0 if l == 0 else ws.out[l - 1]
+            _gemm_tn(ws.dG[l], 0, 4 * H, xin, 0, 0, TB, blk0, n_blk, (0, 0), 2, g0, g1, g0.stride(0), 4 * H, xin.cols,
+                     beta, UNIT4, H, sm_limit)
+        else:   # carried state of frame t: out[t-1] (direction 0) / out[t+1] (direction 1); the h0 term: dwhh_edge
+            _gemm_tn(ws.dG[l], 0, 4 * H, ws.out[l], 0, H, TB, blk0, n_blk, (-B, B), 2, g0, g1, g0.stride(0), 4 * H, H,
+                     beta, UNIT4, H, sm_limit)
+
+    def dw_finish(l, sm_limit=0):
+        """What needs every row of dG[l]: the h0 term of dW_hh, the bias sums; then the bucket hook."""
         s = stream_ptr()
-        dGT, xT = ws.dGT[l], (ws.x0T if l == 0 else ws.outT[l - 1])
-        if overlap:
-            dG = ws.dG[l]
-            call("transpose_sb16", dG.buf, LL(dG.ld), LL(dG.plane), TB, 8 * H, dGT.buf, LL(dGT.ld), LL(dGT.plane), s)
-        for B_op, b_rows, N, kind in ((xT, 0, xT.rows, "ih"), (ws.hprevT[l], H, H, "hh")):
-            g0, g1 = grads["blstm.weight_%s_l%d" % (kind, l)], grads["blstm.weight_%s_l%d_reverse" % (kind, l)]
-            assert g0.stride(0) == g1.stride(0) and g0.stride(1) == 1
-            call("gemm_sb16_x2", dGT.buf, LL(dGT.ld), LL(dGT.plane), 4 * H, B_op.buf, LL(B_op.ld), LL(B_op.plane),
-                 b_rows, g0, g1, LL(g0.stride(0)), 4 * H, N, TB, 1.0, float(beta), UNIT4, H, s)
+        g0, g1 = g_pair("hh", l)
+        call("dwhh_edge", ws.dG[l].buf, LL(ws.dG[l].ld), LL(ws.dG[l].plane), lens_dev, h0[2 * l:2 * l + 2], B, H, g0, g1,
+             LL(g0.stride(0)), s)
         db = ws.db_l[l]
         call("colsum_sb16", ws.dG[l].buf, LL(ws.dG[l].ld), LL(ws.dG[l].plane), TB, 8 * H, ws.cs_partial[l], db, UNIT4, H, s)
         for d, suf in enumerate(("", "_reverse")):
@@ -231,69 +393,77 @@ def backward(ws, wt, p, grads, mix, src, lens_dev, c0, F, n_out, gout, dmask_ext
         if hook is not None:
             hook("l%d" % l)
 
-    # The K-split backward recurrence occupies 80 of the 148 SMs for ~5 ms; the weight gradients of layer l+1 are not
-    # on the critical path, so they run on a side stream, capped to the idle SMs, once layer l's recurrence is
-    # resident (it raises ws.start_flag at its start; the side stream waits on that value without holding an SM).
-    overlap = OVERLAP and B <= 64
-    side = _side_stream(mix.device) if OVERLAP else None
-    main = torch.cuda.current_stream()
-    if side is not None:
-        main.wait_stream(side)                                 # the forward pass's transposed copies
-    deferred = []                                              # work that waits for the next recurrence to be resident
-
-    def defer(fn):
-        ev = torch.cuda.Event()
-        ev.record(main)                                        # its inputs are complete at this point of the main stream
-        side.wait_event(ev)
-        deferred.append(fn)
-
-    if overlap:
-        defer(head_weight_grads)
-    else:
-        head_weight_grads()
+    stream = STREAM and T >= MIN_STREAM_T
+    nsteps = T + (1 if want_d0 else 0)
+    deferred = [head_weight_grads]                             # rides under the next recurrence (or runs at the end)
     for l in range(ws.L - 1, -1, -1):
-        if deferred:
-            ws.start_seq += 1
-            call("lstm_bwd_start_flag", ws.start_flag, ws.start_seq)
+        sj = _Streamer(ws, dev, True, nsteps) if stream else None
         call("lstm_bwd", ws.gx[l], ws.cs[l], c0[2 * l:2 * l + 2], dout,
              dhn[2 * l:2 * l + 2] if dhn is not None else None, dcn[2 * l:2 * l + 2] if dcn is not None else None,
              lens_dev, wt.whhT[l].buf, LL(wt.whhT[l].ld), LL(wt.whhT[l].plane), ws.dG[l].buf, LL(ws.dG[l].plane),
-             None if overlap else ws.dGT[l].buf, LL(ws.dGT[l].ld), LL(ws.dGT[l].plane),
-             dh0[2 * l:2 * l + 2] if want_d0 else None, dc0[2 * l:2 * l + 2] if want_d0 else None, ws.bwd_sync, T, B, H,
-             stream_ptr())
-        if deferred:
-            with torch.cuda.stream(side):
-                call("stream_wait_value32", stream_ptr(), ws.start_flag, ws.start_seq)
-                call("gemm_sm_limit", IDLE_SMS)
-                for fn in deferred:
-                    fn()
-                call("gemm_sm_limit", 0)
+             dh0[2 * l:2 * l + 2] if want_d0 else None, dc0[2 * l:2 * l + 2] if want_d0 else None, ws.bwd_sync,
+             ws.progress[2:] if sj else None, ctypes.c_uint(sj.base if sj else 0), T, B, H, stream_ptr())
+        need_dx = l > 0 or want_dx
+        dxbuf = None
+        if need_dx:
+            if l > 0:   # ping-pong: the running recurrence still reads `dout` while the streamed dX writes the other buffer
+                dxbuf = ws.dout if dout is not ws.dout else ws.dy
+            else:
+                dx = dxbuf = torch.empty(TB, ws.in_dim, dtype=torch.float32, device=dev)
+        if sj is None:
+            for fn in deferred:
+                fn(0)
             deferred = []
-        if overlap and l > 0:
-            defer(lambda l=l: weight_grads(l))
+            if need_dx:
+                _gemm(ws.dG[l], wt.wihT[l], dxbuf, M=TB, K=8 * H)
+            dw_chunk(l, "hh", (0, 0), nblk, beta0, 0)
+            dw_chunk(l, "ih", (0, 0), nblk, beta0, 0)
+            dw_finish(l)
         else:
-            weight_grads(l)
-        if l > 0:
-            _gemm(ws.dG[l], wt.wihT[l], ws.dout, K=8 * H)
-            dout = ws.dout
-        elif want_dx:
-            dx = torch.empty(TB, ws.in_dim, dtype=torch.float32, device=mix.device)
-            _gemm(ws.dG[0], wt.wihT[0], dx, K=8 * H)
-    if side is not None:
-        main.wait_stream(side)
+            # (1) what the previous layer left behind: needs nothing from this recurrence
+            for i, fn in enumerate(deferred):
+                sj.add((), fn, order=-10 + i)
+            deferred = []
+            # (2) dX, on the critical path: direction 0 walks t = T-1..0, direction 1 walks t = 0..T-1
+            if need_dx:
+                wT, dG = wt.wihT[l], ws.dG[l]
+                for (a, b) in _chunks(T, N_CHUNKS):
+                    r0, rows = a * B, (b - a) * B
+                    ready = (T - a, b)
+                    first = 0 if ready[0] <= ready[1] else 1
+                    for d in (0, 1):
+                        def job(sm_limit, d=d, r0=r0, rows=rows, acc=(d != first)):
+                            _gemm(_sb_view(dG, r0, rows, d * 4 * H, 4 * H), _sb_view(wT, 0, wT.rows, d * 4 * H, 4 * H),
+                                  dxbuf[r0:], beta=1.0 if acc else 0.0, M=rows, N=wT.rows, K=4 * H, sm_limit=sm_limit)
+                        sj.add(((d, ready[d]),), job, order=0)
+            # (3) weight gradients that only need this layer's gate gradients, accumulated over row blocks in the order
+            # the two directions produce them (direction 0 from the last block down, direction 1 from the first up)
+            sizes = _block_chunks(nblk, N_CHUNKS)
+            done = 0
+            for ci, n in enumerate(sizes):
+                blk0 = (nblk - done - n, done)
+                done += n
+                # direction 0 has passed block j once T - floor(64 j / B) steps are done; direction 1 once
+                # ceil(64 (j + n) / B) are (capped at T)
+                waits = ((0, T - (blk0[0] * 64) // B), (1, min(T, -(-(blk0[1] + n) * 64 // B))))
+                kinds = ("hh", "ih") if l == 0 else ("hh",)
+                for kind in kinds:
+                    def job(sm_limit, kind=kind, blk0=blk0, n=n, beta=(beta0 if ci == 0 else 1.0)):
+                        dw_chunk(l, kind, blk0, n, beta, sm_limit)
+                    sj.add(waits, job, order=1)
+            sj.launch()
+            sj.run_late()
+            if l > 0:
+                def rest(sm_limit, l=l):
+                    dw_chunk(l, "ih", (0, 0), nblk, beta0, sm_limit)
+                    dw_finish(l, sm_limit)
+                deferred = [rest]
+            else:
+                dw_finish(l)
+        dout = dxbuf
+    for fn in deferred:
+        fn(0)
     return dx, dh0, dc0
-
-
-OVERLAP = not __import__("os").environ.get("SSB_NO_OVERLAP")
-IDLE_SMS = 68                                                  # 148 SMs - the 80 CTAs of the K-split backward recurrence
-_SIDE = {}
-
-
-def _side_stream(device):
-    key = torch.device(device).index if torch.device(device).index is not None else torch.cuda.current_device()
-    if key not in _SIDE:
-        _SIDE[key] = torch.cuda.Stream(device=device)
-    return _SIDE[key]
 
 
 def _acc(grads, name, val, accumulate):

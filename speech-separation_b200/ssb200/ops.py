@@ -238,8 +238,8 @@ def split(x, rowperm=0, hidden=0, col_scale=None, want=True, want_t=False, out=N
     return out, out_t
 
 
-def gemm(a, b, out=None, bias=None, alpha=1.0, beta=0.0, rowmap=0, hidden=0, M=None, N=None, K=None):
-    """out[M,N] = alpha * a @ b^T + bias + beta*out, a: SB16 (M,K), b: SB16 (N,K)."""
+def gemm(a, b, out=None, bias=None, alpha=1.0, beta=0.0, rowmap=0, hidden=0, M=None, N=None, K=None, sm_limit=0):
+    """out[M,N] = alpha * a @ b^T + bias + beta*out, a: SB16 (M,K), b: SB16 (N,K); sm_limit > 0 caps the grid."""
     M = a.rows if M is None else M
     N = b.rows if N is None else N
     K = a.cols if K is None else K
@@ -247,8 +247,23 @@ def gemm(a, b, out=None, bias=None, alpha=1.0, beta=0.0, rowmap=0, hidden=0, M=N
         out = torch.empty(M, N, dtype=torch.float32, device=a.buf.device)
     assert out.dtype == torch.float32 and out.stride(1) == 1
     call("gemm_sb16", a.buf, LL(a.ld), LL(a.plane), b.buf, LL(b.ld), LL(b.plane), out, LL(out.stride(0)), M, N, K, bias,
-         float(alpha), float(beta), rowmap, hidden, stream_ptr())
+         float(alpha), float(beta), rowmap, hidden, int(sm_limit), stream_ptr())
     return out
+
+
+def gemm_tn(a, b, M, N, outs=None, a_col0=0, b_col0=0, a_col_batch=0, b_col_batch=0, R=None, blk0=(0, 0), n_blk=None,
+            shifts=(0, 0), batch=1, beta=0.0, rowmap=0, hidden=0, sm_limit=0):
+    """Weight-gradient form: outs[z][m][n] = sum_r a[r][a_col0 + z*a_col_batch + m] * b[r + shifts[z]][b_col0 + z*b_col_batch
+    + n] (+ beta*outs[z]) over the 64-row blocks [blk0[z], +n_blk) of the R reduction rows; a, b: SB16 with rows = r."""
+    R = a.rows if R is None else R
+    n_blk = (R + 63) // 64 if n_blk is None else n_blk
+    if outs is None:
+        outs = [torch.empty(M, N, dtype=torch.float32, device=a.buf.device) for _ in range(batch)]
+    o0, o1 = outs[0], outs[1] if batch == 2 else None
+    call("gemm_sb16_tn", a.buf, LL(a.ld), LL(a.plane), a.cols, a_col0, a_col_batch, b.buf, LL(b.ld), LL(b.plane), b.cols,
+         b_col0, b_col_batch, R, blk0[0], blk0[1], n_blk, shifts[0], shifts[1], batch, o0, o1, LL(o0.stride(0)), M, N, 1.0,
+         float(beta), rowmap, hidden, int(sm_limit), stream_ptr())
+    return outs
 
 
 def colsum(a, rowmap=0, hidden=0, R=None):

@@ -90,10 +90,12 @@ class SepDNN(nn.Module):
         self.gpuid = gpuid
         self.feat_dim = int(kwargs.get("feat_dim", 257))
         self.num_spk = int(kwargs.get("num_spk", 2))
-        self.num_layers = 2
+        # the reference hard-codes two layers (archs/uPIT.py:115); `num_layers` is an extension (BASELINE.json
+        # configs[0] names a 3-layer net) that keeps the state_dict naming of nn.LSTM (weight_ih_l2, ...)
+        self.num_layers = int(kwargs.get("num_layers", 2))
         for key in kwargs:
             print("modelparam:", key, kwargs[key])
-        self.blstm = nn.LSTM(self.feat_dim, HID, num_layers=2, bidirectional=True)
+        self.blstm = nn.LSTM(self.feat_dim, HID, num_layers=self.num_layers, bidirectional=True)
         self.lin = nn.Linear(HID * 2, self.feat_dim * self.num_spk)
         self.bn = nn.BatchNorm1d(HID * 2)
         self.in_dim = self.feat_dim
@@ -105,8 +107,8 @@ class SepDNN(nn.Module):
 
     def init_hidden(self, batch_size):
         # drawn on the CPU generator and moved, exactly like archs/uPIT.py:121-127 (H1: random on every batch)
-        h = torch.randn(2 * 2, batch_size, HID)
-        c = torch.randn(2 * 2, batch_size, HID)
+        h = torch.randn(2 * self.num_layers, batch_size, HID)
+        c = torch.randn(2 * self.num_layers, batch_size, HID)
         dev = self.lin.weight.device
         if dev.type != "cuda":
             return h.to(dev), c.to(dev)
@@ -132,15 +134,26 @@ class SepDNN(nn.Module):
         return self._wt
 
     def workspace(self, T, B, training, slot=0):
-        key = (T, B, training, slot)
+        """The activation buffers of (training, slot), bound to this batch's (T, B).  Buffers are sized by capacity and
+        grow (with headroom) only when a batch does not fit, so a shuffled loader's ever-changing T_max allocates
+        nothing in steady state; other slots are never touched (a second submit/collect slot may be in flight)."""
+        key = (bool(training), slot)
         ws = self._ws.get(key)
-        if ws is None:
-            if len(self._ws) >= getattr(self, "max_workspaces", 2):
-                self._ws.clear()
-            ws = engine.Workspace(T, B, self.in_dim, self.out_dim, self.num_spk, self.num_layers,
+        if ws is None or not ws.fits(T, B):
+            cap_rows = T * B if ws is None else max(T * B, ws.cap_rows)
+            cap_B = B if ws is None else max(B, ws.cap_B)
+            if ws is not None:                     # growing: leave headroom so the next longer batch fits too
+                cap_rows = cap_rows + cap_rows // 8
+                self._ws.pop(key)
+                del ws
+            ws = engine.Workspace(cap_rows, cap_B, self.in_dim, self.out_dim, self.num_spk, self.num_layers,
                                   self.lin.weight.device, training)
             self._ws[key] = ws
-        return ws
+        return ws.bind(T, B)
+
+    def reserve(self, max_frames, batch_size, training=True, slot=0):
+        """Size the workspace of (training, slot) once for the longest batch expected (frames x batch)."""
+        self.workspace(int(max_frames), int(batch_size), training, slot)
 
     def forward(self, x):
         """x: PackedSequence of mixture features.  Returns the masks (B, T, feat_dim*num_spk) like the reference
@@ -227,8 +240,8 @@ class _UPITLoss(torch.autograd.Function):
         p = {k: v.detach() for k, v in model.param_dict().items()}
         grads = {k: torch.empty_like(p[k]) for k in ctx.names}
         gout = gloss.detach().to(torch.float32).reshape(1).contiguous()
-        engine.backward(ws, wt, p, grads, batch["mix"], batch["src"], batch["lens_dev"], ctx.hidden[1].contiguous(),
-                        model.feat_dim, model.num_spk, gout, training=model.training)
+        engine.backward(ws, wt, p, grads, batch["mix"], batch["src"], batch["lens_dev"], ctx.hidden[0].contiguous(),
+                        ctx.hidden[1].contiguous(), model.feat_dim, model.num_spk, gout, training=model.training)
         return (None, None, None, None) + tuple(grads[k] for k in ctx.names)
 
 
@@ -261,8 +274,8 @@ def loss_and_grads(model, batch_sample, grads, hook=None, hidden=None):
         S, F = model.num_spk, model.feat_dim
         engine.pit_loss(ws, batch["mix"], batch["src"], batch["lens_dev"], F, S, S, mode=0)
         p = {k: v.detach() for k, v in model.param_dict().items()}
-        engine.backward(ws, wt, p, grads, batch["mix"], batch["src"], batch["lens_dev"], model.hidden[1].contiguous(),
-                        F, S, None, training=model.training, hook=hook)
+        engine.backward(ws, wt, p, grads, batch["mix"], batch["src"], batch["lens_dev"], model.hidden[0].contiguous(),
+                        model.hidden[1].contiguous(), F, S, None, training=model.training, hook=hook)
     model.last = {"losses": ws.losses, "indices": ws.idx, "stats": ws.stats, "batch": batch}
     return ws.stats[2], ws.stats[1]
 

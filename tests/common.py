@@ -23,7 +23,7 @@ def case_features(case):
     mixes, srcs = [], [[] for _ in range(case["S"])]
     waves = []
     for b, n in enumerate(case["lens"]):
-        mix, ss = synth.mixture(1000 * case["seed"] + b, n, case["S"])
+        mix, ss = synth.mixture(1000 * case["seed"] + b, n, case["S"], case.get("sr", 8000))
         waves.append((mix, ss))
         mixes.append(stft_oracle.stft_mag(mix, case["n_fft"], case["hop"]).T.copy())
         for i, s in enumerate(ss):

@@ -40,6 +40,15 @@ CASES = {
     "upit_s3_f129": dict(arch="uPIT", S=3, n_fft=256, hop=64, lens=synth.batch_lengths_cfg1(5, 6400, 320), seed=2),
     "rsh_s3_f129": dict(arch="RSH", S=3, n_fft=256, hop=64, lens=synth.batch_lengths_cfg1(4, 6400, 320), seed=3),
     "rsh_s2_f257": dict(arch="RSH", S=2, n_fft=512, hop=128, lens=synth.batch_lengths_cfg1(4, 16000, 640), seed=4),
+    # the BASELINE.json configurations at their full sizes (SURVEY.md 8 table of shapes)
+    # configs[2]: the benched train shape -- B=64, 4-8 s at 8 kHz, 512/128 (T<=501, F=257)
+    "cfg3_upit_b64": dict(arch="uPIT", S=2, n_fft=512, hop=128, lens=synth.uniform_lengths(5, 64, 32000, 64000), seed=5),
+    # configs[3]: 3-speaker mixtures, B=64, 4 s -- RSH (input 2F=514, 3 passes) and uPIT with 6 permutations (771 outputs)
+    "cfg4_rsh_b64": dict(arch="RSH", S=3, n_fft=512, hop=128, lens=synth.uniform_lengths(6, 64, 24000, 32000), seed=6),
+    "cfg4_upit_s3_b64": dict(arch="uPIT", S=3, n_fft=512, hop=128, lens=synth.uniform_lengths(7, 64, 24000, 32000), seed=7),
+    # configs[4]: 16 kHz, 20 s utterances (T=2501), B=8
+    "cfg5_upit_t2501": dict(arch="uPIT", S=2, n_fft=512, hop=128, lens=synth.batch_lengths_cfg1(8, 320000, 3840), seed=8,
+                            sr=16000),
 }
 
 
@@ -64,7 +73,7 @@ def make_samples(case):
     (uPIT.py:66-79 / RSH.py:105-120): arrays (T_b, F)."""
     samples = []
     for b, n in enumerate(case["lens"]):
-        mix, srcs = synth.mixture(1000 * case["seed"] + b, n, case["S"])
+        mix, srcs = synth.mixture(1000 * case["seed"] + b, n, case["S"], case.get("sr", 8000))
         feats = {"mix": stft_oracle.stft_mag(mix, case["n_fft"], case["hop"]).T}
         for i, s in enumerate(srcs):
             feats["source%d" % (i + 1)] = stft_oracle.stft_mag(s, case["n_fft"], case["hop"]).T

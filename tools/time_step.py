@@ -47,8 +47,8 @@ def timed_call(name, *a):
     key = name
     if name == "gemm_sb16":
         key = "gemm_sb16 M=%d N=%d K=%d" % (a[8], a[9], a[10])
-    elif name == "gemm_sb16_x2":
-        key = "gemm_sb16_x2 M=%d N=%d K=%d" % (a[12], a[13], a[14])
+    elif name == "gemm_sb16_tn":
+        key = "gemm_sb16_tn M=%d N=%d K=%d x%d" % (a[22], a[23], 64 * a[15], a[18])
     records.setdefault(key, []).append((e0, e1))
     return r
 
@@ -72,7 +72,7 @@ for k, v in records.items():
     extra = ""
     if k.startswith("gemm"):
         M_, N_, K_ = (int(x.split("=")[1]) for x in k.split()[1:4])
-        fl = 2.0 * M_ * N_ * K_ * (2 if "x2" in k else 1) * (len(v) // args.iters)
+        fl = 2.0 * M_ * N_ * K_ * (2 if k.endswith("x2") else 1) * (len(v) // args.iters)
         extra = "  %6.1f TF/s algorithmic, %6.1f issued" % (fl / ms / 1e9, 3 * fl / ms / 1e9)
     print("%-40s calls/step %3d   ms/step %8.3f%s" % (k, len(v) // args.iters, ms, extra))
 print("sum of kernels ms/step %.3f ; audio-s/step %.1f" % (tot, sum(lens) * 128 / 8000.0))
