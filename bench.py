@@ -159,10 +159,19 @@ def dist_setup(n_gpus):
     return rank, local, world
 
 
-# dram__bytes_read.sum + dram__bytes_write.sum per launch, from the `ncu --set full` captures summarised in
-# profiles/r01_summary.md (sections E, F, H) for the same workloads bench.py runs (largest batch shape for lstm_bwd)
-NCU_TRAFFIC = {"lstm_bwd": 1.319e9, "stft": 37.9e9, "istft": 6.08e9}
-NCU_TRAFFIC_NOTE = "ncu --set full, one launch, profiles/r01_summary.md"
+def ncu_traffic():
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernels, written by tools/ncu_traffic.py
+    from `ncu --set full` captures of the same workloads (profiles/ncu_traffic.json, committed; the .ncu-rep files are
+    not).  {kernel: {"bytes": ..., "source": ...}}"""
+    try:
+        return json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
+    except Exception:
+        return {}
+
+
+def traffic_of(kernel):
+    t = ncu_traffic().get(kernel)
+    return (t["bytes"], t.get("source")) if t else (None, None)
 
 
 def timed_region(fn, steps, warmup, world, sampler=None):
@@ -195,14 +204,14 @@ def timed_region(fn, steps, warmup, world, sampler=None):
     return ms, clocks
 
 
-def train_flops_per_frame(feat=F, num_spk=S):
+def train_flops_per_frame(in_dim=F, out_dim=F * S, passes=1):
     """Algorithmic flops per frame per sequence of one train step, split into the GEMM part (input projections,
     head, and their backward GEMMs) and the recurrence part (h W_hh^T and its backward)  (DESIGN.md)."""
-    inproj = 2 * 4 * H * feat * 2 + 2 * 4 * H * 2 * H * 2           # both directions, layers 0 and 1
-    head = 2 * 2 * H * feat * num_spk
+    inproj = 2 * 4 * H * in_dim * 2 + 2 * 4 * H * 2 * H * 2          # both directions, layers 0 and 1
+    head = 2 * 2 * H * out_dim
     rec = 2 * 4 * H * H * 2 * 2                                     # both directions, two layers
     gemm = (inproj + head) + (inproj + head) + (2 * 4 * H * 2 * H * 2 + head) + rec   # fwd, dW, dX(l1)+dY, dW_hh
-    return gemm, 2 * rec
+    return passes * gemm, passes * 2 * rec
 
 
 def pad_batch(samples, keys):
@@ -243,26 +252,81 @@ def cpu_train_sample(n_utts, steps, warmup, seed=0):
     return sum(lens_s) / SR / sec, sec, cores
 
 
-def run_train(args, rank, local, world):
-    import torch
+# The train-step workloads: BASELINE.json configs[2] (the headline), configs[3] (3-speaker: RSH and 6-permutation uPIT),
+# configs[4] (16 kHz, 20 s).  lens(seed, B) -> utterance lengths in samples, descending.
+WORKLOADS = {
+    "train": dict(arch="uPIT", S=2, B=B_PER_GPU, sr=8000, lens=lambda seed, B: train_lengths(seed, B),
+                  name="configs[2]: uPIT 2-spk BLSTM(2x600 bidir)+BN+Linear train step, WSJ0-2mix shape, 8 kHz, "
+                       "STFT 512/128 (F=257), utterances U[4,8] s, batch 64/GPU"),
+    "train_b100": dict(arch="uPIT", S=2, B=100, sr=8000, lens=lambda seed, B: train_lengths(seed, B),
+                       name="configs[2] shapes at the reference recipe's default batch 100 (run_train.sh:18): B > 64 takes "
+                            "the generic backward recurrence"),
+    "upit3": dict(arch="uPIT", S=3, B=B_PER_GPU, sr=8000,
+                  lens=lambda seed, B: sorted((int(v) for v in np.random.default_rng(seed).integers(24000, 32001, size=B)), reverse=True),
+                  name="configs[3]: uPIT 3-spk (6 permutations, 771 outputs) train step, 8 kHz, 3-4 s, 512/128, batch 64/GPU"),
+    "rsh": dict(arch="RSH", S=3, B=B_PER_GPU, sr=8000,
+                lens=lambda seed, B: sorted((int(v) for v in np.random.default_rng(seed).integers(24000, 32001, size=B)), reverse=True),
+                name="configs[3]: RSH recurrent-selective-hearing train step, 3-spk mixtures (3 passes, greedy assignment), "
+                     "8 kHz, 3-4 s, 512/128 (input 2F=514), batch 64/GPU"),
+    "long": dict(arch="uPIT", S=2, B=8, sr=16000, lens=lambda seed, B: [320000 - 3840 * b for b in range(B)],
+                 name="configs[4]: uPIT 2-spk train step on 16 kHz / 20 s utterances (T=2501), 512/128, batch 8/GPU"),
+}
+
+
+def workload_features(spec, seed):
+    """Collated synthetic batch of a workload (features (T_b, F) per utterance; RSH: [mix || ones] input)."""
+    from ssb200 import RSH, uPIT
+    lens_s = spec["lens"](seed, spec["B"])
+    samples = synth_features(seed, lens_s, spec["S"])
+    if spec["arch"] == "RSH":
+        for d in samples:
+            m = d.pop("mix")
+            d["combo"] = np.concatenate((m, np.ones_like(m)), axis=1)
+        return RSH.Collator("combo")(samples), lens_s
+    return uPIT.Collator("mix")(samples), lens_s
+
+
+def _map_batch(batch, fn):
     from torch.nn.utils.rnn import PackedSequence
-    from ssb200 import train, uPIT
+    if isinstance(batch, dict):
+        return {k: (PackedSequence(fn(v.data), v.batch_sizes) if isinstance(v, PackedSequence) else v) for k, v in batch.items()}
+    import copy
+    out = copy.copy(batch)                                     # RSH MultiSpkBatch: a list of such dicts
+    out.sub_batches = [_map_batch(b, fn) for b in batch.sub_batches]
+    return out
+
+
+def _batch_bytes(batch):
+    from torch.nn.utils.rnn import PackedSequence
+    if isinstance(batch, dict):
+        return sum(v.data.numel() * 4 for v in batch.values() if isinstance(v, PackedSequence))
+    return sum(_batch_bytes(b) for b in batch.sub_batches)
+
+
+def run_train(args, rank, local, world, which="train", detail=True):
+    """One train-step workload.  value: device-resident batches; e2e: pinned host batches through Trainer.prefetch/step
+    with the loss read back every step.  detail: per-kernel pass, rooflines, latency model, DP checks."""
+    import torch
+    from ssb200 import RSH, train, uPIT
+    spec = WORKLOADS[which]
+    arch = RSH if spec["arch"] == "RSH" else uPIT
+    Sx, Bx, sr = spec["S"], spec["B"], spec["sr"]
     hbm, tf_burst, tf_sus, peak_src = peaks()
     torch.manual_seed(0)
-    model = uPIT.SepDNN(local, feat_dim=str(F), num_spk=str(S)).cuda()
-    trainer = train.Trainer(model, uPIT)
+    kwargs = dict(feat_dim=str(F)) if arch is RSH else dict(feat_dim=str(F), num_spk=str(Sx))
+    model = arch.SepDNN(local, **kwargs).cuda()
+    trainer = train.Trainer(model, arch, exact=getattr(args, "dp_exact", False))
     meter = CallMeter()
-    coll = uPIT.Collator("mix")
-    host, dev, audio_s, frames = [], [], [], []
+    host, dev, audio_s, frames, tmax = [], [], [], [], []
     for i in range(N_BATCHES):
         # every rank knows every rank's lengths (seeded), so the job totals need no collective
-        audio_s.append(sum(sum(train_lengths(1000 * r + i, B_PER_GPU)) for r in range(world)) / SR)
-        lens_s = train_lengths(1000 * rank + i, B_PER_GPU)
+        audio_s.append(sum(sum(spec["lens"](1000 * r + i, Bx)) for r in range(world)) / sr)
+        b, lens_s = workload_features(spec, 1000 * rank + i)
         frames.append(sum(1 + n // HOP for n in lens_s))
-        b = coll(synth_features(1000 * rank + i, lens_s))
-        host.append({k: PackedSequence(v.data.pin_memory(), v.batch_sizes) for k, v in b.items()})
-        dev.append({k: PackedSequence(v.data.cuda(), v.batch_sizes) for k, v in b.items()})
-    h2d = int(np.mean([sum(v.data.numel() * 4 for v in b.values()) for b in host]))
+        tmax.append(1 + max(lens_s) // HOP)
+        host.append(_map_batch(b, lambda t: t.pin_memory()))
+        dev.append(_map_batch(b, lambda t: t.cuda()))
+    h2d = int(np.mean([_batch_bytes(b) for b in host]))
     sink = {}
 
     def step_dev(i):
@@ -279,18 +343,40 @@ def run_train(args, rank, local, world):
         sink["host_loss"] = (float(loss), float(norm))          # D2H read of the step's result, every step
 
     K, W = args.steps, args.warmup
-    for i in range(N_BATCHES):          # untimed: every batch shape once, so no workspace is allocated while timing
+    for i in range(N_BATCHES):          # untimed: the workspace grows to the longest batch once (capacity-sized afterwards)
         step_dev(i)
     torch.cuda.synchronize()
-    sampler = ClockSampler(local) if rank == 0 else None
-    meter.launches = 0
+    sampler = ClockSampler(local) if (rank == 0 and detail) else None
+    wt = model._wt
+    meter.launches, replays0 = 0, wt.graph_replays
     ms, clocks = timed_region(step_dev, K, W, world, sampler)
-    launches = meter.launches // (K + W) * K
+    launches = (meter.launches + (wt.graph_replays - replays0) * wt.launches_per_refresh()) // (K + W) * K
     tot_audio = sum(audio_s[(W + i) % N_BATCHES] for i in range(K))
     value = tot_audio / (ms / 1e3)
     ms_e2e, _ = timed_region(step_e2e, K, W, world)
     e2e = tot_audio / (ms_e2e / 1e3)
-    # per-kernel device times (CUDA events around every C-ABI call, same stream), separate untimed pass
+    line = {
+        "metric": "uPIT train audio-sec/sec" if which == "train" else "%s train audio-sec/sec" % spec["arch"],
+        "value": round(value, 1), "unit": "audio-sec/sec", "n_gpus": world,
+        "steps": K, "warmup": W, "ms_per_step": round(ms / K, 3), "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "split-bf16 operands (hi+lo), fp32 accumulate/state", "data": "synthetic",
+        "config": {"workload": spec["name"], "global_batch": Bx * world, "frames_per_step_per_gpu": int(np.mean(frames)),
+                   "parallelism": "dp%d" % world,
+                   "dp_semantics": ("mode B: loss normaliser and BatchNorm statistics over all ranks, gradients summed"
+                                    if trainer.exact else
+                                    "mode A: per-rank loss/BN, gradients averaged") + " (bucketed NCCL allreduce overlapped "
+                                   "with backward)",
+                   "l2": "%d distinct batches rotated (T_max %s; workspace sized by capacity, no allocation while timing); "
+                         "per-step working set ~2 GB >> 126 MB L2" % (N_BATCHES, ",".join(str(t) for t in tmax))},
+        "e2e": {"value": round(e2e, 1), "unit": "audio-sec/sec", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 8,
+                "ms_per_step": round(ms_e2e / K, 3)},
+        "gpu_launches": launches,
+    }
+    if not detail:
+        return line
+    line["clocks"] = clocks
+    # per-kernel device times (CUDA events around every C-ABI call, on the launching stream), separate untimed pass.
+    # Streamed GEMM chunks run on the side stream UNDER the recurrences, so the per-kernel sums exceed the step time.
     meter.timing = True
     PROF = 2
     for i in range(PROF):
@@ -299,14 +385,16 @@ def run_train(args, rank, local, world):
     meter.timing = False
     prof = meter.summary(PROF)
     fr = float(np.mean(frames[:PROF]))
-    gemm_fl, rec_fl = train_flops_per_frame()
+    passes = Sx if arch is RSH else 1
+    gemm_fl, rec_fl = train_flops_per_frame(model.in_dim, model.out_dim, passes)
     rl = {}
     for other in ("gemm_sb16_x2", "gemm_sb16_tn"):   # the batched / weight-gradient launches are the same kernel template
         if other in prof:
             g, x = prof.setdefault("gemm_sb16", {"calls_per_step": 0, "ms_per_step": 0.0, "ms_per_call": 0.0}), prof.pop(other)
             g["calls_per_step"] += x["calls_per_step"]
             g["ms_per_step"] += x["ms_per_step"]
-    for name, fl in (("gemm_sb16", gemm_fl), ("lstm_fwd", rec_fl / 3), ("lstm_bwd", rec_fl / 3)):
+    # the recurrence flops split evenly between the forward and the backward kernel
+    for name, fl in (("gemm_sb16", gemm_fl), ("lstm_fwd", rec_fl / 2), ("lstm_bwd", rec_fl / 2)):
         if name in prof:
             a = fl * fr / (prof[name]["ms_per_step"] * 1e-3) / 1e12
             rl[name] = {"bound": "tensor", "achieved": round(a, 2), "peak": tf_sus, "unit": "TFLOP/s",
@@ -314,40 +402,43 @@ def run_train(args, rank, local, world):
             if name == "gemm_sb16":      # every product is 3 bf16 MMAs (hi*hi + hi*lo + lo*hi)
                 rl[name]["mma_issued_tflops"] = round(3 * a, 1)
                 rl[name]["mma_issued_frac"] = round(3 * a / tf_sus, 4)
-    for name, byts in (("pit_loss_fwd", (2 * S + 1) * 4.0 * F), ("pit_loss_bwd", (2 * S + 1) * 4.0 * F + S * F * 8.0)):
-        if name in prof:
-            a = byts * B_PER_GPU * (fr / B_PER_GPU) / (prof[name]["ms_per_step"] * 1e-3) / 1e9
+    for name, byts in (("pit_loss_fwd", (2 * Sx + 1) * 4.0 * F), ("pit_loss_bwd", (2 * Sx + 1) * 4.0 * F + Sx * F * 8.0)):
+        if name in prof and arch is uPIT:
+            a = byts * fr / (prof[name]["ms_per_step"] * 1e-3) / 1e9
             rl[name] = {"bound": "hbm", "achieved": round(a, 1), "peak": hbm, "unit": "GB/s", "frac": round(a / hbm, 4),
                         "ms_per_step": round(prof[name]["ms_per_step"], 3)}
-    divergence = None
-    if world > 1:                       # replicas must still hold identical parameters after all those steps
+    # The recurrences are chain-latency bound, not roofline bound: T_max dependent steps per launch, both directions in
+    # one kernel.  What matters is microseconds per time step (phase budgets: profiles/).
+    steps_per_launch = float(np.mean(tmax[:PROF]))
+    lat = {}
+    for name in ("lstm_fwd", "lstm_bwd"):
+        if name in prof:
+            launches_per_step = prof[name]["calls_per_step"]
+            lat[name] = {"us_per_time_step": round(prof[name]["ms_per_step"] * 1e3 / (launches_per_step * steps_per_launch), 3),
+                         "time_steps_per_launch": steps_per_launch, "launches_per_train_step": launches_per_step,
+                         "ctas": 100 if name == "lstm_fwd" else (80 if Bx <= 64 else 76),
+                         "tensor_flops_per_time_step": 2 * 2 * 4 * H * H * Bx}
+    divergence = grad_check = None
+    if world > 1:
         import torch.distributed as dist
+        # replicas must still hold identical parameters after all those steps
         ref_p = trainer.flat_p.clone()
         dist.broadcast(ref_p, src=0)
         d = (trainer.flat_p - ref_p).abs().max().reshape(1)
         dist.all_reduce(d, op=dist.ReduceOp.MAX)
         divergence = float(d)
+        grad_check = trainer.grad_exchange_check(dev[0])
     dom = max(prof, key=lambda k: prof[k]["ms_per_step"])
     roofline = dict(rl.get(dom, {"bound": "tensor", "achieved": None, "peak": tf_sus, "unit": "TFLOP/s", "frac": None}))
-    roofline.update({"kernel": dom, "traffic": NCU_TRAFFIC.get(dom), "traffic_source": NCU_TRAFFIC_NOTE if dom in NCU_TRAFFIC else None,
-                     "peak_source": peak_src,
-                     "share_of_step": round(prof[dom]["ms_per_step"] / sum(v["ms_per_step"] for v in prof.values()), 3)})
-    line = {
-        "metric": "uPIT train audio-sec/sec", "value": round(value, 1), "unit": "audio-sec/sec", "n_gpus": world,
-        "steps": K, "warmup": W, "ms_per_step": round(ms / K, 3), "higher_is_better": True, "scaling": "weak",
-        "vs_baseline": None, "dtype": "split-bf16 operands (hi+lo), fp32 accumulate/state", "data": "synthetic",
-        "config": {"workload": "configs[2]: uPIT 2-spk BLSTM(2x600 bidir)+BN+Linear train step, WSJ0-2mix shape, 8 kHz, "
-                               "STFT 512/128 (F=257), utterances U[4,8] s, batch 64/GPU",
-                   "global_batch": B_PER_GPU * world, "frames_per_step_per_gpu": int(fr), "parallelism": "dp%d" % world,
-                   "dp_semantics": "mode A: per-rank loss/BN, gradients averaged (bucketed NCCL allreduce overlapped "
-                                   "with backward)",
-                   "l2": "4 distinct batches rotated; per-step working set ~3 GB >> 126 MB L2"},
-        "e2e": {"value": round(e2e, 1), "unit": "audio-sec/sec", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 8,
-                "ms_per_step": round(ms_e2e / K, 3)},
-        "gpu_launches": launches, "clocks": clocks, "roofline": roofline, "rooflines": rl,
-        "dp_param_divergence": divergence,
-        "kernel_ms_per_step": {k: round(v["ms_per_step"], 3) for k, v in sorted(prof.items(), key=lambda kv: -kv[1]["ms_per_step"])},
-    }
+    tb, tsrc = traffic_of(dom)
+    roofline.update({"kernel": dom, "traffic": tb, "traffic_source": tsrc, "peak_source": peak_src,
+                     "share_of_step": round(prof[dom]["ms_per_step"] / (ms / K), 3),
+                     "note": "chain-latency bound kernel: see latency_model (us per time step), not the tensor fraction"})
+    line.update({"roofline": roofline, "rooflines": rl, "latency_model": lat, "dp_param_divergence": divergence,
+                 "dp_grad_check": grad_check,
+                 "kernel_ms_per_step": {k: round(v["ms_per_step"], 3) for k, v in sorted(prof.items(), key=lambda kv: -kv[1]["ms_per_step"])},
+                 "kernel_ms_note": "CUDA events around each C-ABI call on its own stream; GEMM chunks streamed under the "
+                                   "recurrences overlap them, so the sum exceeds ms_per_step"})
     return line
 
 
@@ -467,7 +558,7 @@ def run_stft(args, rank, local, world, n_mix=20000, e2e_mix=2000):
                 "d2h_bytes_per_step": rag_e.total_frames * STFT_F * 4, "sample": "%d-mixture shard, pinned host memory, ops.stft_host: 8 utterance runs pipelined over copy/compute/copy streams" % e2e_mix},
         "gpu_launches": launches, "clocks": clocks,
         "roofline": {"bound": "hbm", "kernel": "stft_dft256_kernel" if ops.STFT_DFT256 else "stft_kernel<256>", "achieved": round(ach, 1), "peak": hbm, "unit": "GB/s",
-                     "frac": round(ach / hbm, 4), "traffic": NCU_TRAFFIC["stft"], "traffic_source": NCU_TRAFFIC_NOTE,
+                     "frac": round(ach / hbm, 4), "traffic": traffic_of("stft")[0], "traffic_source": traffic_of("stft")[1],
                      "peak_source": peak_src, "algorithmic_bytes_per_frame": bytes_per_frame, "kernel_ms": round(kms, 3)},
     }
 
@@ -503,27 +594,28 @@ def run_istft(args, rank, local, world, n_utts=3000, n_src=2):
             "unit": "frame-sources/sec", "n_gpus": world,
             "config": {"workload": "mask x mixture-phase iSTFT, 512/128, %d utts x %d sources, int16 out" % (n_utts, n_src)},
             "roofline": {"bound": "hbm", "kernel": "istft_kernel<512>", "achieved": round(ach, 1), "peak": hbm,
-                         "unit": "GB/s", "frac": round(ach / hbm, 4), "traffic": NCU_TRAFFIC["istft"],
-                         "traffic_source": NCU_TRAFFIC_NOTE, "peak_source": peak_src,
+                         "unit": "GB/s", "frac": round(ach / hbm, 4), "traffic": traffic_of("istft")[0],
+                         "traffic_source": traffic_of("istft")[1], "peak_source": peak_src,
                          "algorithmic_bytes_per_frame_source": byts, "kernel_ms": round(kms, 3)}}
 
 
-def run_separate(args, rank, local, world):
+def run_separate(args, rank, local, world, which="train"):
     """Evaluation end to end on the device (SURVEY 8 f3, ssb200/pipeline.py:separate): host waveforms -> STFT ->
     BLSTM masks -> mask x mixture-phase iSTFT -> int16 audio on the host; what run_eval.sh does through three
     programs and two sets of .npz files (steps/extract_feats.py test branch, compute_masks, reconstruct_sources.py)."""
     import torch
     from ssb200 import pipeline, uPIT
     K, W = args.steps, args.warmup
+    spec = WORKLOADS[which]
     torch.manual_seed(0)
     model = uPIT.SepDNN(local, feat_dim=str(F), num_spk=str(S)).cuda()
     model.eval()
     rng = np.random.default_rng(11 + rank)
     batches = []
     for i in range(N_BATCHES):
-        lens = train_lengths(5000 + 1000 * rank + i, B_PER_GPU)
+        lens = spec["lens"](5000 + 1000 * rank + i, spec["B"])
         batches.append([rng.uniform(-0.3, 0.3, size=n).astype(np.float32) for n in lens])
-    audio = [sum(len(w) for w in b) / SR for b in batches]
+    audio = [sum(len(w) for w in b) / spec["sr"] for b in batches]
     sink = {}
 
     def step(i):
@@ -543,8 +635,9 @@ def run_separate(args, rank, local, world):
     return {"metric": "uPIT separation audio-sec/sec (waveform in, %d int16 waveforms out)" % S,
             "value": round(tot / (ms / 1e3), 1), "unit": "audio-sec/sec", "n_gpus": world, "steps": K, "warmup": W,
             "ms_per_step": round(ms / K, 3),
-            "config": {"workload": "eval of configs[2] shapes: %d utterances U[4,8] s per step, STFT %d/%d, S=%d, "
-                                   "h0/c0 random per batch like the reference; pipeline.submit/collect on two slots" % (B_PER_GPU, N_FFT, HOP, S)},
+            "config": {"workload": "eval of the shapes of %s: %d utterances per step, STFT %d/%d, S=%d, h0/c0 random per batch "
+                                   "like the reference; pipeline.submit/collect on two slots"
+                                   % (spec["name"].split(":")[0], spec["B"], N_FFT, HOP, S)},
             "e2e": {"value": round(tot / (ms / 1e3), 1), "unit": "audio-sec/sec", "h2d_bytes_per_step": nbytes * 4,
                     "d2h_bytes_per_step": nbytes * 2 * S}}
 
@@ -573,7 +666,10 @@ def run_reference(args, rank, world):
             "n_gpus": world, "steps": K, "warmup": W, "ms_per_step": round(sec * 1e3, 1), "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": "configs[2] uPIT train step (same shapes as the GPU arm), CPU, torch %d threads" % cores,
-                       "batch": n_utts},
+                       "cpu_batch": n_utts, "gpu_arm_batch": B_PER_GPU,
+                       "note": "a bounded sample: %d of the 64 utterances of a batch per CPU step; larger CPU batches run "
+                               "SLOWER per audio-second on this kind of box (16 utterances: 11.5 vs 35.7 audio-s/s at 4), so "
+                               "the GPU/CPU ratio computed from this arm is the conservative one" % n_utts},
             "cpu_baseline": {"value": round(aps, 2), "unit": "audio-sec/sec", "cores": cores, "kind": "port",
                              "sample": "%d of the 64 utterances of one batch per step" % n_utts},
             "e2e": {"value": round(aps, 2), "unit": "audio-sec/sec", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
@@ -584,7 +680,9 @@ def main():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--workload", default="train", choices=["train", "stft", "istft", "separate"])
+    ap.add_argument("--workload", default="train", choices=["train", "stft", "istft", "separate", "separate_long"] +
+                    [k for k in WORKLOADS if k != "train"])
+    ap.add_argument("--dp-exact", action="store_true", help="data-parallel mode B (N > 1): exact large-batch arithmetic")
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-extras", action="store_true", help="skip the stft/istft/cpu_baseline legs of the train line")
     args = ap.parse_args()
@@ -613,23 +711,40 @@ def main():
         line = run_istft(args, rank, local, world)
     elif args.workload == "separate":
         line = run_separate(args, rank, local, world)
+    elif args.workload == "separate_long":
+        line = run_separate(args, rank, local, world, "long")
+    elif args.workload != "train":
+        line = run_train(args, rank, local, world, args.workload)
     else:
         line = run_train(args, rank, local, world)
         if not args.no_extras:
-            sub = argparse.Namespace(steps=max(3, min(args.steps, 5)), warmup=3)
+            sub = argparse.Namespace(steps=max(3, min(args.steps, 5)), warmup=3, dp_exact=False)
             torch.cuda.empty_cache()
             line["stft"] = run_stft(sub, rank, local, world)
             torch.cuda.empty_cache()
             line["istft"] = run_istft(sub, rank, local, world)
             torch.cuda.empty_cache()
             line["separate"] = run_separate(sub, rank, local, world)
+            # the other BASELINE.json configurations, a few steps each (same timing rules; value / e2e / ms_per_step)
+            others = {}
+            for key in ("rsh", "upit3", "long", "train_b100"):
+                torch.cuda.empty_cache()
+                others[key] = run_train(sub, rank, local, world, key, detail=False)
+            torch.cuda.empty_cache()
+            others["separate_long"] = run_separate(sub, rank, local, world, "long")
+            line["configs"] = others
     if rank == 0 and world == 1 and not args.no_extras:
         if args.workload == "train":
             # 4 utterances per CPU step like the --impl reference arm (larger CPU batches run SLOWER per audio-second on
             # this box: 16 utterances 11.5 vs 35.7 audio-s/s), 12 steps ~ 11 s of CPU work
             aps, sec, cores = cpu_train_sample(4, 10, 2)
             line["cpu_baseline"] = {"value": round(aps, 2), "unit": "audio-sec/sec", "cores": cores, "kind": "port",
+                                    "cpu_batch": 4,
                                     "sample": "10 train steps (+2 warm-up) on 4 of the 64 utterances (%.2f s/step)" % sec}
+            try:   # the recorded same-box comparator (tools/time_cudnn_ref.py; informative, not the official baseline)
+                line["cudnn_comparator_recorded"] = [json.loads(l) for l in open(os.path.join(ROOT, "profiles", "r02_cudnn_comparator.jsonl"))]
+            except Exception:
+                pass
             fps, n, c1 = cpu_stft_sample(5.0)
             line["stft"]["cpu_baseline"] = {"value": round(fps, 0), "unit": "frames/sec", "cores": c1, "kind": "port",
                                             "sample": "%d utterances, single process" % n}

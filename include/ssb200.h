@@ -208,6 +208,22 @@ int ss_bn_bwd(float* dy, const void* x, long long ld, long long plane, int R, in
               float* partial, float* dgamma, float* dbeta, float* bwd, void* stream);
 int ss_head_dw_fix(const float* G, const float* dsum, const float* coef, const float* beta, int O, int C, float* dW,
                    void* stream);
+/* Data-parallel mode B (N ranks reproduce the reference's arithmetic on the concatenated batch): the
+ * BatchNorm statistics are taken over the rows of ALL ranks.  ss_bn_sums writes sums[2][C] = column sums of {x, x^2}
+ * (dy == NULL) or {dy, dy*x}; the caller sum-allreduces them, and counts[2] = {total batch size, longest T of any rank}
+ * (their product is the row count of the concatenated, zero-padded batch); then ss_bn_stats_from_sums gives coef and
+ * updates the running statistics exactly as ss_bn_stats(training) would on the big batch, and ss_bn_bwd_from_sums
+ * applies the backward with the global sums while dgamma / dbeta stay this rank's share (the gradient exchange adds
+ * them up).  ss_pit_stats_finalize recomputes stats[2] = loss and stats[3] = 1/(S*norm) after stats[0:2] were
+ * sum-allreduced (archs/uPIT.py:204: one normaliser for the whole batch). */
+int ss_bn_sums(const void* x, long long ld, long long plane, const float* dy, int R, int C, float* partial, float* sums,
+               void* stream);
+int ss_bn_stats_from_sums(const float* sums, const float* counts, int C, const float* gamma, const float* beta, float eps,
+                          float momentum, float* running_mean, float* running_var, float* coef, void* stream);
+int ss_bn_bwd_from_sums(float* dy, const void* x, long long ld, long long plane, int R, int C, const float* coef,
+                        const float* sums_local, const float* sums_global, const float* counts, float* dgamma,
+                        float* dbeta, float* bwd, void* stream);
+int ss_pit_stats_finalize(float* stats, int n_src, void* stream);
 
 /* ---- RSH residual attention.  Replaces archs/RSH.py:254-257 (compute_loss: combos = relu_(combos - [0 || mask]),
  * repack) and :277-281 (compute_masks: no relu) and the autograd backward of that path ----
@@ -220,6 +236,22 @@ int ss_rsh_residual(const float* cur, const float* z, long long ldz, const int* 
                     float* next, void* stream);
 int ss_rsh_residual_bwd(const float* dx, const float* carry_in, const float* next_in, long long R, int F,
                         float* carry_out, float* dmask, void* stream);
+
+/* ---- f4: oracle-mask evaluation.  Replaces steps/evaluate_oracle.py:133-143 (ideal ratio / ideal binary masks applied
+ * to the mixture STFT; the reconstruction itself is ss_istft_masked) and the inner products of the SDR-type scores
+ * computed after it (steps/evaluate_oracle.py:144, steps/evaluate_sources.py:57) ----
+ * ss_oracle_masks: spec = complex64 mixture STFT blocks (ss_stft COMPLEX, (F,T_u) per utterance), src_mag = n_src
+ * magnitude STFTs of the sources in the same ragged layout, source s at src_mag + s*src_stride.  masks: the block layout
+ * ss_istft_masked reads (utterance u, source s at element (frame_off[u]*n_src + s*T_u)*F).
+ * soft (hard = 0): |S_s| / |X| (np.divide); bins where |X| is EXACTLY zero get mask 0 (np.divide would give inf / nan there
+ * and poison the frame -- which bins are exactly zero is an accident of the FFT arithmetic);
+ * hard: 1 where s == argmax_j |S_j| (first maximum wins like np.argmax) else 0.
+ * ss_sdr_sums: item i compares ref[ref_off[i] .. +n_ref[i]) with est[est_off[i] .. +n_est[i]) (zero beyond n_est, the
+ * unfilled tail of evaluate_oracle.py:142-143): sums[i][5] = {sum r, sum e, sum r^2, sum e^2, sum r*e} in fp64. */
+int ss_oracle_masks(const void* spec, const float* src_mag, long long src_stride, const long long* frame_off, int n_utts,
+                    int max_frames, int F, int n_src, int hard, float* masks, void* stream);
+int ss_sdr_sums(const float* ref, const long long* ref_off, const float* est, const long long* est_off, const int* n_ref,
+                const int* n_est, int n_items, int max_ref, double* sums, void* stream);
 
 /* ---- f1: global-norm clip + Adam over one flat fp32 bucket.  Replaces torch.nn.utils.clip_grad_norm_(params,
  * 0.25) and torch.optim.Adam(lr=1e-3).step() at steps/train_qsub.py:95,121-122 ----

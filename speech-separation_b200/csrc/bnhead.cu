@@ -35,13 +35,16 @@ __global__ void __launch_bounds__(256) bn_partial_kernel(const __nv_bfloat16* __
 }
 
 // coef layout (5 x C): [0] scale s = gamma*rstd, [1] shift = beta - mean*s, [2] mean, [3] rstd, [4] var (biased)
-__global__ void __launch_bounds__(256) bn_stats_final_kernel(const float* __restrict__ partial, int parts, int R, int C,
+// nt (optional, data-parallel mode B): the row count is nt[0] * nt[1] (total batch x longest T over all ranks) instead of R
+__global__ void __launch_bounds__(256) bn_stats_final_kernel(const float* __restrict__ partial, int parts, int R_, int C,
+                                                             const float* __restrict__ nt,
                                                              const float* __restrict__ gamma,
                                                              const float* __restrict__ beta, float eps, float momentum,
                                                              int training, float* __restrict__ running_mean,
                                                              float* __restrict__ running_var, float* __restrict__ coef) {
   const int c = blockIdx.x * 256 + threadIdx.x;
   if (c >= C) return;
+  const double R = nt ? (double)nt[0] * (double)nt[1] : (double)R_;
   double mean, var;
   if (training) {
     double s = 0.0, s2 = 0.0;
@@ -52,7 +55,7 @@ __global__ void __launch_bounds__(256) bn_stats_final_kernel(const float* __rest
     mean = s / R;
     var = s2 / R - mean * mean;
     if (var < 0.0) var = 0.0;
-    const double unb = R > 1 ? var * ((double)R / (R - 1.0)) : var;
+    const double unb = R > 1 ? var * (R / (R - 1.0)) : var;
     running_mean[c] = (float)((1.0 - momentum) * running_mean[c] + momentum * mean);
     running_var[c] = (float)((1.0 - momentum) * running_var[c] + momentum * unb);
   } else {
@@ -82,7 +85,10 @@ __global__ void __launch_bounds__(256) head_fold_bias_kernel(const float* __rest
 
 // from partial sums of dy and dy*x: dgamma, dbeta and the coefficients of dx = s*dy + bc*(x - mean) + cc
 // bwd layout (2 x C): [0] bc, [1] cc
-__global__ void __launch_bounds__(256) bn_bwd_final_kernel(const float* __restrict__ partial, int parts, int R, int C,
+// glob / nt (optional, data-parallel mode B): dgamma, dbeta come from this rank's sums (the gradient exchange adds the
+// ranks up), the coefficients of dx from the sums over ALL ranks (glob[2][C]) and the global row count nt[0] * nt[1]
+__global__ void __launch_bounds__(256) bn_bwd_final_kernel(const float* __restrict__ partial, int parts, int R_, int C,
+                                                           const float* __restrict__ glob, const float* __restrict__ nt,
                                                            const float* __restrict__ coef, int training,
                                                            float* __restrict__ dgamma, float* __restrict__ dbeta,
                                                            float* __restrict__ bwd) {
@@ -94,9 +100,15 @@ __global__ void __launch_bounds__(256) bn_bwd_final_kernel(const float* __restri
     bx += (double)partial[((long long)p * 2 + 1) * C + c];
   }
   const double s = coef[0 * C + c], mean = coef[2 * C + c], rstd = coef[3 * C + c];
-  const double dg = (bx - mean * a) * rstd;      // sum dy * xhat
+  double dg = (bx - mean * a) * rstd;            // sum dy * xhat
   dgamma[c] = (float)dg;
   dbeta[c] = (float)a;
+  double R = R_;
+  if (glob) {
+    a = glob[c];
+    dg = ((double)glob[C + c] - mean * a) * rstd;
+    R = (double)nt[0] * (double)nt[1];
+  }
   if (training) {
     bwd[0 * C + c] = (float)(-s * rstd * dg / R);
     bwd[1 * C + c] = (float)(-s * a / R);
@@ -158,6 +170,20 @@ __global__ void __launch_bounds__(256) head_dw_fix_kernel(const float* __restric
   }
 }
 
+// sums[0][c], sums[1][c] = the two column sums of bn_partial_kernel over all row blocks
+__global__ void __launch_bounds__(256) bn_reduce_kernel(const float* __restrict__ partial, int parts, int C,
+                                                        float* __restrict__ sums) {
+  const int c = blockIdx.x * 256 + threadIdx.x;
+  if (c >= C) return;
+  double a = 0.0, b = 0.0;
+  for (int p = 0; p < parts; ++p) {
+    a += (double)partial[((long long)p * 2 + 0) * C + c];
+    b += (double)partial[((long long)p * 2 + 1) * C + c];
+  }
+  sums[c] = (float)a;
+  sums[C + c] = (float)b;
+}
+
 }  // namespace ssb
 
 extern "C" int ss_bn_parts(int R) { return ssb::cdiv(R, ssb::BN_ROWS); }
@@ -170,9 +196,42 @@ extern "C" int ss_bn_stats(const void* x, long long ld, long long plane, int R, 
   const int parts = cdiv(R, BN_ROWS);
   if (training)
     bn_partial_kernel<<<dim3(cdiv(C, 256), parts), 256, 0, st>>>((const __nv_bfloat16*)x, ld, plane, nullptr, R, C, partial);
-  bn_stats_final_kernel<<<cdiv(C, 256), 256, 0, st>>>(partial, parts, R, C, gamma, beta, eps, momentum, training,
+  bn_stats_final_kernel<<<cdiv(C, 256), 256, 0, st>>>(partial, parts, R, C, nullptr, gamma, beta, eps, momentum, training,
                                                       running_mean, running_var, coef);
   return check_launch("ss_bn_stats");
+}
+
+// ---- data-parallel mode B: the same statistics over the rows of ALL ranks.  The caller sum-allreduces
+// `sums` (and the two counts) between ss_bn_sums and the *_from_sums call.
+extern "C" int ss_bn_sums(const void* x, long long ld, long long plane, const float* dy, int R, int C, float* partial,
+                          float* sums, void* stream) {
+  using namespace ssb;
+  cudaStream_t st = (cudaStream_t)stream;
+  const int parts = cdiv(R, BN_ROWS);
+  bn_partial_kernel<<<dim3(cdiv(C, 256), parts), 256, 0, st>>>((const __nv_bfloat16*)x, ld, plane, dy, R, C, partial);
+  bn_reduce_kernel<<<cdiv(C, 256), 256, 0, st>>>(partial, parts, C, sums);
+  return check_launch("ss_bn_sums");
+}
+
+extern "C" int ss_bn_stats_from_sums(const float* sums, const float* counts, int C, const float* gamma, const float* beta,
+                                     float eps, float momentum, float* running_mean, float* running_var, float* coef,
+                                     void* stream) {
+  using namespace ssb;
+  bn_stats_final_kernel<<<cdiv(C, 256), 256, 0, (cudaStream_t)stream>>>(sums, 1, 0, C, counts, gamma, beta, eps, momentum, 1,
+                                                                        running_mean, running_var, coef);
+  return check_launch("ss_bn_stats_from_sums");
+}
+
+extern "C" int ss_bn_bwd_from_sums(float* dy, const void* x, long long ld, long long plane, int R, int C, const float* coef,
+                                   const float* sums_local, const float* sums_global, const float* counts, float* dgamma,
+                                   float* dbeta, float* bwd, void* stream) {
+  using namespace ssb;
+  cudaStream_t st = (cudaStream_t)stream;
+  bn_bwd_final_kernel<<<cdiv(C, 256), 256, 0, st>>>(sums_local, 1, R, C, sums_global, counts, coef, 1, dgamma, dbeta, bwd);
+  const long long n = (long long)R * C;
+  bn_bwd_apply_kernel<<<(int)min((long long)ssb::sm_count() * 8, (n + 255) / 256), 256, 0, st>>>(dy, (const __nv_bfloat16*)x, ld,
+                                                                                      plane, n, C, coef, bwd);
+  return check_launch("ss_bn_bwd_from_sums");
 }
 
 extern "C" int ss_head_fold_bias(const float* W, const float* b, const float* coef, int O, int C, float* bout,
@@ -188,7 +247,7 @@ extern "C" int ss_bn_bwd(float* dy, const void* x, long long ld, long long plane
   cudaStream_t st = (cudaStream_t)stream;
   const int parts = cdiv(R, BN_ROWS);
   bn_partial_kernel<<<dim3(cdiv(C, 256), parts), 256, 0, st>>>((const __nv_bfloat16*)x, ld, plane, dy, R, C, partial);
-  bn_bwd_final_kernel<<<cdiv(C, 256), 256, 0, st>>>(partial, parts, R, C, coef, training, dgamma, dbeta, bwd);
+  bn_bwd_final_kernel<<<cdiv(C, 256), 256, 0, st>>>(partial, parts, R, C, nullptr, nullptr, coef, training, dgamma, dbeta, bwd);
   const long long n = (long long)R * C;
   const bool vec4 = C % 4 == 0 && ld % 4 == 0 && plane % 4 == 0 && n / 4 < 0xffffffffll &&
                     ((reinterpret_cast<uintptr_t>(dy) | reinterpret_cast<uintptr_t>(coef) | reinterpret_cast<uintptr_t>(bwd)) & 15) == 0 &&

@@ -19,11 +19,10 @@
 
 namespace ssb {
 
-constexpr int GB_M = 128, GB_N = 128, GB_K = 64, G_STAGES = 3, G_THREADS = 192;
+constexpr int GB_M = 128, GB_N = 128, GB_K = 64, G_STAGES = 3, G_EPI_WARPS = 8, G_THREADS = 64 + 32 * G_EPI_WARPS;
 constexpr int G_PLANE = GB_M * GB_K * 2;                 // 16 KB: one bf16 plane of one operand tile
 constexpr int G_STAGE_BYTES = 4 * G_PLANE;               // A(hi,lo) + B(hi,lo)
-constexpr int G_EPI_PITCH = 36;                          // floats per staged row: conflict-free 16-byte writes and reads
-constexpr int G_EPI_BYTES = 4 * 32 * G_EPI_PITCH * 4;    // one 32 x 32 block per epilogue warp
+constexpr int G_EPI_BYTES = G_EPI_WARPS * 32 * 32 * 4;   // one 32 x 32 fp32 block per epilogue warp (XOR-swizzled, no padding)
 constexpr int G_SMEM = G_STAGES * G_STAGE_BYTES + G_EPI_BYTES + 1024 /*align*/ + 256 /*barriers*/;
 constexpr int G_TMEM = 2 * GB_N;                         // two accumulators: epilogue of tile i overlaps mainloop of i+1
 
@@ -77,7 +76,7 @@ gemm_sb16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(&tfull[a], 1);
-      mbar_init(&tempty[a], 4);
+      mbar_init(&tempty[a], G_EPI_WARPS);
     }
     fence_barrier_init();
   }
@@ -143,68 +142,91 @@ gemm_sb16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       }
     }
   } else {
-    // epilogue: warp w may touch TMEM lanes [32*(w%4), +32)
-    const int q = warp & 3;
+    // Epilogue, 8 warps: warp w may touch TMEM lanes [32*(w%4), +32); warps 2..5 drain columns [0, 64) of the tile,
+    // warps 6..9 columns [64, 128).  A thread owns an accumulator ROW after tcgen05.ld; one transposing pass through
+    // shared memory (4 KB per warp, 16-byte pieces XOR-swizzled with the row so both passes are conflict-free) turns
+    // that into the store role -- a fixed column quad, 8 rows -- where a warp instruction covers 4 rows x 128 contiguous
+    // bytes and alpha / bias / beta are applied per column quad (one bias load per 32-column chunk, the `beta` reads of a
+    // chunk all issued before the first use).  The per-warp instruction stream is what bounds a short-K GEMM:
+    // profiles/r02_summary.md (ncu, K = 257: 9.4k warp-instructions per tile with 4 warps -> this form).
+    const int q = warp & 3, ch = (warp - 2) >> 2;
+    const int sr = lane >> 3, cqi = lane & 7;                  // store role: row within a group of 4, column quad
+    float4* stg = reinterpret_cast<float4*>(epi) + (warp - 2) * 256;        // this warp's 32 x 8 float4 staging block
+    const bool unit4 = p.rowmap == SS_ROWMAP_UNIT4;
+    const long long rstep = unit4 ? p.ldc : 4 * p.ldc;         // rows rl = 4 rr + sr: output pointer advance per rr
     int lt = 0;
     for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x, ++lt) {
       const int z = tile / (mt * nt), rem = tile - z * mt * nt;
       const int m0 = (rem / nt) * GB_M, n0 = (rem % nt) * GB_N;
       const int acc = lt & 1;
-      const int m = m0 + q * 32 + lane;
+      const int mw = m0 + q * 32;                              // first row of this warp (a multiple of 32)
       mbar_wait(&tfull[acc], (lt >> 1) & 1);
       tc_fence_after();
-      const uint32_t tmem_d = tmem_base + acc * GB_N;
-      long long orow = m;
-      if (p.rowmap == SS_ROWMAP_UNIT4) orow = (long long)(m & 3) * p.hidden + (m >> 2);
+      const uint32_t tmem_d = tmem_base + acc * GB_N + ((uint32_t)(q * 32) << 16);
       float* Cz = p.C[z];
-      float* crow = Cz + orow * p.ldc;
       const bool vec = ((p.ldc & 3) == 0) && ((reinterpret_cast<uintptr_t>(Cz) & 15) == 0);
-      float* stg = epi + (warp - 2) * 32 * G_EPI_PITCH;         // this warp's staging block
-      const int sr = lane >> 3, sc = (lane & 7) * 4;            // store role: row within a group of 4, column quad
-      for (int c = 0; c < GB_N; c += 32) {
-        if (n0 + c >= p.N) break;                       // warp-uniform
-        float v[32];
-        tmem_ld16(tmem_d + ((uint32_t)(q * 32) << 16) + c, v);
-        tmem_ld16(tmem_d + ((uint32_t)(q * 32) << 16) + c + 16, v + 16);
-        const int nb = n0 + c;
+      // row mw + sr of the store role: natural, or gate-interleaved 4u+g -> g*hidden + u (mw % 4 == 0, so g = sr)
+      const long long orow0 = unit4 ? (long long)sr * p.hidden + (mw >> 2) : (long long)(mw + sr);
+      const int rows_ok = p.M - mw - sr;                       // row rl = 4 rr + sr exists iff 4 rr < rows_ok
 #pragma unroll
-        for (int i = 0; i < 32; ++i) {
-          float r = p.alpha * v[i];
-          if (p.bias && nb + i < p.N) r += p.bias[nb + i];
-          v[i] = r;
-        }
+      for (int cc = 0; cc < 2; ++cc) {
+        const int c = ch * 64 + cc * 32, nb = n0 + c;
+        if (nb >= p.N) break;                                  // warp-uniform
+        float v[32];
+        tmem_ld32(tmem_d + c, v);
         if (vec && nb + 32 <= p.N) {
-          // a thread owns an accumulator ROW; through shared memory a warp instruction stores 4 rows x 128 contiguous
-          // bytes instead of 32 rows x 16 bytes
 #pragma unroll
           for (int i = 0; i < 8; ++i)
-            *reinterpret_cast<float4*>(stg + lane * G_EPI_PITCH + 4 * i) = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+            stg[lane * 8 + (i ^ (lane & 7))] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
           __syncwarp();
+          float4 b4 = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (p.bias) {
+            const float* bp = p.bias + nb + 4 * cqi;
+            b4 = make_float4(bp[0], bp[1], bp[2], bp[3]);
+          }
+          float* dst = Cz + orow0 * p.ldc + nb + 4 * cqi;
+          float4 o[8];
 #pragma unroll
           for (int rr = 0; rr < 8; ++rr) {
-            const int rl = rr * 4 + sr, mm = m0 + q * 32 + rl;
-            float4 o = *reinterpret_cast<const float4*>(stg + rl * G_EPI_PITCH + sc);
-            if (mm < p.M) {
-              long long orow2 = mm;
-              if (p.rowmap == SS_ROWMAP_UNIT4) orow2 = (long long)(mm & 3) * p.hidden + (mm >> 2);
-              float4* dst = reinterpret_cast<float4*>(Cz + orow2 * p.ldc + nb + sc);
-              if (p.beta != 0.0f) {
-                const float4 old = *dst;
-                o.x += p.beta * old.x; o.y += p.beta * old.y; o.z += p.beta * old.z; o.w += p.beta * old.w;
-              }
-              *dst = o;
+            const int rl = rr * 4 + sr;
+            o[rr] = stg[rl * 8 + (cqi ^ (rl & 7))];
+            o[rr].x = fmaf(p.alpha, o[rr].x, b4.x); o[rr].y = fmaf(p.alpha, o[rr].y, b4.y);
+            o[rr].z = fmaf(p.alpha, o[rr].z, b4.z); o[rr].w = fmaf(p.alpha, o[rr].w, b4.w);
+          }
+          if (p.beta != 0.0f) {
+            float4 old[8];
+#pragma unroll
+            for (int rr = 0; rr < 8; ++rr)
+              old[rr] = 4 * rr < rows_ok ? *reinterpret_cast<const float4*>(dst + rr * rstep) : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+            for (int rr = 0; rr < 8; ++rr) {
+              o[rr].x = fmaf(p.beta, old[rr].x, o[rr].x); o[rr].y = fmaf(p.beta, old[rr].y, o[rr].y);
+              o[rr].z = fmaf(p.beta, old[rr].z, o[rr].z); o[rr].w = fmaf(p.beta, old[rr].w, o[rr].w);
             }
           }
-          __syncwarp();
-        } else if (m < p.M) {
 #pragma unroll
-          for (int i = 0; i < 32; ++i)
-            if (nb + i < p.N) crow[nb + i] = v[i] + (p.beta != 0.0f ? p.beta * crow[nb + i] : 0.0f);
+          for (int rr = 0; rr < 8; ++rr)
+            if (4 * rr < rows_ok) *reinterpret_cast<float4*>(dst + rr * rstep) = o[rr];
+          __syncwarp();
+        } else {
+          // edge columns / unaligned output: the thread stores its own row
+          const int m = mw + lane;
+          if (m < p.M) {
+            const long long orow = unit4 ? (long long)(m & 3) * p.hidden + (m >> 2) : (long long)m;
+            float* crow = Cz + orow * p.ldc;
+#pragma unroll
+            for (int i = 0; i < 32; ++i)
+              if (nb + i < p.N) {
+                float r = p.alpha * v[i];
+                if (p.bias) r += p.bias[nb + i];
+                crow[nb + i] = r + (p.beta != 0.0f ? p.beta * crow[nb + i] : 0.0f);
+              }
+          }
         }
       }
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&tempty[acc]);         // this warp's TMEM lanes of the accumulator are free again
+      if (lane == 0) mbar_arrive(&tempty[acc]);         // this warp's TMEM lanes / columns of the accumulator are free again
     }
   }
   __syncthreads();

@@ -185,6 +185,20 @@ pit_bwd_kernel(const float* __restrict__ z, long long ldz, const float* __restri
 
 }  // namespace ssb
 
+namespace ssb {
+__global__ void pit_stats_finalize_kernel(float* stats, int n_src) {
+  stats[2] = stats[0] / stats[1];
+  stats[3] = (float)(1.0 / ((double)n_src * (double)stats[1]));
+}
+}  // namespace ssb
+
+// data-parallel mode B: stats[0] (sum of min losses / S) and stats[1] (norm) have been sum-allreduced over the ranks;
+// recompute the loss and the gradient scale from them
+extern "C" int ss_pit_stats_finalize(float* stats, int n_src, void* stream) {
+  ssb::pit_stats_finalize_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(stats, n_src);
+  return ssb::check_launch("ss_pit_stats_finalize");
+}
+
 extern "C" int ss_pit_chunks(int T) { return ssb::cdiv(T, ssb::PL_CHUNK); }
 
 extern "C" int ss_pit_loss_fwd(const float* z, long long ldz, const float* mix, const float* src, const int* lens,

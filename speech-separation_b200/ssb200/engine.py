@@ -20,6 +20,7 @@ behind a stream-ordered wait on the progress counter and capped to the idle SMs 
 GEMM form (ss_gemm_sb16_tn): activations and gate gradients are read as they were written, no transposed copies.
 """
 import ctypes
+import os
 
 import torch
 
@@ -29,9 +30,12 @@ from .ops import SB16, up8
 
 H = 600          # archs/uPIT.py:115, archs/RSH.py:155 (hard-coded in the reference)
 UNIT4 = 1
-STREAM = True    # stream GEMMs under the recurrences (module switch for A/B tests; results are identical either way)
+# stream GEMMs under the recurrences (module switch for A/B tests and profiling; results agree either way)
+STREAM = os.environ.get("SSB_STREAM", "1") != "0"
 N_CHUNKS = 8     # time chunks of a streamed GEMM
+FWD_STREAM_FRACTION = 0.64   # forward: stream the x-projection halves that are ready within this fraction of the recurrence
 MIN_STREAM_T = 48
+GRAPH_REFRESH = os.environ.get("SSB_GRAPH_REFRESH", "1") != "0"
 
 
 def _sb_view(sb, row0=0, rows=None, col0=0, cols=None):
@@ -70,9 +74,33 @@ class Weights:
         self.linT = SB16(2 * H, out_dim, device)           # natural W_lin^T for the dY GEMM
         self.lin_folded = SB16(out_dim, 2 * H, device)     # W_lin * diag(bn scale), per batch
         self.bias_folded = torch.empty(out_dim, dtype=torch.float32, device=device)
+        self._graphs = {}
+        self.graph_replays = 0          # replays so far; each stands for launches_per_refresh() kernel launches
+
+    def launches_per_refresh(self, need_grad_copies=True):
+        return self.L * 2 * (3 + (1 if need_grad_copies else 0)) + (1 if need_grad_copies else 0)
 
     def refresh(self, p, need_grad_copies=True):
-        """p: dict name -> fp32 cuda tensor with the reference's state_dict names."""
+        """p: dict name -> fp32 cuda tensor with the reference's state_dict names.  The ~25 tiny split / bias launches
+        are launch-latency bound (1.3 ms of host-paced gaps per train step), so they are captured once per set of
+        parameter addresses into a CUDA graph and replayed (one launch) afterwards."""
+        key = (bool(need_grad_copies),) + tuple(t.data_ptr() for t in p.values())
+        g = self._graphs.get(key)
+        if g is not None:
+            g.replay()
+            self.graph_replays += 1
+            return
+        self._refresh_eager(p, need_grad_copies)
+        if not GRAPH_REFRESH:
+            return
+        if len(self._graphs) >= 4:
+            self._graphs.clear()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            self._refresh_eager(p, need_grad_copies)
+        self._graphs[key] = g
+
+    def _refresh_eager(self, p, need_grad_copies):
         for l in range(self.L):
             for d, suf in enumerate(("", "_reverse")):
                 w_ih = p["blstm.weight_ih_l%d%s" % (l, suf)]
@@ -122,6 +150,8 @@ class Workspace:
         self._used = torch.zeros(Bc, dtype=torch.int32, device=device)
         self.stats = torch.zeros(4, **f32)
         # progress counters of the recurrence kernels: [fwd dir0, fwd dir1, bwd dir0, bwd dir1]; values only grow
+        # data-parallel mode B: {sum x, sum x^2 | B_total, T_max} and the backward pair {sum dy, sum dy*x}, local + global
+        self.bn_sums = torch.zeros(3, 2 * (2 * H) + 2, **f32)
         self.progress = torch.zeros(4, dtype=torch.int32, device=device)
         self.prog_base = 0
         self.training = training
@@ -217,6 +247,10 @@ class _Streamer:
         self.sm_limit = idle_sms(device, backward, ws.B)
         self.jobs, self.late = [], []
         self.base = ws.next_base()
+        # inputs of the gated jobs that precede the recurrence on the main stream: recorded BEFORE the recurrence is
+        # launched (an event recorded after it would only fire when the kernel has ended)
+        self.before = torch.cuda.Event()
+        self.before.record()
 
     def add(self, waits, fn, order=0):
         """fn(sm_limit) may run once, for every (direction, steps) in `waits`, that many steps of the direction are
@@ -233,9 +267,7 @@ class _Streamer:
         """Enqueue the gated jobs on the side stream (call right AFTER the recurrence launch has succeeded)."""
         if not self.jobs:
             return
-        ev = torch.cuda.Event()
-        ev.record()
-        self.side.wait_event(ev)                               # inputs that precede the recurrence on the main stream
+        self.side.wait_event(self.before)
         with torch.cuda.stream(self.side):
             for ready, _, waits, fn in sorted(self.jobs, key=lambda j: (j[0], j[1])):
                 for direction, steps in waits:
@@ -259,10 +291,10 @@ def _lstm_fwd(ws, wt, l, h0, c0, lens_dev, training, sj):
          ctypes.c_uint(sj.base if sj else 0), ws.T, ws.B, H, stream_ptr())
 
 
-def forward(ws, wt, p, x, lens_dev, h0, c0, bn_train, save=True, bn_momentum=0.1, bn_eps=1e-5):
+def forward(ws, wt, p, x, lens_dev, h0, c0, bn_train, save=True, bn_momentum=0.1, bn_eps=1e-5, dp=None):
     """x: fp32 (T*B, in_dim) padded time-major.  Leaves the head pre-activations in ws.z[:, :out_dim].
     bn_train: BatchNorm uses batch statistics and updates the running ones (model.train()); save: keep what the
-    backward pass needs."""
+    backward pass needs.  dp (data-parallel mode B, ssb200.train.ExactDP): BatchNorm statistics over all ranks' rows."""
     training = save
     T, B, TB = ws.T, ws.B, ws.TB
     st = stream_ptr()
@@ -280,36 +312,61 @@ def forward(ws, wt, p, x, lens_dev, h0, c0, bn_train, save=True, bn_momentum=0.1
             continue
         # x-projection of layer l+1, streamed: direction d's half of out[l] for frames [a, b) is final after b steps of
         # direction 0 (t = 0..) / T - a steps of direction 1 (t = T-1..); whichever half of a chunk comes first writes
-        # (beta = 0, + bias), the other accumulates
+        # (beta = 0, + bias), the other accumulates.  The 48 idle SMs cannot absorb the whole GEMM inside the recurrence's
+        # 2.9 ms (profiles/r02_summary.md), so only halves that are ready in its first FWD_STREAM_FRACTION are streamed;
+        # the others follow on the main stream at full width, as ONE full-K GEMM where both halves of a chunk are late.
         o, w, gx, bias = ws.out[l], wt.wih[l + 1], ws.gx[l + 1], wt.bias[l + 1]
+        cut = min(sj.max_reported, int(FWD_STREAM_FRACTION * T))
         for (a, b) in _chunks(T, N_CHUNKS):
             r0, rows = a * B, (b - a) * B
-            ready = (b, T - a)
-            first = 0 if ready[0] <= ready[1] else 1
-            for d in (0, 1):
-                def job(sm_limit, d=d, r0=r0, rows=rows, acc=(d != first)):
+            halves = sorted(((b, 0), (T - a, 1)))              # (ready, direction), earliest first
+            if halves[0][0] > cut:
+                def full(sm_limit, r0=r0, rows=rows):
+                    _gemm(_sb_view(o, r0, rows), w, gx[r0:], bias=bias, M=rows, N=8 * H, K=2 * H, sm_limit=sm_limit)
+                sj.late.append((halves[0][0], 0, full))
+                continue
+            for i, (ready, d) in enumerate(halves):
+                def job(sm_limit, d=d, r0=r0, rows=rows, acc=(i == 1)):
                     _gemm(_sb_view(o, r0, rows, d * H, H), _sb_view(w, 0, 8 * H, d * H, H), gx[r0:], bias=None if acc else bias,
                           beta=1.0 if acc else 0.0, M=rows, N=8 * H, K=H, sm_limit=sm_limit)
-                sj.add(((d, ready[d]),), job, order=0 if d == first else 1)
+                if ready <= cut:
+                    sj.add(((d, ready),), job, order=i)
+                else:
+                    sj.late.append((ready, i, job))
         sj.launch()
         sj.run_late()
     top = ws.out[-1]
-    call("bn_stats", top.buf, LL(top.ld), LL(top.plane), TB, 2 * H, p["bn.weight"], p["bn.bias"], float(bn_eps),
-         float(bn_momentum), int(bn_train), p["bn.running_mean"], p["bn.running_var"], ws.bn_partial, ws.coef, st)
+    if dp is not None and bn_train:
+        C = 2 * H
+        loc = ws.bn_sums[0]
+        call("bn_sums", top.buf, LL(top.ld), LL(top.plane), None, TB, C, ws.bn_partial, loc, st)
+        loc[2 * C:].copy_(dp.counts(B, T, x.device), non_blocking=True)
+        dp.allreduce_sum(loc[:2 * C + 1])                      # sum x, sum x^2, total batch size
+        dp.allreduce_max(loc[2 * C + 1:])                      # longest T: rows of the concatenated batch = B_total * T_max
+        call("bn_stats_from_sums", loc, loc[2 * C:], C, p["bn.weight"], p["bn.bias"], float(bn_eps), float(bn_momentum),
+             p["bn.running_mean"], p["bn.running_var"], ws.coef, st)
+    else:
+        call("bn_stats", top.buf, LL(top.ld), LL(top.plane), TB, 2 * H, p["bn.weight"], p["bn.bias"], float(bn_eps),
+             float(bn_momentum), int(bn_train), p["bn.running_mean"], p["bn.running_var"], ws.bn_partial, ws.coef, st)
     _split_into(p["lin.weight"], wt.lin_folded, col_scale=ws.coef[0])
     call("head_fold_bias", p["lin.weight"], p["lin.bias"], ws.coef, ws.out_dim, 2 * H, wt.bias_folded, st)
     _gemm(top, wt.lin_folded, ws.z, bias=wt.bias_folded, M=TB)
     return ws.z
 
 
-def pit_loss(ws, mix, src, lens_dev, F, n_out, n_src, mode=0, accumulate=False, mask_out=None, used=None, stats=None):
+def pit_loss(ws, mix, src, lens_dev, F, n_out, n_src, mode=0, accumulate=False, mask_out=None, used=None, stats=None, dp=None):
     """mix fp32 (T*B,F); src fp32 (n_src,T*B,F).  Fills ws.losses/idx/assign and stats (ws.stats unless a shared
-    accumulator is given, as the RSH passes do together with the shared `used` bitmasks)."""
+    accumulator is given, as the RSH passes do together with the shared `used` bitmasks).  dp (mode B): the loss
+    normaliser is the frame count of ALL ranks (archs/uPIT.py:204 on the concatenated batch)."""
     st = stream_ptr()
     call("pit_loss_fwd", ws.z, LL(ws.ldz), mix, src, lens_dev, ws.T, ws.B, F, n_out, n_src, mask_out, ws.pit_partial, st)
     call("pit_select", ws.pit_partial, lib().ss_pit_chunks(ws.T), lens_dev, ws.B, F, n_out, n_src, mode,
          int(accumulate), ws.losses, ws.idx, ws.assign, ws.used if used is None else used,
          ws.stats if stats is None else stats, st)
+    if dp is not None:
+        stt = ws.stats if stats is None else stats
+        dp.allreduce_sum(stt[:2])
+        call("pit_stats_finalize", stt, n_src, st)
 
 
 def _gemm_tn(a, a_col0, a_col_batch, b, b_col0, b_col_batch, R, blk0, n_blk, shifts, batch, c0, c1, ldc, M, N, beta,
@@ -327,7 +384,7 @@ def _block_chunks(nblk, n):
 
 
 def backward(ws, wt, p, grads, mix, src, lens_dev, h0, c0, F, n_out, gout, dmask_extra=None, dhn=None, dcn=None,
-             want_dx=False, want_d0=False, training=True, accumulate=False, hook=None, stats=None):
+             want_dx=False, want_d0=False, training=True, accumulate=False, hook=None, stats=None, dp=None):
     """Backward of loss -> every parameter gradient in `grads` (dict name -> fp32 tensor, natural layouts).
     Returns (dx or None, dh0 or None, dc0 or None)."""
     T, B, TB = ws.T, ws.B, ws.TB
@@ -353,8 +410,17 @@ def backward(ws, wt, p, grads, mix, src, lens_dev, h0, c0, F, n_out, gout, dmask
             hook("head")
 
     _gemm(ws.dz, wt.linT, ws.dy, M=TB, K=O)
-    call("bn_bwd", ws.dy, top.buf, LL(top.ld), LL(top.plane), TB, 2 * H, ws.coef, int(training), ws.bn_partial,
-         ws.dgamma, ws.dbeta, ws.bn_bwd, stream_ptr())
+    if dp is not None and training:
+        C = 2 * H
+        loc, glob = ws.bn_sums[1], ws.bn_sums[2]
+        call("bn_sums", top.buf, LL(top.ld), LL(top.plane), ws.dy, TB, C, ws.bn_partial, loc, stream_ptr())
+        glob[:2 * C].copy_(loc[:2 * C], non_blocking=True)
+        dp.allreduce_sum(glob[:2 * C])                         # sum dy, sum dy*x over all ranks
+        call("bn_bwd_from_sums", ws.dy, top.buf, LL(top.ld), LL(top.plane), TB, C, ws.coef, loc, glob, ws.bn_sums[0][2 * C:],
+             ws.dgamma, ws.dbeta, ws.bn_bwd, stream_ptr())
+    else:
+        call("bn_bwd", ws.dy, top.buf, LL(top.ld), LL(top.plane), TB, 2 * H, ws.coef, int(training), ws.bn_partial,
+             ws.dgamma, ws.dbeta, ws.bn_bwd, stream_ptr())
     _acc(grads, "bn.weight", ws.dgamma, accumulate)
     _acc(grads, "bn.bias", ws.dbeta, accumulate)
     dout = ws.dy

@@ -71,6 +71,26 @@ def allreduce_buckets(flat, buckets, group=None, tags=BUCKET_ORDER):
     return works
 
 
+class ExactDP:
+    """Data-parallel mode B: the small collectives that make N ranks reproduce the reference's arithmetic
+    on the concatenated batch -- sum of (BatchNorm sums, batch size), max of T, sum of (loss numerator, normaliser), sum
+    of the BatchNorm backward sums.  Stream-ordered NCCL calls on the current stream; nothing is read back."""
+
+    def __init__(self, group=None):
+        self.group = group
+
+    def counts(self, B, T, device):
+        return torch.tensor([float(B), float(T)], dtype=torch.float32).pin_memory().to(device, non_blocking=True)
+
+    def allreduce_sum(self, t):
+        import torch.distributed as dist
+        dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.group)
+
+    def allreduce_max(self, t):
+        import torch.distributed as dist
+        dist.all_reduce(t, op=dist.ReduceOp.MAX, group=self.group)
+
+
 class _Staged(dict):
     """A collated batch whose PackedSequence data already travels to (or sits on) the device; .event marks the copy."""
     event = None
@@ -79,16 +99,23 @@ class _Staged(dict):
 class Trainer:
     """Owns the flat parameter / gradient / Adam buckets of one SepDNN and runs whole train steps."""
 
-    def __init__(self, model, arch, lr=1e-3, clip=0.25, betas=(0.9, 0.999), eps=1e-8, group=None, host_rng=False):
+    def __init__(self, model, arch, lr=1e-3, clip=0.25, betas=(0.9, 0.999), eps=1e-8, group=None, host_rng=False,
+                 exact=False):
         """host_rng: draw the random initial state (h0, c0) of every batch on the CPU generator and copy it over,
         exactly as the reference's init_hidden does (archs/uPIT.py:121-127); default draws the same N(0,1) state on
-        the device generator, which keeps ~2 ms of host work and a blocking copy out of every step."""
+        the device generator, which keeps ~2 ms of host work and a blocking copy out of every step.
+        exact: data-parallel mode B -- loss normaliser and BatchNorm statistics over all ranks' utterances, gradients
+        summed (not averaged): the N-rank step IS the reference step on the concatenated batch (uPIT arch only)."""
         import torch.distributed as dist
         self.model, self.arch = model, arch
         self.host_rng = host_rng
         self.lr, self.clip, self.betas, self.eps = float(lr), float(clip), betas, float(eps)
         self.world = dist.get_world_size(group) if dist.is_available() and dist.is_initialized() else 1
         self.group = group
+        self.exact = bool(exact) and self.world > 1
+        if self.exact and not hasattr(arch, "loss_and_grads"):
+            raise ValueError("exact data-parallel mode needs the arch's loss_and_grads")
+        self.dp = ExactDP(group) if self.exact else None
         named = [(k, p) for k, p in model.named_parameters()]
         dev = named[0][1].device
         if dev.type != "cuda":
@@ -157,13 +184,45 @@ class Trainer:
         """One optimisation step on a collated batch.  Returns device scalars (loss, norm) of this rank's shard."""
         if getattr(batch_sample, "event", None) is not None:
             torch.cuda.current_stream().wait_event(batch_sample.event)
+        kw = {"dp": self.dp} if self.exact else {}
         loss, norm = self.arch.loss_and_grads(self.model, batch_sample, self.grads, hook=self._bucket_ready,
-                                              hidden=None if self.host_rng else self._device_hidden)
+                                              hidden=None if self.host_rng else self._device_hidden, **kw)
         loss, norm = loss.clone(), norm.clone()
         if self.world > 1:
             torch.cuda.current_stream().wait_stream(self.comm)
         self.apply_update()
         return loss, norm
+
+    def grad_exchange_check(self, batch_sample):
+        """Diagnostic for N > 1 (bench.py `dp_grad_check`, outside any timed region): one backward pass WITHOUT the
+        exchange gives this rank's gradient; all ranks' gradients are gathered, and the bucketed allreduce the real step
+        uses must deliver exactly their sum (the clip kernel then scales by 1/world in mode A).  Parameters and optimizer
+        state are not touched.  Returns {max_abs_err, ref_max_abs, rank_spread}."""
+        import torch.distributed as dist
+        if self.world == 1:
+            return None
+        fixed = {}                                               # the same (h0, c0) for the two passes below
+
+        def hidden(B):
+            if B not in fixed:
+                fixed[B] = self._device_hidden(B)
+            return fixed[B]
+        kw = {"dp": self.dp} if self.exact else {}
+        bn = [b.clone() for b in (self.model.bn.running_mean, self.model.bn.running_var)]
+        self.arch.loss_and_grads(self.model, batch_sample, self.grads, hook=None, hidden=hidden, **kw)
+        local = self.flat_g.clone()
+        gathered = [torch.empty_like(local) for _ in range(self.world)]
+        dist.all_gather(gathered, local, group=self.group)
+        want = torch.stack(gathered).sum(0)
+        self.arch.loss_and_grads(self.model, batch_sample, self.grads, hook=self._bucket_ready, hidden=hidden, **kw)
+        torch.cuda.current_stream().wait_stream(self.comm)
+        err = float((self.flat_g - want).abs().max())
+        spread = float((gathered[0] - gathered[-1]).abs().max())
+        for dst, src in zip((self.model.bn.running_mean, self.model.bn.running_var), bn):
+            dst.copy_(src)
+        return {"max_abs_err": err, "ref_max_abs": float(want.abs().max()), "rank_spread_max_abs": spread,
+                "exchange": "sum over ranks of flat buckets (l0 | l1 | head); scaled by %s in the clip kernel"
+                            % ("1" if self.exact else "1/world")}
 
     def _device_hidden(self, batch_size):
         dev = self.flat_p.device
@@ -173,7 +232,7 @@ class Trainer:
     def apply_update(self):
         """clip_grad_norm_(clip) + Adam.step() on the flat buckets (steps/train_qsub.py:121-122)."""
         st = stream_ptr()
-        gscale = 1.0 / self.world
+        gscale = 1.0 if self.exact else 1.0 / self.world       # mode B sums the ranks' gradients, mode A averages them
         self.steps += 1
         call("grad_norm", self.flat_g, LL(self.n), gscale, self.partial, self.norm, st)
         call("clip_adam", self.flat_p, self.flat_g, self.flat_m, self.flat_v, LL(self.n), self.norm, gscale,

@@ -205,7 +205,7 @@ def unpack_batch(batch_sample, keys, device, src_keys=()):
     return out
 
 
-def run_forward(model, batch, hidden, save, slot=0, x=None):
+def run_forward(model, batch, hidden, save, slot=0, x=None, dp=None):
     p = model.param_dict()
     wt = model.weights(p, need_grad_copies=save)
     ws = model.workspace(batch["T"], batch["B"], save, slot)
@@ -213,7 +213,7 @@ def run_forward(model, batch, hidden, save, slot=0, x=None):
     h0, c0 = hidden
     pd = {k: v.detach() for k, v in p.items()}
     return engine.forward(ws, wt, pd, batch["mix"] if x is None else x, batch["lens_dev"], h0.contiguous(), c0.contiguous(),
-                          bn_train=model.training, save=save)
+                          bn_train=model.training, save=save, dp=dp)
 
 
 class _UPITLoss(torch.autograd.Function):
@@ -260,22 +260,24 @@ def compute_loss(model, epoch, batch_sample, plotdir=""):
     return loss, norm.detach()
 
 
-def loss_and_grads(model, batch_sample, grads, hook=None, hidden=None):
+def loss_and_grads(model, batch_sample, grads, hook=None, hidden=None, dp=None):
     """compute_loss + loss.backward() without the autograd tape: every parameter gradient is written (not
     accumulated) straight into grads[name] -- e.g. views of the trainer's flat bucket (ssb200/train.py).  `hook(tag)`
     is called when a gradient bucket ('head', 'l1', 'l0') has been enqueued; `hidden(B)` (optional) supplies (h0, c0)
-    instead of model.init_hidden.  Returns device scalars (loss, norm)."""
+    instead of model.init_hidden; `dp` (ssb200.train.ExactDP, data-parallel mode B) makes the loss normaliser and the
+    BatchNorm statistics those of all ranks' utterances together, so that the SUM of the ranks' gradients is the
+    reference's gradient on the concatenated batch.  Returns device scalars (loss, norm)."""
     dev = model.lin.weight.device
     batch = unpack_batch(batch_sample, ["mix"], dev, ["source%d" % (i + 1) for i in range(model.num_spk)])
     model.hidden = model.init_hidden(batch["B"]) if hidden is None else hidden(batch["B"])
     with torch.no_grad():
-        run_forward(model, batch, model.hidden, save=True)
+        run_forward(model, batch, model.hidden, save=True, dp=dp)
         ws, wt = batch["ws"], batch["wt"]
         S, F = model.num_spk, model.feat_dim
-        engine.pit_loss(ws, batch["mix"], batch["src"], batch["lens_dev"], F, S, S, mode=0)
+        engine.pit_loss(ws, batch["mix"], batch["src"], batch["lens_dev"], F, S, S, mode=0, dp=dp)
         p = {k: v.detach() for k, v in model.param_dict().items()}
         engine.backward(ws, wt, p, grads, batch["mix"], batch["src"], batch["lens_dev"], model.hidden[0].contiguous(),
-                        model.hidden[1].contiguous(), F, S, None, training=model.training, hook=hook)
+                        model.hidden[1].contiguous(), F, S, None, training=model.training, hook=hook, dp=dp)
     model.last = {"losses": ws.losses, "indices": ws.idx, "stats": ws.stats, "batch": batch}
     return ws.stats[2], ws.stats[1]
 
