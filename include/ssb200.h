@@ -40,15 +40,18 @@ int ss_stft_tile_frames(void);
 int ss_stft(const float* sig, const long long* sig_off, const long long* frame_off, const int* tile_off, int n_utts,
             int total_tiles, int n_fft, int hop, int flags, void* out, void* stream);
 
-/* K1 on the tensor cores (csrc/stft_mma.cu): the same magnitude STFT as ss_stft(n_fft = 256, hop = 64, flags = 0),
- * replacing librosa.core.stft + np.abs at steps/extract_feats.py:87,89, evaluated as split-bf16 tcgen05 GEMMs of the
- * folded frames against a resident windowed cos/sin basis.  Work is described per tile of
- * ss_stft_dft256_tile_frames() consecutive frames of ONE utterance: tiles[i] = four int64
- * { s0 = first sample of the utterance in sig, obase = first output element of the utterance (frame_off[u]*129),
- *   N_u | T_u << 32, t0 = first frame of the tile }.  Output as ss_stft: (129, T_u) row-major per utterance.
- * Utterances whose first sample is not 16-byte aligned take a slower scalar load path (same results). */
+/* K1 on the tensor cores (csrc/stft_mma.cu): the same magnitude STFT as ss_stft(n_fft = 256, hop = 64, flags = 0 or
+ * SS_STFT_LOG), replacing librosa.core.stft + np.abs at steps/extract_feats.py:87,89, evaluated as a split-bf16 tcgen05
+ * GEMM of the frames against a resident windowed DFT basis.  hop = n_fft/4 makes frame r the four 64-sample rows
+ * r..r+3 of the reflect-padded signal, so the operand descriptors read frames straight out of ONE bf16 hi/lo copy of the
+ * samples.  Work is the ROW STREAM of all utterances: utterance u owns T_u + 3 rows; utts[u] = four int64
+ * { first sample in sig, first output element (frame_off[u]*129), N_u | T_u << 32, first stream row };
+ * tile_u0[i] = utterance of stream row i * ss_stft_dft256_tile_frames(); total_rows = sum (T_u + 3).
+ * Output as ss_stft: (129, T_u) row-major per utterance.  Utterances whose first sample is 16-byte aligned take the
+ * vector load path (same results). */
 int ss_stft_dft256_tile_frames(void);
-int ss_stft_dft256(const float* sig, const long long* tiles, int n_tiles, float* out, void* stream);
+int ss_stft_dft256(const float* sig, const long long* utts, int n_utts, const int* tile_u0, int n_tiles,
+                   long long total_rows, float* out, int flags, void* stream);
 
 /* ---- K7: masked iSTFT.  Replaces steps/reconstruct_sources.py:39-42 (np.multiply, librosa.core.istft,
  * *32767, astype('int16')) ----

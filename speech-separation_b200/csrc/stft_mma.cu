@@ -1,68 +1,65 @@
-// K1 on the tensor cores: 256-point / hop-64 magnitude STFT as two tcgen05 GEMMs against a resident, windowed
-// DFT basis.  Replaces librosa.core.stft + np.abs at steps/extract_feats.py:87,89 (same contract as ss_stft with
-// n_fft = 256, hop = 64, flags = 0; the FFT kernel in stft.cu stays the general path).
+// K1 on the tensor cores: 256-point / hop-64 magnitude STFT as a tcgen05 GEMM against a resident, windowed DFT basis.
+// Replaces librosa.core.stft + np.abs at steps/extract_feats.py:87,89 (same contract as ss_stft with n_fft = 256,
+// hop = 64, magnitude, (F, T) layout; the FFT kernel in stft.cu stays the general path).
 //
-// Algebra.  With the periodic Hann window w[n] = w[256-n], w[0] = 0 and a real frame x[0..255]:
-//   Re X[k] =  sum_{n=1..128} (w[n] cos(2 pi k n/256)) e[n],   e[n] = x[n] + x[256-n] (n < 128), e[128] = x[128]
-//   Im X[k] = -sum_{n=1..127} (w[n] sin(2 pi k n/256)) o[n],   o[n] = x[n] - x[256-n]
-// so a tile of 128 frames is  E[128 x 128] * C^T[128 x 128]  and  O[128 x 128] * S^T[128 x 128]  (K = n-1, bins 0..127;
-// the Nyquist bin X[128] = sum_n (-1)^n w[n] e[n] is real and summed outside the GEMMs).  The
-// window lives inside the basis (a diagonal scaling along K), the fold halves the flops of a plain 256-point DFT
-// matrix, and every operand is split-bf16 (hi + lo) with the three products hi*hi + hi*lo + lo*hi accumulated in
-// fp32 in TMEM (error ~2^-16, inside the 1e-4 feature bar).
+// Frames are never materialised.  hop = n_fft / 4, so frame r of an utterance is samples [64 r - 128, 64 r + 128) of
+// the reflect-padded signal: with the padded signal stored as ROWS of 64 samples (128 bytes of bf16), frame r is rows
+// r .. r+3 side by side.  A K-major SWIZZLE_128B operand whose start address is advanced by kc rows therefore IS the
+// K block kc (64 samples) of 128 consecutive frames: every sample is split into bf16 hi / lo ONCE, stored ONCE per
+// plane, and read by four different descriptors.  (The previous version folded and re-split every frame: its
+// producers, not its MMAs, bounded it -- profiles/r01_summary.md section K.)
 //
-// One persistent CTA per SM, 21 warps:
-//   warps 0..15  producers: half a warp per frame and 64-wide K block; two LDG.128 (x[n..n+3] and the mirrored quad)
-//                per lane, fold, split into hi/lo bf16, 8-byte stores into a 128B-swizzled K-major A stage.  The odd
-//                part o stays packed in registers until the next ring slot is free, so every sample is loaded once
-//                per frame.  The same warps sum the Nyquist bin, sum_n (-1)^n w[n] e[n], on the FMA pipe (16-lane
-//                shuffle reduction per frame) so that both GEMMs are N = 128 and TMEM holds two full accumulator sets.
-//   warp 16      one thread issues the MMAs (M=128, N=128, K=16; 48 per tile) and the commits
-//   warps 17..20 epilogue: pipelined tcgen05.ld -> sqrt(re^2 + im^2) -> (F, T_u) rows of the utterance; a warp
-//                stores 32 consecutive frames of one bin (128 contiguous bytes)
-// Shared memory: the 128 KB basis image (cos hi | cos lo | sin hi | sin lo, bins 0..127, loaded once per CTA by bulk
-// copies) and a ring of three 32 KB A stages that the fills E(kb0), O(kb0), E(kb1), O(kb1), ... go round.
-// TMEM: 2 x (128 cos + 128 sin) columns; the epilogue drains tile i while the MMAs of tile i+1 run.
-// Measured (profiles/r01_summary.md section K): parity <= 3e-5 against the oracle, 16.4 ms on configs[1] against the
-// FFT kernel's 13.4 ms -- the MMAs take 5.8 ms alone, the producers 10.3 ms alone -- hence opt-in.
+//   X[k] = sum_{n < 256} w[n] x[n] exp(-2 pi i k n / 256),   w = periodic Hann
+//   D[frame][col] = sum_n A[frame][n] * Bas[col][n]   with the window inside the basis (a diagonal scaling along K),
+//   three products hi*hi + hi*lo + lo*hi, fp32 accumulation in TMEM (error ~2^-16, inside the 1e-4 feature bar).
+//
+// The basis (256 outputs x 256 samples x hi/lo = 256 KB) does not fit one SM, so the bins are split between two CTA
+// types: type h holds bins 64 h .. 64 h + 63 (columns 0..63 = Re, 64..127 = Im; 128 KB resident) and both types walk the
+// same tiles, so a tile's samples come from HBM once and from L2 the second time.  Im X[0] is identically zero, so that
+// column of type 0 carries the Nyquist bin instead (real: sum_n (-1)^n w[n] x[n]).
+// Per 16-sample k-step two instructions: x_hi . [B_hi ; B_lo] (N = 256: the hi*hi and hi*lo products side by side in
+// TMEM) and x_lo . B_hi (N = 128, accumulated onto the first half); the epilogue adds the two halves.  Stacking the planes
+// in N fetches 20 KB of operands per k-step from shared memory instead of 24 KB for three N = 128 instructions -- the
+// kernel's MMAs are shared-memory-bandwidth bound (both operands come from there: profiles/r02_summary.md).
+//
+// Work units are 128 consecutive frames of the STREAM of all utterances: utterance u owns T_u + 3 stream rows (its
+// reflect-padded signal), so a tile may straddle two utterances; the 3 frames that would mix two utterances are
+// computed and dropped (0.4 % instead of the 8.5 % a per-utterance tiling wastes on partial tiles at configs[1]).
+//
+// One persistent CTA per SM, 21 warps: warps 0..11 producers (global fp32 -> split -> swizzled stage; the loads of tile
+// i+1 are in flight while tile i is split and stored), warp 12 MMA issuer (32 MMAs per tile), warps 13..20 epilogue
+// (tcgen05.ld -> sqrt(re^2+im^2) -> (F, T_u) rows; a warp stores 32 consecutive frames of one bin = 128 contiguous bytes;
+// two warps per TMEM lane quarter, 32 bins each).  Two sample stages and two TMEM accumulators: producers fill tile i+1
+// and the epilogue drains tile i-1 while the MMAs of tile i run.  Every role is a latency-bound instruction stream
+// (ncu: 0.14 instructions per cycle and scheduler with 8 + 4 warps), hence the warp counts.
 #include "../../include/ssb200.h"
 #include "common.cuh"
 
 namespace ssb {
 
 constexpr int D_TM = 128;                                 // frames per tile
-#ifndef SSB_DFT_EXP
-#define SSB_DFT_EXP 0   // timing experiments (wrong results): 1 no MMAs, 2 no producer work, 4 no epilogue stores
-#endif
-#ifndef SSB_DFT_EPI_WARPS
-#define SSB_DFT_EPI_WARPS 4
-#endif
-constexpr int D_PROD_WARPS = 16, D_EPI_WARPS = SSB_DFT_EPI_WARPS;
-constexpr int D_TASKS = D_TM * 16 / (D_PROD_WARPS * 32);  // (frame, 16-lane) tasks per producer thread and K block
+constexpr int D_ROWS = 136;                               // sample rows per stage: 128 + 3, rounded up to 8-row atoms
+constexpr int D_PROD_WARPS = 12, D_EPI_WARPS = 8;
 constexpr int D_THREADS = (D_PROD_WARPS + 1 + D_EPI_WARPS) * 32;
-constexpr int D_KB = 128 * 128;                           // bytes of one 64-wide K block of one basis plane (128 bins)
-constexpr int D_PLANE = 2 * D_KB;
-constexpr int D_BASIS = 4 * D_PLANE;                      // cos hi | cos lo | sin hi | sin lo = 128 KB
-constexpr int D_APLANE = D_TM * 128;                      // one bf16 plane of an A stage: 128 frames x 64 k
-constexpr int D_STAGE = 2 * D_APLANE;                     // hi + lo
-constexpr int D_NSTAGE = 3;                               // A stages: fills E(g), O(g), E(g+1), ... go round the ring
-constexpr int D_SMEM = D_BASIS + D_NSTAGE * D_STAGE + 256 /*barriers*/ + 512 /*Nyquist weights*/ + 1024 /*align*/;
+constexpr int D_KB = 2 * 128 * 128;                       // one 64-sample K block of the basis: [hi 128 columns | lo 128 columns] x 128 B
+constexpr int D_BASIS = 4 * D_KB;                         // 128 KB per CTA type
+constexpr int D_APLANE = D_ROWS * 128;                    // 17408 B
+constexpr int D_STAGE = 2 * D_APLANE;                     // hi | lo = 34 KB
+constexpr int D_TASKS = D_ROWS * 8;                       // (row, 16-byte chunk of 8 samples) tasks per stage
+constexpr int D_SMEM = D_BASIS + 2 * D_STAGE + 256 /*barriers*/ + 1024 /*align*/;
 static_assert(D_SMEM <= 232448, "shared memory budget");
-static_assert(D_TASKS == 4, "producer mapping assumes 8 frames per warp");
+static_assert(D_STAGE % 1024 == 0, "stages must keep the 1024-byte swizzle pattern alignment");
 
-struct DftMeta {
-  long long s0, obase;   // first sample of the utterance in sig; first output element of the utterance
-  int N, T, t0;          // samples, frames of the utterance; first frame of the tile
+struct DftUtt {            // 32 bytes per utterance
+  long long sig_off;       // first sample in sig
+  long long out_off;       // first output element (frame_off[u] * 129)
+  long long nt;            // N_u | T_u << 32
+  long long row_off;       // first stream row (prefix sum of T_u + 3)
 };
-__device__ __forceinline__ DftMeta dft_meta(const longlong2* __restrict__ tiles, int tile) {
-  const longlong2 a = __ldg(tiles + 2 * (long long)tile), b = __ldg(tiles + 2 * (long long)tile + 1);
-  DftMeta m;
-  m.s0 = a.x;
-  m.obase = a.y;
-  m.N = (int)(b.x & 0xffffffffll);
-  m.T = (int)(b.x >> 32);
-  m.t0 = (int)b.y;
-  return m;
+__device__ __forceinline__ DftUtt dft_utt(const DftUtt* __restrict__ tab, int u) {
+  const longlong2 a = __ldg(reinterpret_cast<const longlong2*>(tab + u));
+  const longlong2 b = __ldg(reinterpret_cast<const longlong2*>(tab + u) + 1);
+  return DftUtt{a.x, a.y, b.x, b.y};
 }
 
 __device__ __forceinline__ float dft_sqrt(float x) {
@@ -71,41 +68,25 @@ __device__ __forceinline__ float dft_sqrt(float x) {
   return r;
 }
 __device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
-__device__ __forceinline__ void sts64(uint32_t addr, uint2 v) {
-  asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(addr), "r"(v.x), "r"(v.y) : "memory");
+__device__ __forceinline__ void sts128(uint32_t addr, uint4 v) {
+  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
 }
-// four floats -> packed bf16 hi (two words) and the bf16 of the residuals
-__device__ __forceinline__ void split4(const float* v, uint2& hi, uint2& lo) {
-  const __nv_bfloat162 h01 = __floats2bfloat162_rn(v[0], v[1]), h23 = __floats2bfloat162_rn(v[2], v[3]);
-  hi.x = *reinterpret_cast<const uint32_t*>(&h01);
-  hi.y = *reinterpret_cast<const uint32_t*>(&h23);
-  // bf16 -> f32 is a 16-bit shift: one instruction per element instead of extract + shift
-  const __nv_bfloat162 l01 = __floats2bfloat162_rn(v[0] - __uint_as_float(hi.x << 16), v[1] - __uint_as_float(hi.x & 0xffff0000u));
-  const __nv_bfloat162 l23 = __floats2bfloat162_rn(v[2] - __uint_as_float(hi.y << 16), v[3] - __uint_as_float(hi.y & 0xffff0000u));
-  lo.x = *reinterpret_cast<const uint32_t*>(&l01);
-  lo.y = *reinterpret_cast<const uint32_t*>(&l23);
-}
-// two 16-column TMEM loads, one wait
-__device__ __forceinline__ void tmem_ld16x2(uint32_t a0, uint32_t a1, float* v0, float* v1) {
-  uint32_t r[32];
-  asm volatile(
-      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%32];\n\t"
-      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%33];\n\t"
-      "tcgen05.wait::ld.sync.aligned;"
-      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
-        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
-        "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
-        "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
-      : "r"(a0), "r"(a1)
-      : "memory");
+// eight floats -> packed bf16 hi (four words) and the bf16 of the residuals
+__device__ __forceinline__ void split8(const float* v, uint4& hi, uint4& lo) {
+  uint32_t h[4], l[4];
 #pragma unroll
-  for (int i = 0; i < 16; ++i) {
-    v0[i] = __uint_as_float(r[i]);
-    v1[i] = __uint_as_float(r[16 + i]);
+  for (int i = 0; i < 4; ++i) {
+    const __nv_bfloat162 hh = __floats2bfloat162_rn(v[2 * i], v[2 * i + 1]);
+    h[i] = *reinterpret_cast<const uint32_t*>(&hh);
+    // bf16 -> f32 is a 16-bit shift
+    const __nv_bfloat162 ll = __floats2bfloat162_rn(v[2 * i] - __uint_as_float(h[i] << 16),
+                                                    v[2 * i + 1] - __uint_as_float(h[i] & 0xffff0000u));
+    l[i] = *reinterpret_cast<const uint32_t*>(&ll);
   }
+  hi = make_uint4(h[0], h[1], h[2], h[3]);
+  lo = make_uint4(l[0], l[1], l[2], l[3]);
 }
-
-// the same loads without the wait, and a wait that the 32 result registers depend on (software pipelining)
+// the same loads without the wait, and a wait that the result registers depend on (software pipelining)
 __device__ __forceinline__ void tmem_ld16x2_issue(uint32_t a0, uint32_t a1, uint32_t* r) {
   asm volatile(
       "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%32];\n\t"
@@ -126,60 +107,58 @@ __device__ __forceinline__ void tmem_ld_wait(uint32_t* r) {
                :
                : "memory");
 }
+__device__ __forceinline__ void mbar_wait_backoff(uint64_t* bar, uint32_t parity) {
+  while (!mbar_try_wait(bar, parity)) __nanosleep(32);
+}
 
-// Basis image in the exact shared-memory layout the MMA descriptors read (K-major rows of 128 B, 16-byte chunks
-// XOR-swizzled with row%8, 8-row atoms 1024 B apart): plane = [K block 0: 128 bins][K block 1: 128 bins].
-// Rows are bins 0..127 (the sin row of bin 0 is all zero); the Nyquist bin is summed by the producers.
+// Basis image in the exact shared-memory layout the MMA descriptors read: [type h][K block kc][plane][column][64 k],
+// rows of 128 B, 16-byte chunks XOR-swizzled with row % 8, 8-row atoms 1024 B apart (the lo plane directly behind the hi
+// plane, so that one N = 256 descriptor covers both).
+// Column c of type h: bin k = 64 h + (c & 63); c < 64: w[n] cos(2 pi k n / 256), c >= 64: -w[n] sin(2 pi k n / 256),
+// except column 64 of type 0 (Im X[0] = 0): the Nyquist bin, (-1)^n w[n].
 __global__ void dft256_basis_kernel(unsigned char* __restrict__ img) {
-  const int e = blockIdx.x * blockDim.x + threadIdx.x;
-  if (e >= 2 * 2 * 128 * 64) return;
-  const bool is_sin = e >= 2 * 128 * 64;
-  const int q = e & (2 * 128 * 64 - 1);
-  const int kb = q >> 13, r = (q >> 6) & 127, kk = q & 63;
-  const int n = kb * 64 + kk + 1;                                       // sample index 1..128
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;          // (h, kc, c, kk)
+  if (e >= 2 * 4 * 128 * 64) return;
+  const int kk = e & 63, c = (e >> 6) & 127, kc = (e >> 13) & 3, h = e >> 15;
+  const int n = kc * 64 + kk;                                           // sample index within the frame
   const double w = 0.5 - 0.5 * cospi((double)n / 128.0);               // periodic Hann, n_fft = 256
-  const int m = (r * n) & 255;                                          // angle 2 pi m / 256
-  const double v = is_sin ? -w * sinpi((double)m / 128.0) : w * cospi((double)m / 128.0);
+  const int k = 64 * h + (c & 63);
+  const int m = (k * n) & 255;                                          // angle 2 pi m / 256
+  double v = c >= 64 ? -w * sinpi((double)m / 128.0) : w * cospi((double)m / 128.0);
+  if (h == 0 && c == 64) v = (n & 1) ? -w : w;
   const __nv_bfloat16 hi = __float2bfloat16_rn((float)v);
   const __nv_bfloat16 lo = __float2bfloat16_rn((float)(v - (double)__bfloat162float(hi)));
-  const int off = kb * D_KB + r * 128 + ((((kk >> 3) ^ (r & 7))) << 4) + (kk & 7) * 2;
-  unsigned char* base = img + (is_sin ? 2 * D_PLANE : 0);
+  const int off = kc * D_KB + c * 128 + ((((kk >> 3) ^ (c & 7))) << 4) + (kk & 7) * 2;
+  unsigned char* base = img + (size_t)h * D_BASIS;
   *reinterpret_cast<__nv_bfloat16*>(base + off) = hi;
-  *reinterpret_cast<__nv_bfloat16*>(base + D_PLANE + off) = lo;
+  *reinterpret_cast<__nv_bfloat16*>(base + D_KB / 2 + off) = lo;
 }
 
-// waits of the many-warp roles back off so their polling does not take issue slots from the working warps
-__device__ __forceinline__ void mbar_wait_backoff(uint64_t* bar, uint32_t parity) {
-#ifdef SSB_DFT_NOSLEEP
-  while (!mbar_try_wait(bar, parity)) {
-  }
-#else
-  while (!mbar_try_wait(bar, parity)) __nanosleep(32);
-#endif
-}
-
+// Swizzle phase of the row-shifted A descriptors: the tensor core XORs the 16-byte chunk index with bits [7,10) of the
+// ABSOLUTE shared-memory address, which is also how the producers place the chunks (the stages are 1024-byte aligned), so
+// a start address advanced by kc * 128 B needs nothing else; the descriptor's matrix-base-offset field stays 0 (measured:
+// setting it to (start >> 7) & 7 reads the wrong chunks -- errors of order 1, profiles/r02_summary.md).
 __global__ void __launch_bounds__(D_THREADS, 1)
-stft_dft256_kernel(const float* __restrict__ sig, const longlong2* __restrict__ tiles, int n_tiles,
-                   const unsigned char* __restrict__ basis, float* __restrict__ out) {
+stft_dft256_kernel(const float* __restrict__ sig, const DftUtt* __restrict__ utts, int n_utts,
+                   const int* __restrict__ tile_u0, int n_tiles, long long total_rows,
+                   const unsigned char* __restrict__ basis, float* __restrict__ out, int log_out, int exp) {
   extern __shared__ unsigned char smem_raw[];
   unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   unsigned char* stages = smem + D_BASIS;
-  uint64_t* full = reinterpret_cast<uint64_t*>(smem + D_BASIS + D_NSTAGE * D_STAGE);
-  uint64_t* empty = full + D_NSTAGE;
-  uint64_t* tfull = empty + D_NSTAGE;
+  uint64_t* full = reinterpret_cast<uint64_t*>(stages + 2 * D_STAGE);
+  uint64_t* empty = full + 2;
+  uint64_t* tfull = empty + 2;
   uint64_t* tempty = tfull + 2;
   uint64_t* basis_bar = tempty + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(basis_bar + 1);
-  float* nyq_w = reinterpret_cast<float*>(smem + D_BASIS + D_NSTAGE * D_STAGE + 256);   // (-1)^n w[n], n = 1..128
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int h = blockIdx.x & 1, pair = blockIdx.x >> 1, n_pairs = gridDim.x >> 1;
 
   if (threadIdx.x == 0) {
-    for (int s = 0; s < D_NSTAGE; ++s) {
+    for (int s = 0; s < 2; ++s) {
       mbar_init(&full[s], D_PROD_WARPS);
       mbar_init(&empty[s], 1);
-    }
-    for (int s = 0; s < 2; ++s) {
       mbar_init(&tfull[s], 1);
       mbar_init(&tempty[s], D_EPI_WARPS);
     }
@@ -187,11 +166,6 @@ stft_dft256_kernel(const float* __restrict__ sig, const longlong2* __restrict__ 
     fence_barrier_init();
   }
   if (warp == D_PROD_WARPS) tmem_alloc<512>(tmem_slot);
-  if (threadIdx.x < 128) {
-    const int n = threadIdx.x + 1;
-    const float w = 0.5f - 0.5f * cospif((float)n * (1.0f / 128.0f));
-    nyq_w[threadIdx.x] = (n & 1) ? -w : w;
-  }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -199,243 +173,177 @@ stft_dft256_kernel(const float* __restrict__ sig, const longlong2* __restrict__ 
 
   if (warp < D_PROD_WARPS) {
     // ------------------------------------------------------------------ producers
-    const int half = lane >> 4, jq = lane & 15;
-    const int rbase = warp * (2 * D_TASKS) + half;                      // frame of task i: rbase + 2 i
-    float4 LA[D_TASKS], LB[D_TASKS];
-    float EX[D_TASKS], NY[D_TASKS];
-    uint2 OH[D_TASKS], OL[D_TASKS];
-    uint32_t offs[D_TASKS];                                            // byte offset of this lane's 8 bytes in a plane
-#pragma unroll
-    for (int i = 0; i < D_TASKS; ++i) {
-      const int r = rbase + 2 * i;
-      offs[i] = (uint32_t)(r * 128 + ((((jq >> 1) ^ (r & 7))) << 4) + ((jq & 1) << 3));
-    }
-    const uint32_t st_base = smem_u32(stages), nyq_s = smem_u32(nyq_w);
-    int fb = 0;                                                        // ring slot of the next fill
-    uint32_t fph = 0;                                                  // its use parity
-    bool wfast = false;
+    const int tid = threadIdx.x;                                       // 0 .. 32 * D_PROD_WARPS - 1
+    const int c = tid & 7;                                             // 16-byte chunk (8 samples) of the row, fixed
+    const uint32_t st_base = smem_u32(stages);
+    constexpr int NP = D_PROD_WARPS * 32;
+    constexpr int NT = (D_TASKS + NP - 1) / NP;                        // tasks per thread (the last one partial)
+    static_assert(NP % 8 == 0 && (D_TASKS % 32) == 0, "chunk index fixed per thread, task predicate warp-uniform");
 
-    // loads of one K block (samples nb+1 .. nb+64 and their mirrors) for this thread's four frames
-    auto issue = [&](const DftMeta& m, int kb) {
-      if (SSB_DFT_EXP & 2) return;
-      const int nb = kb * 64;
-      const int tf = m.t0 + warp * (2 * D_TASKS);                       // first of the warp's 8 frames
-      const float* ub = sig + m.s0;
-      wfast = tf >= 2 && (tf + 2 * D_TASKS - 1) * 64 + 128 <= m.N && (reinterpret_cast<uintptr_t>(ub) & 15) == 0;
-      if (wfast) {
-        const float* pa = ub + ((m.t0 + rbase) * 64 - 128 + 4 * jq);   // x[4 jq] of task 0's frame
-        const float* pb = pa + (252 - 8 * jq);                         // x[252 - 4 jq]
+    // all of this thread's loads of one tile, issued together (rows ascend with the task index)
+    auto load_tile = [&](int tile, float (&x)[NT][8]) {
+      int u = __ldg(tile_u0 + tile);
+      DftUtt U = dft_utt(utts, u);
+      long long next_off = u + 1 < n_utts ? __ldg(&utts[u + 1].row_off) : total_rows;
+      const long long R0 = (long long)tile * D_TM;
 #pragma unroll
-        for (int i = 0; i < D_TASKS; ++i) {
-          LA[i] = __ldg(reinterpret_cast<const float4*>(pa + nb + 128 * i));
-          LB[i] = __ldg(reinterpret_cast<const float4*>(pb - nb + 128 * i));
-        }
-        if (kb == 0 && lane == 31) {
-#pragma unroll
-          for (int i = 0; i < D_TASKS; ++i) EX[i] = __ldg(pa + 4 + 128 * i);   // x[64]
-        }
-      } else {
-        // reflect padding (np.pad(y, n_fft//2, 'reflect')), unaligned utterances, frames past the end
-#pragma unroll
-        for (int i = 0; i < D_TASKS; ++i) {
-          const int t = m.t0 + rbase + 2 * i, start = t * 64 - 128;
-          const bool valid = t < m.T;
-          float xa[4], xb[4];
-#pragma unroll
-          for (int q = 0; q < 4; ++q) {
-            const int n = nb + 4 * jq + 1 + q;
-            int ia = start + n, ib = start + 256 - n;
-            ia = ia < 0 ? -ia : ia;
-            ib = ib < 0 ? -ib : ib;
-            ia = ia >= m.N ? 2 * m.N - 2 - ia : ia;
-            ib = ib >= m.N ? 2 * m.N - 2 - ib : ib;
-            xa[q] = valid ? __ldg(ub + ia) : 0.0f;
-            xb[q] = valid ? __ldg(ub + ib) : 0.0f;
+      for (int it = 0; it < NT; ++it) {
+        const int task = tid + it * NP;
+        const long long R = R0 + (task >> 3);
+        if (task < D_TASKS && R < total_rows && !(exp & 2)) {
+          while (R >= next_off) {
+            ++u;
+            U = dft_utt(utts, u);
+            next_off = u + 1 < n_utts ? __ldg(&utts[u + 1].row_off) : total_rows;
           }
-          LA[i] = make_float4(0.0f, xa[0], xa[1], xa[2]);
-          EX[i] = xa[3];
-          LB[i] = make_float4(xb[3], xb[2], xb[1], xb[0]);
+          const int N = (int)(U.nt & 0xffffffffll);
+          const int i0 = (int)(R - U.row_off) * 64 - 128 + 8 * c;      // first of the 8 samples, utterance-relative
+          const float* p = sig + U.sig_off;
+          if (i0 >= 0 && i0 + 8 <= N && ((reinterpret_cast<uintptr_t>(p + i0) & 15) == 0)) {
+            const float4 a = __ldg(reinterpret_cast<const float4*>(p + i0));
+            const float4 b = __ldg(reinterpret_cast<const float4*>(p + i0) + 1);
+            x[it][0] = a.x; x[it][1] = a.y; x[it][2] = a.z; x[it][3] = a.w;
+            x[it][4] = b.x; x[it][5] = b.y; x[it][6] = b.z; x[it][7] = b.w;
+          } else {
+            // reflect padding (np.pad(y, n_fft//2, 'reflect')), unaligned utterances
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              int jx = i0 + i;
+              jx = jx < 0 ? -jx : jx;
+              jx = jx >= N ? 2 * N - 2 - jx : jx;
+              jx = jx < 0 ? 0 : jx;                                    // (rows of the 3 dropped frames past a short utterance)
+              x[it][i] = __ldg(p + jx);
+            }
+          }
+        } else {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) x[it][i] = 0.0f;
         }
       }
     };
-
-    int tile = blockIdx.x;
-    DftMeta cur = {0, 0, 0, 0, 0}, nxt = cur, nn = cur;
-    if (tile < n_tiles) {
-      cur = dft_meta(tiles, tile);
-      issue(cur, 0);
-    }
-    if (tile + (int)gridDim.x < n_tiles) nxt = dft_meta(tiles, tile + gridDim.x);
-    int g = 0;                                                         // steps done: 2 per tile, one per K block
-    for (; tile < n_tiles; tile += gridDim.x) {
-      const int tile_n = tile + gridDim.x, tile_nn = tile_n + gridDim.x;
-      if (tile_nn < n_tiles) nn = dft_meta(tiles, tile_nn);            // consumed one iteration later
-      if (tile_n < n_tiles) {
-        // the next tile's samples (32 KB + halo) go to L2 now: one 128-byte line per producer thread
-        long long a = (long long)nxt.t0 * 64 - 128, b = a + (D_TM - 1) * 64 + 256;
-        a = a < 0 ? 0 : a;
-        b = b > nxt.N ? nxt.N : b;
-        const char* p0 = reinterpret_cast<const char*>(sig + nxt.s0 + a);
-        const long long off = (long long)threadIdx.x * 128;
-        if (off < (b - a) * 4) asm volatile("prefetch.global.L2 [%0];" ::"l"(p0 + off));
-      }
+    // split + swizzled stores of one tile into stage s, once the MMAs of the tile two back have read it
+    auto store_tile = [&](int lt, const float (&x)[NT][8]) {
+      const int s = lt & 1;
+      mbar_wait_backoff(&empty[s], ((lt >> 1) & 1) ^ 1);
+      const uint32_t sa = st_base + s * D_STAGE;
 #pragma unroll
-      for (int kb = 0; kb < 2; ++kb, ++g) {
-        float cn[4];
-        asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(cn[0]), "=f"(cn[1]), "=f"(cn[2]), "=f"(cn[3])
-                     : "r"(nyq_s + (uint32_t)(kb * 64 + 4 * jq) * 4u));
-        mbar_wait_backoff(&empty[fb], fph ^ 1);
-        const uint32_t st0 = st_base + fb * D_STAGE;
-#pragma unroll
-        for (int i = 0; i < ((SSB_DFT_EXP & 2) ? 0 : D_TASKS); ++i) {
-          float nx = __shfl_down_sync(0xffffffffu, LA[i].x, 1);
-          if (!wfast) nx = EX[i];
-          else if (lane == 31) nx = kb ? LB[i].x : EX[i];
-          const float xa[4] = {LA[i].y, LA[i].z, LA[i].w, nx};
-          const float xb[4] = {LB[i].w, LB[i].z, LB[i].y, LB[i].x};
-          float ev[4], ov[4];
-#pragma unroll
-          for (int q = 0; q < 4; ++q) {
-            ev[q] = xa[q] + xb[q];
-            ov[q] = xa[q] - xb[q];
-          }
-          if (kb == 1 && jq == 15) {                                   // n = 128 is its own mirror
-            ev[3] = xa[3];
-            ov[3] = 0.0f;
-          }
-          float ny = kb ? NY[i] : 0.0f;                                // Nyquist bin: sum (-1)^n w[n] e[n]
-#pragma unroll
-          for (int q = 0; q < 4; ++q) ny = fmaf(cn[q], ev[q], ny);
-          NY[i] = ny;
-          uint2 eh, el;
-          split4(ev, eh, el);
-          split4(ov, OH[i], OL[i]);
-          sts64(st0 + offs[i], eh);
-          sts64(st0 + D_APLANE + offs[i], el);
-        }
-        fence_proxy_async_smem();                                      // own stores -> async proxy, then one arrival
-        __syncwarp();                                                  // per warp (512 arrivals on one word serialise)
-        if (lane == 0) mbar_arrive(&full[fb]);
-        if (++fb == D_NSTAGE) { fb = 0; fph ^= 1; }
-        // loads of the next step fly while the odd part is stored
-        if (kb == 0) issue(cur, 1);
-        else if (tile_n < n_tiles) issue(nxt, 0);
-        mbar_wait_backoff(&empty[fb], fph ^ 1);
-        const uint32_t st1 = st_base + fb * D_STAGE;
-#pragma unroll
-        for (int i = 0; i < ((SSB_DFT_EXP & 2) ? 0 : D_TASKS); ++i) {
-          sts64(st1 + offs[i], OH[i]);
-          sts64(st1 + D_APLANE + offs[i], OL[i]);
-        }
-        fence_proxy_async_smem();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&full[fb]);
-        if (++fb == D_NSTAGE) { fb = 0; fph ^= 1; }
-      }
-      // Nyquist bin of the four frames: 16-lane sums, written by the first lane of each half warp
-      {
-        float* onq = out + cur.obase + 128ll * cur.T;
-#pragma unroll
-        for (int i = 0; i < D_TASKS; ++i) {
-          float v = NY[i];
-#pragma unroll
-          for (int o = 8; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-          const int t = cur.t0 + rbase + 2 * i;
-          if (jq == 0 && t < cur.T) onq[t] = fabsf(v);
+      for (int it = 0; it < NT; ++it) {
+        const int task = tid + it * NP;
+        if (task < D_TASKS && !(exp & 2)) {
+          const int m = task >> 3;
+          uint4 hi, lo;
+          split8(x[it], hi, lo);
+          const uint32_t off = (uint32_t)(m * 128 + ((c ^ (m & 7)) << 4));
+          sts128(sa + off, hi);
+          sts128(sa + D_APLANE + off, lo);
         }
       }
-      cur = nxt;
-      nxt = nn;
+      fence_proxy_async_smem();                                        // own stores -> async proxy, then one arrival
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&full[s]);
+    };
+    float xa[NT][8], xb[NT][8];
+    int lt = 0, tile = pair;
+    if (tile < n_tiles) load_tile(tile, xa);
+    while (tile < n_tiles) {                                           // two tiles per trip: the register sets alternate
+      int nxt = tile + n_pairs;
+      if (nxt < n_tiles) load_tile(nxt, xb);
+      store_tile(lt++, xa);
+      tile = nxt;
+      if (tile >= n_tiles) break;
+      nxt = tile + n_pairs;
+      if (nxt < n_tiles) load_tile(nxt, xa);
+      store_tile(lt++, xb);
+      tile = nxt;
     }
   } else if (warp == D_PROD_WARPS) {
     // ------------------------------------------------------------------ MMA issuer
     if (lane == 0) {
       mbar_arrive_expect_tx(basis_bar, D_BASIS);
       constexpr int CH = D_BASIS / 8;
-      for (int c = 0; c < 8; ++c) bulk_load(smem + c * CH, basis + c * CH, CH, basis_bar);
+      for (int i = 0; i < 8; ++i) bulk_load(smem + i * CH, basis + (size_t)h * D_BASIS + i * CH, CH, basis_bar);
       mbar_wait(basis_bar, 0);
-      constexpr uint32_t idesc = umma_idesc_bf16(128, 128);
-      const uint64_t dbase = umma_desc_sw128(smem_u32(smem));
-      const uint64_t abase = dbase + (D_BASIS >> 4);
-      int fb = 0, lt = 0;
-      uint32_t fph = 0;
-      for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++lt) {
-        const int buf = lt & 1;
-        mbar_wait(&tempty[buf], ((lt >> 1) & 1) ^ 1);                   // epilogue drained this pair of accumulators
+      constexpr uint32_t idesc256 = umma_idesc_bf16(128, 256), idesc128 = umma_idesc_bf16(128, 128);
+      const uint64_t bbase = umma_desc_sw128(smem_u32(smem));
+      int lt = 0;
+      for (int tile = pair; tile < n_tiles; tile += n_pairs, ++lt) {
+        const int s = lt & 1;
+        const uint32_t ph = (lt >> 1) & 1;
+        mbar_wait(&tempty[s], ph ^ 1);                                  // epilogue drained this accumulator
+        mbar_wait(&full[s], ph);
         tc_fence_after();
-        const uint32_t acc_c = tmem_base + buf * 256, acc_s = acc_c + 128;
+        const uint32_t acc = tmem_base + s * 256;
+        const uint64_t abase = umma_desc_sw128(smem_u32(stages + s * D_STAGE));
 #pragma unroll
-        for (int kb = 0; kb < 2; ++kb) {
-          const uint64_t ch = dbase + (uint32_t)((kb * D_KB) >> 4), cl = ch + (D_PLANE >> 4);
-          const uint64_t sh = ch + (2 * D_PLANE >> 4), sl = sh + (D_PLANE >> 4);
-          {
-            const uint64_t ah = abase + (uint32_t)(fb * (D_STAGE >> 4)), al = ah + (D_APLANE >> 4);
-            mbar_wait(&full[fb], fph);
-            tc_fence_after();
+        for (int kc = 0; kc < 4; ++kc) {
+          // K block kc of every frame = the sample rows shifted by kc: start address + kc * 128 B
+          const uint64_t ah = abase + (uint32_t)((kc * 128) >> 4), al = ah + (D_APLANE >> 4);
+          const uint64_t bb = bbase + (uint32_t)((kc * D_KB) >> 4);      // [B_hi ; B_lo] of this K block, 256 rows
 #pragma unroll
-            for (int k = 0; k < ((SSB_DFT_EXP & 1) ? 0 : 4); ++k) {     // small terms first
-              umma_bf16(acc_c, al + 2 * k, ch + 2 * k, idesc, (kb | k) ? 1u : 0u);
-              umma_bf16(acc_c, ah + 2 * k, cl + 2 * k, idesc, 1u);
-              umma_bf16(acc_c, ah + 2 * k, ch + 2 * k, idesc, 1u);
-            }
-            umma_commit(&empty[fb]);
-            if (++fb == D_NSTAGE) { fb = 0; fph ^= 1; }
-          }
-          {
-            const uint64_t ah = abase + (uint32_t)(fb * (D_STAGE >> 4)), al = ah + (D_APLANE >> 4);
-            mbar_wait(&full[fb], fph);
-            tc_fence_after();
-#pragma unroll
-            for (int k = 0; k < ((SSB_DFT_EXP & 1) ? 0 : 4); ++k) {
-              umma_bf16(acc_s, al + 2 * k, sh + 2 * k, idesc, (kb | k) ? 1u : 0u);
-              umma_bf16(acc_s, ah + 2 * k, sl + 2 * k, idesc, 1u);
-              umma_bf16(acc_s, ah + 2 * k, sh + 2 * k, idesc, 1u);
-            }
-            umma_commit(&empty[fb]);
-            if (++fb == D_NSTAGE) { fb = 0; fph ^= 1; }
+          for (int k = 0; k < 4; ++k) {                                  // 16 samples = 32 bytes inside the 128-byte row
+            if (exp & 1) break;
+            umma_bf16(acc, ah + 2 * k, bb + 2 * k, idesc256, (kc | k) ? 1u : 0u);         // x_hi . [B_hi ; B_lo]
+            umma_bf16(acc, al + 2 * k, bb + 2 * k, idesc128, 1u);                        // x_lo . B_hi
           }
         }
-        umma_commit(&tfull[buf]);
+        umma_commit(&empty[s]);
+        umma_commit(&tfull[s]);
       }
     }
   } else {
-    // ------------------------------------------------------------------ epilogue (bins 0..127)
-    const int q = warp & 3, h = (warp - (D_PROD_WARPS + 1)) >> 2;       // TMEM lane quarter; which share of the bins
-    constexpr int NCH = 8 / (D_EPI_WARPS / 4);                          // 16-bin chunks per warp
-    const int r = q * 32 + lane;
+    // ------------------------------------------------------------------ epilogue
+    const int q = warp & 3;                                             // TMEM lane quarter this warp may read
+    const int eh = (warp - (D_PROD_WARPS + 1)) >> 2;                    // which 32 of the CTA's 64 bins
+    const int r = q * 32 + lane;                                        // frame within the tile
     int lt = 0;
-    for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, ++lt) {
-      const DftMeta m = dft_meta(tiles, tile);
-      const int buf = lt & 1;
-      const int t = m.t0 + r;
-      const bool valid = t < m.T;
-      const uint32_t acc_c = tmem_base + ((uint32_t)(q * 32) << 16) + buf * 256 + h * (NCH * 16), acc_s = acc_c + 128;
-      const uint32_t T4 = (uint32_t)m.T * 4u;                             // byte stride between bins
-      char* o = reinterpret_cast<char*>(out + m.obase + t) + (unsigned long long)T4 * (uint32_t)(h * NCH * 16);
-      mbar_wait_backoff(&tfull[buf], (lt >> 1) & 1);
+    for (int tile = pair; tile < n_tiles; tile += n_pairs, ++lt) {
+      const int s = lt & 1;
+      const long long R = (long long)tile * D_TM + r;                   // stream frame
+      bool valid = false;
+      float* o = out;
+      uint32_t T4 = 0;
+      if (R < total_rows) {
+        int u = __ldg(tile_u0 + tile);
+        DftUtt U = dft_utt(utts, u);
+        while (u + 1 < n_utts && R >= __ldg(&utts[u + 1].row_off)) U = dft_utt(utts, ++u);
+        const int T = (int)(U.nt >> 32), t = (int)(R - U.row_off);
+        valid = t < T;                                                  // the last 3 stream frames of an utterance are dropped
+        o = out + U.out_off + t;
+        T4 = (uint32_t)T * 4u;                                          // byte stride between bins
+      }
+      char* ob = reinterpret_cast<char*>(o) + (unsigned long long)T4 * (uint32_t)(64 * h + 32 * eh);
+      mbar_wait_backoff(&tfull[s], (lt >> 1) & 1);
       tc_fence_after();
-      // chunk c+1 is in flight from TMEM while chunk c is squared, rooted and stored
+      // columns: [0,64) Re hi*hi+lo*hi, [64,128) Im ..., [128,192) Re hi*lo, [192,256) Im hi*lo
+      const uint32_t acc_re = tmem_base + ((uint32_t)(q * 32) << 16) + s * 256 + 32 * eh, acc_im = acc_re + 64;
       uint32_t ra[32], rb[32];
-      tmem_ld16x2_issue(acc_c, acc_s, ra);
-      tmem_ld_wait(ra);
 #pragma unroll
-      for (int c = 0; c < NCH; ++c) {
-        uint32_t* cur_r = (c & 1) ? rb : ra;
-        uint32_t* nxt_r = (c & 1) ? ra : rb;
-        if (c + 1 < NCH) tmem_ld16x2_issue(acc_c + (c + 1) * 16, acc_s + (c + 1) * 16, nxt_r);
-        if (valid && !((SSB_DFT_EXP & 4) && cur_r[0] != 123u)) {
+      for (int cch = 0; cch < 2; ++cch) {
+        tmem_ld16x2_issue(acc_re + cch * 16, acc_im + cch * 16, ra);
+        tmem_ld16x2_issue(acc_re + 128 + cch * 16, acc_im + 128 + cch * 16, rb);
+        tmem_ld_wait(ra);
+        tmem_ld_wait(rb);
+        if (valid && !(exp & 4)) {
 #pragma unroll
-          for (int i = 0; i < 16; ++i) {                                // one IMAD.WIDE.U32 per address
-            const float re = __uint_as_float(cur_r[i]), im = __uint_as_float(cur_r[16 + i]);
-            *reinterpret_cast<float*>(o + (unsigned long long)T4 * (uint32_t)i) = dft_sqrt(re * re + im * im);
+          for (int i = 0; i < 16; ++i) {
+            const float re = __uint_as_float(ra[i]) + __uint_as_float(rb[i]);
+            float im = __uint_as_float(ra[16 + i]) + __uint_as_float(rb[16 + i]);
+            const bool nyq_col = h == 0 && eh == 0 && cch == 0 && i == 0;     // that column holds the Nyquist bin, Im X[0] = 0
+            float v = dft_sqrt(re * re + (nyq_col ? 0.0f : im * im));
+            if (log_out) v = logf(fmaxf(v, 1e-8f));
+            *reinterpret_cast<float*>(ob + (unsigned long long)T4 * (uint32_t)i) = v;
+            if (nyq_col) {
+              float vn = fabsf(im);
+              if (log_out) vn = logf(fmaxf(vn, 1e-8f));
+              *reinterpret_cast<float*>(ob + (unsigned long long)T4 * 128u) = vn;          // bin 128
+            }
           }
         }
-        o += (unsigned long long)T4 * 16u;
-        if (c + 1 < NCH) tmem_ld_wait(nxt_r);
+        ob += (unsigned long long)T4 * 16u;
       }
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&tempty[buf]);
+      if (lane == 0) mbar_arrive(&tempty[s]);
     }
   }
   __syncthreads();
@@ -449,27 +357,29 @@ stft_dft256_kernel(const float* __restrict__ sig, const longlong2* __restrict__ 
 
 extern "C" int ss_stft_dft256_tile_frames(void) { return ssb::D_TM; }
 
-extern "C" int ss_stft_dft256(const float* sig, const long long* tiles, int n_tiles, float* out, void* stream) {
+extern "C" int ss_stft_dft256(const float* sig, const long long* utts, int n_utts, const int* tile_u0, int n_tiles,
+                              long long total_rows, float* out, int flags, void* stream) {
   using namespace ssb;
-  if (n_tiles <= 0) return 0;
-  SS_REQUIRE(sig && tiles && out, "ss_stft_dft256: null pointer");
-  SS_REQUIRE((reinterpret_cast<uintptr_t>(tiles) & 15) == 0, "ss_stft_dft256: tile table must be 16-byte aligned");
+  if (n_tiles <= 0 || n_utts <= 0) return 0;
+  SS_REQUIRE(sig && utts && tile_u0 && out, "ss_stft_dft256: null pointer");
+  SS_REQUIRE((reinterpret_cast<uintptr_t>(utts) & 15) == 0, "ss_stft_dft256: utterance table must be 16-byte aligned");
+  // (flag bits 8..10: timing experiments of tools/_diag_dft.py -- no MMAs / no producer work / no epilogue stores; wrong results)
+  SS_REQUIRE((flags & ~(SS_STFT_LOG | 0x700)) == 0, "ss_stft_dft256: magnitude (optionally log) in the (F, T) layout only");
   cudaStream_t st = (cudaStream_t)stream;
   static unsigned char* basis[64] = {nullptr};                          // per device, built on first use
-  static int n_sm[64] = {0};
   int dev = 0;
   cudaGetDevice(&dev);
   SS_REQUIRE(dev >= 0 && dev < 64, "ss_stft_dft256: device index %d", dev);
   if (!basis[dev]) {
-    SS_REQUIRE(cudaMalloc(&basis[dev], D_BASIS) == cudaSuccess, "ss_stft_dft256: cudaMalloc of the basis failed");
-    dft256_basis_kernel<<<cdiv(2 * 2 * 128 * 64, 256), 256, 0, st>>>(basis[dev]);
+    SS_REQUIRE(cudaMalloc(&basis[dev], 2 * D_BASIS) == cudaSuccess, "ss_stft_dft256: cudaMalloc of the basis failed");
+    dft256_basis_kernel<<<cdiv(2 * 4 * 128 * 64, 256), 256, 0, st>>>(basis[dev]);
     cudaFuncSetAttribute(stft_dft256_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, D_SMEM);
-    cudaDeviceGetAttribute(&n_sm[dev], cudaDevAttrMultiProcessorCount, dev);
     int rc = check_launch("ss_stft_dft256(basis)");
     if (rc) return rc;
   }
-  const int grid = n_tiles < n_sm[dev] ? n_tiles : n_sm[dev];
-  stft_dft256_kernel<<<grid, D_THREADS, D_SMEM, st>>>(sig, reinterpret_cast<const longlong2*>(tiles), n_tiles,
-                                                      basis[dev], out);
+  int grid = sm_count() & ~1;                                           // CTA pairs: type 0 / type 1 of the same tiles
+  if (grid > 2 * n_tiles) grid = 2 * n_tiles;
+  stft_dft256_kernel<<<grid, D_THREADS, D_SMEM, st>>>(sig, reinterpret_cast<const DftUtt*>(utts), n_utts, tile_u0, n_tiles,
+                                                      total_rows, basis[dev], out, (flags & SS_STFT_LOG) ? 1 : 0, (flags >> 8) & 7);
   return check_launch("ss_stft_dft256");
 }

@@ -58,16 +58,19 @@ class Ragged:
         self.d_istft_tiles = _i32(self.istft_tiles, device)
 
     def dft_tiles(self):
-        """Tile table of ss_stft_dft256 (include/ssb200.h): one row of four int64 per 128-frame tile."""
+        """Tables of ss_stft_dft256 (include/ssb200.h): the utterance table (four int64 per utterance: first sample,
+        first output element, N | T << 32, first stream row) and, per 128-frame tile of the row stream, the utterance
+        its first row belongs to.  Utterance u owns T_u + 3 stream rows of 64 samples (its reflect-padded signal)."""
         if self._dft_tiles is None:
             tf = lib().ss_stft_dft256_tile_frames()
-            nt = (self.T + tf - 1) // tf
-            u = np.repeat(np.arange(self.n_utts), nt)
-            first = np.concatenate([[0], np.cumsum(nt)])[:-1]
-            t0 = (np.arange(int(nt.sum())) - np.repeat(first, nt)) * tf
-            tab = np.stack([self.sig_off[:-1][u], self.frame_off[:-1][u] * self.F,
-                            self.n_samples[u] | (self.T[u] << 32), t0], axis=1).astype(np.int64)
-            self._dft_tiles = torch.as_tensor(np.ascontiguousarray(tab), device=self.device)
+            row_off = np.concatenate([[0], np.cumsum(self.T + 3)]).astype(np.int64)
+            total = int(row_off[-1])
+            n_tiles = (total + tf - 1) // tf
+            u0 = (np.searchsorted(row_off, np.arange(n_tiles, dtype=np.int64) * tf, side="right") - 1).astype(np.int32)
+            tab = np.stack([self.sig_off[:-1], self.frame_off[:-1] * self.F, self.n_samples | (self.T << 32), row_off[:-1]],
+                           axis=1).astype(np.int64)
+            self._dft_tiles = (torch.as_tensor(np.ascontiguousarray(tab), device=self.device),
+                               torch.as_tensor(u0, device=self.device), n_tiles, total)
         return self._dft_tiles
 
     @property
@@ -80,8 +83,9 @@ class Ragged:
 
 
 STFT_COMPLEX, STFT_TF, STFT_LOG = 1, 2, 4
-# 256/64 magnitude features on the tensor cores (csrc/stft_mma.cu) instead of the FFT kernel.  Parity-green, but
-# measured slower on configs[1] (16.4 vs 13.4 ms, profiles/r01_summary.md section K), so it is opt-in.
+# 256/64 magnitude features on the tensor cores (csrc/stft_mma.cu) instead of the FFT kernel.  Parity-green (2e-6 against
+# the oracle) but slower on configs[1]: 17.1 vs 13.3 ms (its MMAs alone take 11.1 ms, profiles/r02_summary.md section E),
+# so it is opt-in.
 STFT_DFT256 = os.environ.get("SSB_STFT_DFT256", "0") == "1"
 ISTFT_TF, ISTFT_F32 = 1, 2
 
@@ -95,9 +99,9 @@ def stft(sig, rag, complex_out=False, layout_tf=False, log=False, out=None):
     if out is None:
         out = torch.empty(n, dtype=torch.complex64 if complex_out else torch.float32, device=sig.device)
     flags = (STFT_COMPLEX if complex_out else 0) | (STFT_TF if layout_tf else 0) | (STFT_LOG if log else 0)
-    if flags == 0 and rag.n_fft == 256 and rag.hop == 64 and STFT_DFT256:
-        tiles = rag.dft_tiles()
-        call("stft_dft256", sig, tiles, int(tiles.shape[0]), out, stream_ptr())
+    if (flags & ~STFT_LOG) == 0 and rag.n_fft == 256 and rag.hop == 64 and STFT_DFT256:
+        tab, u0, n_tiles, total_rows = rag.dft_tiles()
+        call("stft_dft256", sig, tab, rag.n_utts, u0, n_tiles, LL(total_rows), out, flags, stream_ptr())
         return out
     if rag.align != 1:
         raise ValueError("an aligned Ragged layout is only read by the tensor-core 256/64 magnitude path (STFT_DFT256)")

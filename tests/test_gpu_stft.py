@@ -79,6 +79,26 @@ def test_stft_dft256_matches_oracle_and_fft_kernel(align, monkeypatch):
             assert mx2 <= 3e-5, (u, mx2)
 
 
+@pytest.mark.parametrize("n_fft,hop,dft", [(256, 64, True), (256, 64, False), (512, 128, False)])
+def test_stft_log_flag(n_fft, hop, dft, monkeypatch):
+    """SS_STFT_LOG (an extension; the reference stores plain magnitudes): log(max(|X|, 1e-8)) of the same features, on the
+    FFT kernel and on the tensor-core kernel."""
+    monkeypatch.setattr(ops, "STFT_DFT256", dft)
+    lens = [5000, 12345, n_fft // 2 + 1]
+    sigs = _corpus(5, lens)
+    rag = ops.Ragged(lens, n_fft, hop, DEV)
+    flat = torch.from_numpy(np.concatenate(sigs)).to(DEV)
+    mag = ops.stft(flat, rag)
+    lg = ops.stft(flat, rag, log=True)
+    want = torch.log(torch.clamp(mag, min=1e-8))
+    assert float((lg - want).abs().max()) <= 2e-5
+    for u, v in enumerate(ops.stft_views(lg, rag)):
+        mag_ref = so.stft_mag(sigs[u], n_fft, hop)
+        ref = np.log(np.maximum(mag_ref, 1e-8))
+        big = mag_ref > 0.05 * mag_ref.max()            # (an absolute error of 1e-5 * peak is a large RELATIVE error of a tiny bin)
+        assert np.abs(v.cpu().numpy() - ref)[big].max() <= 1e-3
+
+
 def test_stft_dft256_full_size_properties(monkeypatch):
     monkeypatch.setattr(ops, "STFT_DFT256", True)
     # BASELINE-sized shard: homogeneity |STFT(a x)| == a |STFT(x)|, agreement with the FFT kernel, and Parseval per

@@ -45,16 +45,17 @@ def test_ragged_offsets_and_dft_tile_table(lib):
         assert np.array_equal(rag.T, 1 + lens // 64)
         assert all(int(o) % align == 0 for o in rag.sig_off)
         assert all(int(rag.sig_off[u + 1] - rag.sig_off[u]) >= lens[u] for u in range(len(lens)))
-        tab = rag.dft_tiles().numpy()
-        # every frame of every utterance is covered exactly once by tiles of <= 128 frames of one utterance
-        seen = {u: np.zeros(int(rag.T[u]), dtype=int) for u in range(len(lens))}
-        by_s0 = {int(rag.sig_off[u]): u for u in range(len(lens))}
-        for s0, obase, nt, t0 in tab:
-            u = by_s0[int(s0)]
-            assert int(nt) & 0xffffffff == lens[u] and int(nt) >> 32 == rag.T[u]
-            assert int(obase) == int(rag.frame_off[u]) * 129 and t0 % 128 == 0
-            seen[u][t0:t0 + 128] += 1
-        assert all((v == 1).all() for v in seen.values())
+        tab, u0, n_tiles, total = rag.dft_tiles()
+        tab, u0 = tab.numpy(), u0.numpy()
+        # the row stream: utterance u owns T_u + 3 rows; every tile starts inside the utterance the table names
+        assert total == int((rag.T + 3).sum()) and n_tiles == -(-total // 128) and len(u0) == n_tiles
+        row_off = np.concatenate([[0], np.cumsum(rag.T + 3)])
+        assert np.array_equal(tab[:, 3], row_off[:-1])
+        for i in range(n_tiles):
+            assert row_off[u0[i]] <= i * 128 < row_off[u0[i] + 1]
+        for u in range(len(lens)):
+            assert int(tab[u, 0]) == int(rag.sig_off[u]) and int(tab[u, 1]) == int(rag.frame_off[u]) * 129
+            assert int(tab[u, 2]) & 0xffffffff == lens[u] and int(tab[u, 2]) >> 32 == rag.T[u]
     with pytest.raises(ValueError):
         ops.Ragged([128], 256, 64, "cpu")                  # reflect padding needs N > n_fft/2
 
