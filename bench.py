@@ -120,6 +120,8 @@ class CallMeter:
         self.launches = 0
         self.timing = False
         self.records = {}
+        import torch
+        self.main_stream = torch.cuda.current_stream().cuda_stream
         mods = [m for n, m in sys.modules.items() if n.startswith("ssb200") and hasattr(m, "call")]
         for m in mods:
             if getattr(m, "call") is self.orig:
@@ -135,14 +137,19 @@ class CallMeter:
         e0.record()
         r = self.orig(name, *a)
         e1.record()
-        self.records.setdefault(name, []).append((e0, e1))
+        main = torch.cuda.current_stream().cuda_stream == self.main_stream
+        self.records.setdefault(name, []).append((e0, e1, main))
         return r
 
     def summary(self, steps):
+        """per C-ABI entry: time per step over all streams, and the part launched on the main stream (the critical path;
+        the rest runs on the side stream under a recurrence)"""
         out = {}
         for k, v in self.records.items():
-            ms = [a.elapsed_time(b) for a, b in v]
-            out[k] = {"calls_per_step": len(ms) / steps, "ms_per_step": sum(ms) / steps, "ms_per_call": sum(ms) / len(ms)}
+            ms = [a.elapsed_time(b) for a, b, _ in v]
+            ms_main = [a.elapsed_time(b) for a, b, m in v if m]
+            out[k] = {"calls_per_step": len(ms) / steps, "ms_per_step": sum(ms) / steps, "ms_per_call": sum(ms) / len(ms),
+                      "ms_main_per_step": sum(ms_main) / steps}
         return out
 
 
@@ -329,12 +336,23 @@ def run_train(args, rank, local, world, which="train", detail=True):
     h2d = int(np.mean([_batch_bytes(b) for b in host]))
     sink = {}
 
+    # strong scaling (--global-batch G): every rank runs G / (B * world) micro-batches per optimisation step with
+    # gradient accumulation, one exchange and one update per step
+    n_micro = max(1, getattr(args, "global_batch", 0) // (Bx * world)) if getattr(args, "global_batch", 0) else 1
+
     def step_dev(i):
-        sink["loss"], _ = trainer.step(dev[i % N_BATCHES])
+        if n_micro == 1:
+            sink["loss"], _ = trainer.step(dev[i % N_BATCHES])
+        else:
+            sink["loss"], _ = trainer.step_accumulate([dev[(i * n_micro + m) % N_BATCHES] for m in range(n_micro)])
 
     def step_e2e(i):
         # the user-facing loop: the copy of batch i+1 (pinned host memory) is started before step i is enqueued, so it
         # overlaps step i's kernels; every step still copies one full batch H2D and reads its loss back
+        if n_micro > 1:
+            loss, norm = trainer.step_accumulate([trainer.prefetch(host[(i * n_micro + m) % N_BATCHES]) for m in range(n_micro)])
+            sink["host_loss"] = (float(loss), float(norm))
+            return
         staged = sink.pop("staged", None)
         if staged is None or sink.get("staged_i") != i:
             staged = trainer.prefetch(host[i % N_BATCHES])
@@ -351,16 +369,17 @@ def run_train(args, rank, local, world, which="train", detail=True):
     meter.launches, replays0 = 0, wt.graph_replays
     ms, clocks = timed_region(step_dev, K, W, world, sampler)
     launches = (meter.launches + (wt.graph_replays - replays0) * wt.launches_per_refresh()) // (K + W) * K
-    tot_audio = sum(audio_s[(W + i) % N_BATCHES] for i in range(K))
+    tot_audio = sum(audio_s[((W + i) * n_micro + m) % N_BATCHES] for i in range(K) for m in range(n_micro))
     value = tot_audio / (ms / 1e3)
     ms_e2e, _ = timed_region(step_e2e, K, W, world)
     e2e = tot_audio / (ms_e2e / 1e3)
     line = {
         "metric": "uPIT train audio-sec/sec" if which == "train" else "%s train audio-sec/sec" % spec["arch"],
         "value": round(value, 1), "unit": "audio-sec/sec", "n_gpus": world,
-        "steps": K, "warmup": W, "ms_per_step": round(ms / K, 3), "higher_is_better": True, "scaling": "weak",
+        "steps": K, "warmup": W, "ms_per_step": round(ms / K, 3), "higher_is_better": True,
+        "scaling": "strong" if n_micro > 1 or getattr(args, "global_batch", 0) else "weak",
         "vs_baseline": None, "dtype": "split-bf16 operands (hi+lo), fp32 accumulate/state", "data": "synthetic",
-        "config": {"workload": spec["name"], "global_batch": Bx * world, "frames_per_step_per_gpu": int(np.mean(frames)),
+        "config": {"workload": spec["name"], "global_batch": Bx * world * n_micro, "micro_batches_per_step": n_micro, "frames_per_step_per_gpu": int(np.mean(frames)),
                    "parallelism": "dp%d" % world,
                    "dp_semantics": ("mode B: loss normaliser and BatchNorm statistics over all ranks, gradients summed"
                                     if trainer.exact else
@@ -390,9 +409,10 @@ def run_train(args, rank, local, world, which="train", detail=True):
     rl = {}
     for other in ("gemm_sb16_x2", "gemm_sb16_tn"):   # the batched / weight-gradient launches are the same kernel template
         if other in prof:
-            g, x = prof.setdefault("gemm_sb16", {"calls_per_step": 0, "ms_per_step": 0.0, "ms_per_call": 0.0}), prof.pop(other)
+            g, x = prof.setdefault("gemm_sb16", {"calls_per_step": 0, "ms_per_step": 0.0, "ms_per_call": 0.0, "ms_main_per_step": 0.0}), prof.pop(other)
             g["calls_per_step"] += x["calls_per_step"]
             g["ms_per_step"] += x["ms_per_step"]
+            g["ms_main_per_step"] = g.get("ms_main_per_step", 0.0) + x["ms_main_per_step"]
     # the recurrence flops split evenly between the forward and the backward kernel
     for name, fl in (("gemm_sb16", gemm_fl), ("lstm_fwd", rec_fl / 2), ("lstm_bwd", rec_fl / 2)):
         if name in prof:
@@ -416,7 +436,8 @@ def run_train(args, rank, local, world, which="train", detail=True):
             launches_per_step = prof[name]["calls_per_step"]
             lat[name] = {"us_per_time_step": round(prof[name]["ms_per_step"] * 1e3 / (launches_per_step * steps_per_launch), 3),
                          "time_steps_per_launch": steps_per_launch, "launches_per_train_step": launches_per_step,
-                         "ctas": 100 if name == "lstm_fwd" else (80 if Bx <= 64 else 76),
+                         "ctas": 100 if name == "lstm_fwd" else 80,
+                         "batch_per_launch": Bx if (name == "lstm_fwd" or Bx <= 64) else (Bx + 1) // 2,
                          "tensor_flops_per_time_step": 2 * 2 * 4 * H * H * Bx}
     divergence = grad_check = None
     if world > 1:
@@ -428,15 +449,16 @@ def run_train(args, rank, local, world, which="train", detail=True):
         dist.all_reduce(d, op=dist.ReduceOp.MAX)
         divergence = float(d)
         grad_check = trainer.grad_exchange_check(dev[0])
-    dom = max(prof, key=lambda k: prof[k]["ms_per_step"])
+    dom = max(prof, key=lambda k: prof[k]["ms_main_per_step"])        # dominant kernel of the critical path (main stream)
     roofline = dict(rl.get(dom, {"bound": "tensor", "achieved": None, "peak": tf_sus, "unit": "TFLOP/s", "frac": None}))
     tb, tsrc = traffic_of(dom)
     roofline.update({"kernel": dom, "traffic": tb, "traffic_source": tsrc, "peak_source": peak_src,
-                     "share_of_step": round(prof[dom]["ms_per_step"] / (ms / K), 3),
+                     "share_of_step": round(prof[dom]["ms_main_per_step"] / (ms / K), 3),
                      "note": "chain-latency bound kernel: see latency_model (us per time step), not the tensor fraction"})
     line.update({"roofline": roofline, "rooflines": rl, "latency_model": lat, "dp_param_divergence": divergence,
                  "dp_grad_check": grad_check,
                  "kernel_ms_per_step": {k: round(v["ms_per_step"], 3) for k, v in sorted(prof.items(), key=lambda kv: -kv[1]["ms_per_step"])},
+                 "kernel_ms_main_stream": {k: round(v["ms_main_per_step"], 3) for k, v in sorted(prof.items(), key=lambda kv: -kv[1]["ms_main_per_step"]) if v["ms_main_per_step"] > 0},
                  "kernel_ms_note": "CUDA events around each C-ABI call on its own stream; GEMM chunks streamed under the "
                                    "recurrences overlap them, so the sum exceeds ms_per_step"})
     return line
@@ -683,6 +705,8 @@ def main():
     ap.add_argument("--workload", default="train", choices=["train", "stft", "istft", "separate", "separate_long"] +
                     [k for k in WORKLOADS if k != "train"])
     ap.add_argument("--dp-exact", action="store_true", help="data-parallel mode B (N > 1): exact large-batch arithmetic")
+    ap.add_argument("--global-batch", type=int, default=0,
+                    help="strong scaling: fixed global batch (e.g. 512) run as micro-batches of 64 per rank with gradient accumulation")
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-extras", action="store_true", help="skip the stft/istft/cpu_baseline legs of the train line")
     args = ap.parse_args()
@@ -718,7 +742,7 @@ def main():
     else:
         line = run_train(args, rank, local, world)
         if not args.no_extras:
-            sub = argparse.Namespace(steps=max(3, min(args.steps, 5)), warmup=3, dp_exact=False)
+            sub = argparse.Namespace(steps=max(3, min(args.steps, 5)), warmup=3, dp_exact=False, global_batch=0)
             torch.cuda.empty_cache()
             line["stft"] = run_stft(sub, rank, local, world)
             torch.cuda.empty_cache()

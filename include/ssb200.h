@@ -32,13 +32,20 @@ int ss_device_check(void); /* >0: SM count of the current sm_100 device; <0: err
  * [frame_off[u], frame_off[u+1]) with T_u = 1 + N_u/hop, and CTA tiles [tile_off[u], tile_off[u+1]) with
  * ceil(T_u / ss_stft_tile_frames()) tiles.  Output block of utterance u starts at element frame_off[u]*F
  * (F = n_fft/2+1; float for magnitude, float2 for complex) and is (F, T_u) row-major -- the layout of the
- * reference's .npz arrays -- or (T_u, F) with SS_STFT_LAYOUT_TF.  N_u must exceed n_fft/2 (reflect padding). */
+ * reference's .npz arrays -- or (T_u, F) with SS_STFT_LAYOUT_TF.  N_u must exceed n_fft/2 (reflect padding).
+ * Any even n_fft and any hop <= n_fft (the reference passes --fft-dim / --step-size straight to librosa): n_fft 256 / 512
+ * with an even hop run the packed-FFT kernel, every other size a direct-summation kernel (correct, O(n_fft^2)). */
 #define SS_STFT_COMPLEX 1   /* keep complex64 (extract_feats.py test branch :98,105) instead of |X| (:87,89) */
 #define SS_STFT_LAYOUT_TF 2 /* (T,F) per utterance instead of the file layout (F,T) */
 #define SS_STFT_LOG 4       /* log(max(|X|,1e-8)); NOT reference behaviour, off for parity */
 int ss_stft_tile_frames(void);
 int ss_stft(const float* sig, const long long* sig_off, const long long* frame_off, const int* tile_off, int n_utts,
             int total_tiles, int n_fft, int hop, int flags, void* out, void* stream);
+
+/* Per-utterance, per-bin mean-variance normalisation of the (log-)magnitude blocks ss_stft wrote, in place:
+ * x <- (x - mean_t) / sqrt(var_t + eps) over the T_u frames of each (utterance, bin) row (biased variance).  An optional
+ * epilogue of K1 (north_star); the reference stores plain magnitudes, so it is off on every parity path. */
+int ss_cmvn(float* feat, const long long* frame_off, int n_utts, int F, int layout_tf, float eps, void* stream);
 
 /* K1 on the tensor cores (csrc/stft_mma.cu): the same magnitude STFT as ss_stft(n_fft = 256, hop = 64, flags = 0 or
  * SS_STFT_LOG), replacing librosa.core.stft + np.abs at steps/extract_feats.py:87,89, evaluated as a split-bf16 tcgen05
@@ -58,7 +65,8 @@ int ss_stft_dft256(const float* sig, const long long* utts, int n_utts, const in
  * spec: complex64 mixture STFT blocks as written by ss_stft(COMPLEX); mask: for utterance u, n_src blocks of
  * the same (F,T_u) shape starting at element (frame_off[u]*n_src)*F.  Output of (u, s) starts at
  * wav_off[u] + s*L_u, L_u = hop*(T_u-1) samples (int16, or float before the *32767 with SS_ISTFT_OUT_F32).
- * tile_off counts ceil(L_u / (ss_istft_tile_hops()*hop)) tiles per utterance. */
+ * tile_off counts ceil(L_u / (ss_istft_tile_hops()*hop)) tiles per utterance.  Any even n_fft = 2(F-1) and hop <= n_fft;
+ * the packed-FFT kernel covers n_fft 256 / 512 with an even hop >= n_fft/4, a direct-summation kernel the rest. */
 #define SS_ISTFT_LAYOUT_TF 1
 #define SS_ISTFT_OUT_F32 2
 int ss_istft_tile_hops(void);
@@ -122,8 +130,8 @@ int ss_colsum_sb16(const void* in, long long ld, long long plane, int R, int C, 
  * = chosen source per output slot; mode 1 (RSH.py:229-238): losses[n_src][B] with +inf for sources in the
  * bitmask used[B], idx = argmin, used updated.  stats[4] = {sum_b min/S, sum_b len_b*F, loss = [0]/[1], 1/(S*[1])},
  * accumulated over calls when accumulate != 0 (RSH.py:240-241).
- * bwd (gout NULL = 1): dz = (2*(m*x - src[assign])*x*stats[3]*gout[0] + dmask_extra) * m*(1-m), as sb16 [T*B][ld_dz] and
- * (dzT != NULL) transposed sb16 [n_out*F][ld_dzT]; rows with t >= len_b are zero. */
+ * bwd (gout NULL = 1): dz = (2*(m*x - src[assign])*x*stats[3]*gout[0] + dmask_extra) * m*(1-m), as sb16 [T*B][ld_dz];
+ * rows with t >= len_b are zero. */
 int ss_pit_chunks(int T);
 int ss_pit_loss_fwd(const float* z, long long ldz, const float* mix, const float* src, const int* lens, int T, int B,
                     int F, int n_out, int n_src, float* mask_out, float* partial, void* stream);
@@ -131,8 +139,7 @@ int ss_pit_select(const float* partial, int chunks, const int* lens, int B, int 
                   int accumulate, float* losses, int* idx, int* assign, int* used, float* stats, void* stream);
 int ss_pit_loss_bwd(const float* z, long long ldz, const float* mix, const float* src, const int* lens,
                     const int* assign, int T, int B, int F, int n_out, const float* stats, const float* gout,
-                    const float* dmask_extra, void* dz, long long ld_dz, long long dz_plane, void* dzT,
-                    long long ld_dzT, long long dzT_plane, void* stream);
+                    const float* dmask_extra, void* dz, long long ld_dz, long long dz_plane, void* stream);
 
 /* out[R][C] = sigmoid(z[R][ldz]) -- F.sigmoid of the head output (archs/uPIT.py:144) */
 int ss_sigmoid(const float* z, long long ldz, int R, int C, float* out, void* stream);
@@ -170,6 +177,10 @@ int ss_masks_to_ragged(const float* z, long long ldz, const long long* frame_off
  * bwd: dout [T*B][2H] gradient wrt out; whhT sb16 [2H][4H] (row dir*H+j, column 4u+gate);
  *      dG sb16 [T*B][8H] gate pre-activation gradients (zero at t>=len_b);
  *      dhn,dcn (optional) gradient wrt (hn,cn); dh0,dc0 (optional) gradient wrt (h0,c0).
+ *      batch_pitch (0 = B): the pointers may address a SUB-BATCH of a wider padded batch -- rows b0..b0+B of every frame,
+ *      every pointer advanced to its row / entry b0 by the caller, batch_pitch = rows per frame of the whole batch (and
+ *      entries per direction of c0 / dhn / dcn / dh0 / dc0).  Batch rows are independent chains, so a batch of
+ *      64 < B <= 128 is run as two halves through the K-split kernel (H = 600) instead of the slower generic one.
  * progress (optional, both): two counters, one per direction; while it runs the kernel stores
  *      progress[d] = prog_base + (number of steps of direction d whose out / dG rows are globally visible), every few
  *      steps (never the last ones: kernel completion covers those).  Direction 0 forward and direction 1 backward walk
@@ -183,18 +194,9 @@ int ss_lstm_fwd(float* gx, const void* whh_r, long long whh_ld, long long whh_pl
 int ss_lstm_bwd(const float* gates, const float* cs, const float* c0, const float* dout, const float* dhn,
                 const float* dcn, const int* lens, const void* whhT, long long whhT_ld, long long whhT_plane, void* dG,
                 long long dG_plane, float* dh0, float* dc0, void* ws, unsigned int* progress, unsigned int prog_base,
-                int T, int B, int H, void* stream);
+                int T, int B, int batch_pitch, int H, void* stream);
 /* Stream-ordered wait until (int)(*addr - value) >= 0 (cuStreamWaitValue32, GEQ): no SM is occupied while waiting. */
 int ss_stream_wait_value32(void* stream, unsigned int* addr, unsigned int value);
-/* Transposed sb16 copies (K = T*B contiguous) for the K-major form of the weight-gradient GEMMs; superseded by
- * ss_gemm_sb16_tn and kept only as the cross-check path of tests/test_gpu_gemm.py:
- * out[c][r] = in[r][c] for both planes; hprevT[d*H+j][t*B+b] = the state direction d carried INTO frame t of row b
- * (h0 at the row's first processed frame, zero at t >= len_b). */
-int ss_transpose_sb16(const void* in, long long ld, long long plane, int R, int C, void* out, long long ldT,
-                      long long planeT, void* stream);
-int ss_hprev_transpose(const void* out_sb, long long ld, long long plane, int T, int B, int H, const int* lens,
-                       const float* h0, void* hprevT, long long ldT, long long planeT, void* stream);
-
 /* ---- K3/K4 glue: BatchNorm1d(2H) over all T*B rows (padding included, archs/uPIT.py:119,138) folded into the
  * head Linear (archs/uPIT.py:117,141), and its backward ----
  * coef[5][C] = {s = gamma*rstd, shift = beta - mean*s, mean, rstd, biased var}; training updates the running

@@ -28,11 +28,12 @@ static inline int cdiv(long long a, long long b) { return (int)((a + b - 1) / b)
 int make_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t* dims,
                    const uint64_t* strides_bytes, const uint32_t* box);
 
-// transpose.cu: transposed sb16 copies made after the recurrence kernels (same stream)
-int launch_transpose_sb16(const void* in, long long ld, long long plane, int R, int C, void* out, long long ldT,
-                          long long planeT, cudaStream_t st);
-int launch_hprev_transpose(const void* out_sb, long long ld, long long plane, int T, int B, int H, const int* lens,
-                           const float* h0, void* hprevT, long long ldT, long long planeT, cudaStream_t st);
+// stft_generic.cu: direct-summation STFT / masked iSTFT for the sizes the packed-FFT kernels do not cover
+int launch_stft_generic(const float* sig, const long long* sig_off, const long long* frame_off, const int* tile_off,
+                        int n_utts, int total_tiles, int n_fft, int hop, int flags, float* out, cudaStream_t st);
+int launch_istft_generic(const void* spec, const float* mask, const long long* frame_off, const long long* wav_off,
+                         const int* tile_off, int n_utts, int n_src, int total_tiles, int tile_samples, int n_fft, int hop,
+                         int flags, void* out, cudaStream_t st);
 
 // ---- split-bf16 ("sb16"): x ~= hi + lo, each bf16; products use hi*hi + hi*lo + lo*hi ----
 __device__ __forceinline__ void split_bf16(float x, __nv_bfloat16& hi, __nv_bfloat16& lo) {

@@ -398,3 +398,47 @@ extern "C" int ss_dwhh_edge(const void* dG, long long ld, long long plane, const
       (const __nv_bfloat16*)dG, ld, plane, lens, h0, B, H, dW0, dW1, ldw);
   return check_launch("ss_dwhh_edge");
 }
+
+// ---- per-utterance mean-variance normalisation of (log-)magnitude features (north_star K1 epilogue option; the
+// reference stores plain magnitudes, SURVEY D2, so this is an extension that is off on every parity path):
+//   x[u][k][t] <- (x[u][k][t] - mean_t x[u][k][:]) / sqrt(var_t x[u][k][:] + eps)     (biased variance over the frames)
+// One warp per (utterance, bin) row; two passes over the row (the second hits L2).
+namespace ssb {
+__global__ void __launch_bounds__(256)
+cmvn_kernel(float* __restrict__ x, const long long* __restrict__ frame_off, int n_utts, int F, int layout_tf, float eps) {
+  const int lane = threadIdx.x & 31;
+  const long long n_rows = (long long)n_utts * F;
+  for (long long row = (long long)blockIdx.x * 8 + (threadIdx.x >> 5); row < n_rows; row += (long long)gridDim.x * 8) {
+    const int u = (int)(row / F), k = (int)(row - (long long)u * F);
+    const long long f0 = frame_off[u];
+    const int T = (int)(frame_off[u + 1] - f0);
+    float* base = x + f0 * F + (layout_tf ? k : (long long)k * T);
+    const long long st = layout_tf ? F : 1;
+    double s = 0.0, s2 = 0.0;
+    for (int t = lane; t < T; t += 32) {
+      const double v = base[t * st];
+      s += v;
+      s2 += v * v;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      s += __shfl_xor_sync(0xffffffffu, s, o);
+      s2 += __shfl_xor_sync(0xffffffffu, s2, o);
+    }
+    const double mean = s / T;
+    double var = s2 / T - mean * mean;
+    var = var < 0.0 ? 0.0 : var;
+    const float m = (float)mean, r = (float)(1.0 / sqrt(var + (double)eps));
+    for (int t = lane; t < T; t += 32) base[t * st] = (base[t * st] - m) * r;
+  }
+}
+}  // namespace ssb
+
+extern "C" int ss_cmvn(float* feat, const long long* frame_off, int n_utts, int F, int layout_tf, float eps, void* stream) {
+  using namespace ssb;
+  if (n_utts <= 0) return 0;
+  const long long rows = (long long)n_utts * F;
+  const int grid = (int)min((long long)sm_count() * 8, (rows + 7) / 8);
+  cmvn_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(feat, frame_off, n_utts, F, layout_tf, eps);
+  return check_launch("ss_cmvn");
+}

@@ -315,11 +315,13 @@ extern "C" int ss_istft_masked(const void* spec, const float* mask, const long l
                                const long long* wav_off, const int* tile_off, int n_utts, int n_src, int total_tiles,
                                int n_fft, int hop, int flags, void* out, void* stream) {
   using namespace ssb;
-  SS_REQUIRE(n_fft == 512 || n_fft == 256, "ss_istft_masked: n_fft must be 256 or 512 (got %d)", n_fft);
-  SS_REQUIRE(hop > 0 && hop % 2 == 0 && hop * 4 >= n_fft && hop <= n_fft, "ss_istft_masked: hop %d unsupported for n_fft %d",
-             hop, n_fft);
+  SS_REQUIRE(n_fft >= 4 && n_fft % 2 == 0, "ss_istft_masked: n_fft must be even (got %d)", n_fft);
+  SS_REQUIRE(hop > 0 && hop <= n_fft, "ss_istft_masked: bad hop %d for n_fft %d", hop, n_fft);
   if (total_tiles == 0 || n_src == 0) return 0;
   cudaStream_t st = (cudaStream_t)stream;
+  if ((n_fft != 512 && n_fft != 256) || hop % 2 != 0 || hop * 4 < n_fft)   // sizes the packed-FFT kernel does not cover
+    return launch_istft_generic(spec, mask, frame_off, wav_off, tile_off, n_utts, n_src, total_tiles,
+                                ss_istft_tile_hops() * hop, n_fft, hop, flags, out, st);
   const float2* sp = (const float2*)spec;
   const bool tf = flags & SS_ISTFT_LAYOUT_TF, f32 = flags & SS_ISTFT_OUT_F32;
 #define SS_GO(NF, A, B) return launch_istft<NF, A, B>(sp, mask, frame_off, wav_off, tile_off, n_utts, n_src, total_tiles, hop, out, st)

@@ -5,7 +5,7 @@
 //   dh_rec[b][j] = sum_n dG_prev[b][n] * W_hh[n][j]            (tcgen05, K = 4H)
 // with dG_prev (the gate pre-activation gradients of the previously processed frame) streamed by TMA straight
 // from the dG matrix all CTAs of the direction write; then the cell backward for its units, producing dG[t].
-// dG is written as sb16 [T*B][8H] (operand of the dX GEMM) and transposed [8H][T*B] (operand of the dW GEMMs).
+// dG is written as sb16 [T*B][8H]: the K-major operand of the dX GEMM and the MN-major operand of the dW GEMMs.
 #include <stdlib.h>
 
 #include "../../include/ssb200.h"
@@ -241,16 +241,20 @@ lstm_bwd_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
 extern "C" int ss_lstm_bwd(const float* gates, const float* cs, const float* c0, const float* dout, const float* dhn,
                            const float* dcn, const int* lens, const void* whhT, long long whhT_ld,
                            long long whhT_plane, void* dG, long long dG_plane, float* dh0, float* dc0, void* ws,
-                           unsigned int* progress, unsigned int prog_base, int T, int B, int H, void* stream) {
+                           unsigned int* progress, unsigned int prog_base, int T, int B, int batch_pitch, int H,
+                           void* stream) {
   using namespace ssb;
   SS_REQUIRE(T > 0 && B > 0 && B <= 128, "ss_lstm_bwd: need 1 <= B <= 128 (got %d) and T > 0", B);
+  if (batch_pitch <= 0) batch_pitch = B;
+  SS_REQUIRE(batch_pitch >= B, "ss_lstm_bwd: batch_pitch %d < B %d", batch_pitch, B);
+  SS_REQUIRE(batch_pitch == B || (H == 600 && B <= 64), "ss_lstm_bwd: a sub-batch view (batch_pitch != B) needs H = 600, B <= 64");
   SS_REQUIRE(H % 8 == 0 && 4 * H <= 64 * LB_MAXKC, "ss_lstm_bwd: unsupported hidden size %d", H);
   cudaStream_t st = (cudaStream_t)stream;
   LstmBwdParams p;
   p.gates = gates; p.cs = cs; p.c0 = c0; p.dout = dout; p.dhn = dhn; p.dcn = dcn; p.lens = lens;
   p.dG = (__nv_bfloat16*)dG; p.dG_plane = dG_plane;
   p.dh0 = dh0; p.dc0 = dc0;
-  p.T = T; p.B = B; p.H = H;
+  p.T = T; p.B = B; p.H = H; p.Bp = batch_pitch;
   p.R = B <= 64 ? 64 : 128;
   p.NC = cdiv(H, LB_U);
   p.KC = cdiv(4 * H, 64);

@@ -20,6 +20,7 @@ struct LstmBwdParams {
   unsigned int* progress;    // [2] or null: prog_base + number of steps whose dG rows are globally visible, per direction
   unsigned int prog_base;
   int T, B, H, R, NC, KC, NS, want_d0, ROT;
+  int Bp;                    // rows per frame of the padded batch the pointers walk (K-split kernel; >= B)
   long long* dbg;            // optional clock64 trace of CTA 0: [step][32]
 };
 

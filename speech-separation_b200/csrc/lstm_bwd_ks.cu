@@ -101,7 +101,7 @@ lstm_bwd_ks_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
   const int rank = (int)cluster_rank();
   const int cl = blockIdx.x / KS_CL;
   const int dir = cl / KS_NCL, c = cl % KS_NCL;
-  const int T = p.T, B = p.B;
+  const int T = p.T, B = p.B, Bp = p.Bp;                       // Bp: rows per frame of the padded batch (>= B)
   constexpr int H = KS_H;
   const int nsteps = T + (p.want_d0 ? 1 : 0);
   const int ch0 = ks_chunk_begin(rank), nch = rank < 2 ? 10 : 9;
@@ -145,7 +145,7 @@ lstm_bwd_ks_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
             mbar_wait(&empty[st], ((phase >> st) & 1) ^ 1);
             phase ^= 1u << st;
             mbar_arrive_expect_tx(&full[st], KS_CHUNK);
-            tma_load_3d(ring + st * KS_CHUNK, &tmG, &full[st], dir * 4 * H + (ch0 + i) * 64, 0, tp * B);
+            tma_load_3d(ring + st * KS_CHUNK, &tmG, &full[st], dir * 4 * H + (ch0 + i) * 64, 0, tp * Bp);
           }
         }
         // progress for stream-ordered consumers (ss_stream_wait_value32): the counter just observed covers the dG rows of
@@ -201,13 +201,13 @@ lstm_bwd_ks_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
     float dc[2] = {0.0f, 0.0f};
     float dh0[2] = {0.0f, 0.0f};
     // running pointers of this thread's (row, unit pair): one add per step instead of 64-bit multiplies
-    const long long rstep = dir ? (long long)B : -(long long)B;           // rows per step in processing order
-    const long long row0 = (long long)(dir ? 0 : T - 1) * B + (row_ok ? fb : 0);
+    const long long rstep = dir ? (long long)Bp : -(long long)Bp;         // rows per step in processing order
+    const long long row0 = (long long)(dir ? 0 : T - 1) * Bp + (row_ok ? fb : 0);
     const float* gptr = p.gates + row0 * (8LL * H) + (long long)dir * 4 * H + 4 * ug;
     const float* cptr = p.cs + row0 * (2LL * H) + dir * H + ug;
     const float* dptr = p.dout + row0 * (2LL * H) + dir * H + ug;
     __nv_bfloat16* optr = p.dG + row0 * (8LL * H) + (long long)dir * 4 * H + 4 * ug;
-    const float* c0ptr = p.c0 + ((long long)dir * B + (row_ok ? fb : 0)) * H + ug;
+    const float* c0ptr = p.c0 + ((long long)dir * Bp + (row_ok ? fb : 0)) * H + ug;
     for (int s = 0; s < nsteps; ++s) {
       const int t = dir ? s : (T - 1 - s);                     // t == -1 / T on the extra step
       const bool in_range = s < T;
@@ -279,8 +279,8 @@ lstm_bwd_ks_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
           float dh = doa[j] + dhr[j];
           float dct = dc[j];
           if (first && p.dhn) {
-            dh += p.dhn[((long long)dir * B + fb) * H + ug + j];
-            dct += p.dcn[((long long)dir * B + fb) * H + ug + j];
+            dh += p.dhn[((long long)dir * Bp + fb) * H + ug + j];
+            dct += p.dcn[((long long)dir * Bp + fb) * H + ug + j];
           }
           const float gi = g4[j].x, gf = g4[j].y, gg = g4[j].z, go = g4[j].w;
           const float tc = tanhf_(cta_[j]);
@@ -317,8 +317,8 @@ lstm_bwd_ks_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
     if (row_ok && p.want_d0) {
 #pragma unroll
       for (int j = 0; j < 2; ++j) {
-        p.dh0[((long long)dir * B + fb) * H + ug + j] = dh0[j];
-        p.dc0[((long long)dir * B + fb) * H + ug + j] = dc[j];
+        p.dh0[((long long)dir * Bp + fb) * H + ug + j] = dh0[j];
+        p.dc0[((long long)dir * Bp + fb) * H + ug + j] = dc[j];
       }
     }
   }
@@ -341,7 +341,7 @@ int launch_lstm_bwd_ks(const LstmBwdParams& p, const void* whhT, long long whhT_
     if (rc) return rc;
   }
   {  // (columns, plane, row): a box lands in shared memory as rows 2*b + plane
-    uint64_t dims[3] = {(uint64_t)8 * H, 2, (uint64_t)p.T * p.B};
+    uint64_t dims[3] = {(uint64_t)8 * H, 2, (uint64_t)p.T * p.Bp - (uint64_t)(p.Bp - p.B)};   // rows of THIS sub-batch's view
     uint64_t str[2] = {(uint64_t)p.dG_plane * 2, (uint64_t)8 * H * 2};
     uint32_t box[3] = {64, 2, 64};
     int rc = make_tmap_bf16(&tmG, p.dG, 3, dims, str, box);

@@ -131,15 +131,13 @@ pit_select_kernel(const float* __restrict__ partial, int chunks, const int* __re
   }
 }
 
-// dz = [ 2*(m*x - s_assigned)*x * gout/(S*norm) + dmask_extra ] * m*(1-m), written as sb16 (rows t*B+b) and as its
-// transpose (rows = output column), both consumed by the head's backward GEMMs.
+// dz = [ 2*(m*x - s_assigned)*x * gout/(S*norm) + dmask_extra ] * m*(1-m), written as sb16 (rows t*B+b): the operand of
+// both head backward GEMMs (dY = dz W in the K-major form, dW = dz^T y in the MN-major form).
 __global__ void __launch_bounds__(256)
 pit_bwd_kernel(const float* __restrict__ z, long long ldz, const float* __restrict__ mix, const float* __restrict__ src,
                const int* __restrict__ lens, const int* __restrict__ assign, int T, int B, int F, int n_out,
                const float* __restrict__ stats, const float* __restrict__ gout, const float* __restrict__ dmask_extra,
-               __nv_bfloat16* __restrict__ dz, long long ld_dz, long long dz_plane, __nv_bfloat16* __restrict__ dzT,
-               long long ld_dzT, long long dzT_plane) {
-  __shared__ float tile[32][33];
+               __nv_bfloat16* __restrict__ dz, long long ld_dz, long long dz_plane) {
   const int c0 = blockIdx.x * 32, r0 = blockIdx.y * 32;
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
   const int R = T * B, C = n_out * F;
@@ -165,20 +163,6 @@ pit_bwd_kernel(const float* __restrict__ z, long long ldz, const float* __restri
       const long long o = (long long)r * ld_dz + c;
       dz[o] = hi;
       dz[o + dz_plane] = lo;
-    }
-    tile[ty + 8 * i][tx] = v;
-  }
-  if (!dzT) return;                                            // (block-uniform) only the transposed-copy form wants it
-  __syncthreads();
-#pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    const int c = c0 + ty + 8 * i, r = r0 + tx;
-    if (r < R && c < C) {
-      __nv_bfloat16 hi, lo;
-      split_bf16(tile[tx][ty + 8 * i], hi, lo);
-      const long long o = (long long)c * ld_dzT + r;
-      dzT[o] = hi;
-      dzT[o + dzT_plane] = lo;
     }
   }
 }
@@ -234,12 +218,11 @@ extern "C" int ss_pit_select(const float* partial, int chunks, const int* lens, 
 extern "C" int ss_pit_loss_bwd(const float* z, long long ldz, const float* mix, const float* src, const int* lens,
                                const int* assign, int T, int B, int F, int n_out, const float* stats,
                                const float* gout, const float* dmask_extra, void* dz, long long ld_dz,
-                               long long dz_plane, void* dzT, long long ld_dzT, long long dzT_plane, void* stream) {
+                               long long dz_plane, void* stream) {
   using namespace ssb;
   if (T == 0 || B == 0) return 0;
   dim3 grid(cdiv(n_out * F, 32), cdiv((long long)T * B, 32));
   pit_bwd_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(z, ldz, mix, src, lens, assign, T, B, F, n_out, stats, gout,
-                                                        dmask_extra, (__nv_bfloat16*)dz, ld_dz, dz_plane,
-                                                        (__nv_bfloat16*)dzT, ld_dzT, dzT_plane);
+                                                        dmask_extra, (__nv_bfloat16*)dz, ld_dz, dz_plane);
   return check_launch("ss_pit_loss_bwd");
 }

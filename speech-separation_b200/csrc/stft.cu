@@ -309,13 +309,15 @@ static int launch_stft(const float* sig, const long long* sig_off, const long lo
 extern "C" int ss_stft(const float* sig, const long long* sig_off, const long long* frame_off, const int* tile_off,
                        int n_utts, int total_tiles, int n_fft, int hop, int flags, void* out, void* stream) {
   using namespace ssb;
-  SS_REQUIRE(n_fft == 512 || n_fft == 256, "ss_stft: n_fft must be 256 or 512 (got %d)", n_fft);
-  SS_REQUIRE(hop > 0 && hop <= n_fft && hop % 2 == 0, "ss_stft: bad hop %d", hop);
+  SS_REQUIRE(n_fft >= 4 && n_fft % 2 == 0, "ss_stft: n_fft must be even (got %d)", n_fft);
+  SS_REQUIRE(hop > 0 && hop <= n_fft, "ss_stft: bad hop %d", hop);
   if (total_tiles == 0) return 0;
   cudaStream_t st = (cudaStream_t)stream;
   float* o = (float*)out;
   const bool cplx = flags & SS_STFT_COMPLEX, tf = flags & SS_STFT_LAYOUT_TF, lg = flags & SS_STFT_LOG;
   SS_REQUIRE(!(cplx && lg), "ss_stft: LOG applies to magnitude output only");
+  if ((n_fft != 512 && n_fft != 256) || hop % 2 != 0)       // any other even size / odd hop: direct-summation kernel
+    return launch_stft_generic(sig, sig_off, frame_off, tile_off, n_utts, total_tiles, n_fft, hop, flags, o, st);
 #define SS_GO(NF, C, T, L) return launch_stft<NF, C, T, L>(sig, sig_off, frame_off, tile_off, n_utts, total_tiles, hop, o, st)
 #define SS_DISPATCH(NF)                         \
   if (cplx) { if (tf) SS_GO(NF, true, true, false); else SS_GO(NF, true, false, false); } \

@@ -62,7 +62,8 @@ def plan(args, suffix):
     """-> list of (out_id, num_spk, [(key, path, offset, duration)])"""
     segs = {}
     seg_path = os.path.join(args.data_dir, "segments" + suffix)
-    if os.path.isfile(seg_path):
+    use_segs = os.path.isfile(seg_path)                        # steps/extract_feats.py:51-60
+    if use_segs:
         for line in open(seg_path):
             s = line.split()
             segs.setdefault(s[1], []).append((s[0], float(s[2]), float(s[3])))
@@ -75,8 +76,8 @@ def plan(args, suffix):
             keyed = [("mix" if i == 0 else "s%d" % i, f) for i, f in enumerate(files)]
         else:
             keyed = [("mix", filename)]
-        if segs:
-            for sid, t0, t1 in segs.get(reco, []):
+        if use_segs:
+            for sid, t0, t1 in segs[reco]:                     # KeyError for a recording without segments, like :71
                 items.append((sid, num_spk, [(k, f, t0, t1 - t0) for k, f in keyed]))
         else:
             items.append((reco, num_spk, [(k, f, None, None) for k, f in keyed]))

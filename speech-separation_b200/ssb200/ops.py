@@ -110,6 +110,13 @@ def stft(sig, rag, complex_out=False, layout_tf=False, log=False, out=None):
     return out
 
 
+def cmvn(feat, rag, layout_tf=False, eps=1e-8):
+    """In-place per-utterance mean-variance normalisation of (log-)magnitude features (an extension, see ss_cmvn)."""
+    assert feat.dtype == torch.float32 and feat.numel() == rag.total_frames * rag.F
+    call("cmvn", feat, rag.d_frame_off, rag.n_utts, rag.F, int(bool(layout_tf)), float(eps), stream_ptr())
+    return feat
+
+
 class _HostStream:
     """Cached plan of stft_host: utterance chunks, their sub-corpora and two device buffers of each kind."""
 

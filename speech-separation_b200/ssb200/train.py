@@ -224,15 +224,35 @@ class Trainer:
                 "exchange": "sum over ranks of flat buckets (l0 | l1 | head); scaled by %s in the clip kernel"
                             % ("1" if self.exact else "1/world")}
 
+    def step_accumulate(self, batches):
+        """One optimisation step over several micro-batches (gradient accumulation): every micro-batch runs forward and
+        backward with its own loss normaliser and BatchNorm statistics, the gradients add up in the flat bucket, the
+        exchange starts with the LAST micro-batch's buckets, and the mean over micro-batches (and ranks) is clipped and
+        applied once.  This is how a fixed global batch larger than 64 x world is run (strong scaling, bench.py
+        --global-batch).  uPIT arch.  Returns the last micro-batch's (loss, norm)."""
+        n = len(batches)
+        loss = norm = None
+        for i, b in enumerate(batches):
+            if getattr(b, "event", None) is not None:
+                torch.cuda.current_stream().wait_event(b.event)
+            last = i == n - 1
+            loss, norm = self.arch.loss_and_grads(self.model, b, self.grads, hook=self._bucket_ready if last else None,
+                                                  hidden=None if self.host_rng else self._device_hidden, accumulate=i > 0)
+        loss, norm = loss.clone(), norm.clone()
+        if self.world > 1:
+            torch.cuda.current_stream().wait_stream(self.comm)
+        self.apply_update(extra_scale=1.0 / n)
+        return loss, norm
+
     def _device_hidden(self, batch_size):
         dev = self.flat_p.device
         n = 2 * self.model.num_layers
         return (torch.randn(n, batch_size, 600, device=dev), torch.randn(n, batch_size, 600, device=dev))
 
-    def apply_update(self):
+    def apply_update(self, extra_scale=1.0):
         """clip_grad_norm_(clip) + Adam.step() on the flat buckets (steps/train_qsub.py:121-122)."""
         st = stream_ptr()
-        gscale = 1.0 if self.exact else 1.0 / self.world       # mode B sums the ranks' gradients, mode A averages them
+        gscale = (1.0 if self.exact else 1.0 / self.world) * extra_scale   # mode B sums the ranks' gradients, mode A averages
         self.steps += 1
         call("grad_norm", self.flat_g, LL(self.n), gscale, self.partial, self.norm, st)
         call("clip_adam", self.flat_p, self.flat_g, self.flat_m, self.flat_v, LL(self.n), self.norm, gscale,

@@ -260,13 +260,14 @@ def compute_loss(model, epoch, batch_sample, plotdir=""):
     return loss, norm.detach()
 
 
-def loss_and_grads(model, batch_sample, grads, hook=None, hidden=None, dp=None):
+def loss_and_grads(model, batch_sample, grads, hook=None, hidden=None, dp=None, accumulate=False):
     """compute_loss + loss.backward() without the autograd tape: every parameter gradient is written (not
     accumulated) straight into grads[name] -- e.g. views of the trainer's flat bucket (ssb200/train.py).  `hook(tag)`
     is called when a gradient bucket ('head', 'l1', 'l0') has been enqueued; `hidden(B)` (optional) supplies (h0, c0)
     instead of model.init_hidden; `dp` (ssb200.train.ExactDP, data-parallel mode B) makes the loss normaliser and the
     BatchNorm statistics those of all ranks' utterances together, so that the SUM of the ranks' gradients is the
-    reference's gradient on the concatenated batch.  Returns device scalars (loss, norm)."""
+    reference's gradient on the concatenated batch; `accumulate` adds to grads instead of writing them (gradient
+    accumulation over micro-batches).  Returns device scalars (loss, norm)."""
     dev = model.lin.weight.device
     batch = unpack_batch(batch_sample, ["mix"], dev, ["source%d" % (i + 1) for i in range(model.num_spk)])
     model.hidden = model.init_hidden(batch["B"]) if hidden is None else hidden(batch["B"])
@@ -277,7 +278,8 @@ def loss_and_grads(model, batch_sample, grads, hook=None, hidden=None, dp=None):
         engine.pit_loss(ws, batch["mix"], batch["src"], batch["lens_dev"], F, S, S, mode=0, dp=dp)
         p = {k: v.detach() for k, v in model.param_dict().items()}
         engine.backward(ws, wt, p, grads, batch["mix"], batch["src"], batch["lens_dev"], model.hidden[0].contiguous(),
-                        model.hidden[1].contiguous(), F, S, None, training=model.training, hook=hook, dp=dp)
+                        model.hidden[1].contiguous(), F, S, None, training=model.training, hook=hook, dp=dp,
+                        accumulate=accumulate)
     model.last = {"losses": ws.losses, "indices": ws.idx, "stats": ws.stats, "batch": batch}
     return ws.stats[2], ws.stats[1]
 

@@ -74,3 +74,33 @@ def test_extract_feats_and_reconstruct(tmp_path, monkeypatch, n_fft, hop):
             ref = so.masked_istft_int16(spec, masks[i][k], hop)
             assert fs == 8000 and got.dtype == np.int16 and got.shape == ref.shape
             assert np.abs(got.astype(np.int64) - ref.astype(np.int64)).max() <= 1
+
+
+def test_extract_feats_segments_and_sge_task_suffix(tmp_path, monkeypatch):
+    """The `segments[.k]` branch (steps/extract_feats.py:51-60,70-81) under an SGE array task: inputs and outputs carry the
+    `.k` suffix, every segment becomes its own feature file cut at [t0, t1) seconds, and a recording that has no
+    segment raises KeyError exactly like the reference's `seg_dict[reco_id]`."""
+    root = str(tmp_path)
+    data, ids = _corpus(root, n_utts=2)
+    os.rename(os.path.join(data, "wav.scp"), os.path.join(data, "wav.scp.3"))
+    segs = [("utt0-a", "utt0", 0.1, 0.6), ("utt0-b", "utt0", 0.5, 1.0), ("utt1-a", "utt1", 0.0, 0.75)]
+    with open(os.path.join(data, "segments.3"), "w") as f:
+        for sid, reco, t0, t1 in segs:
+            f.write("%s %s %.2f %.2f\n" % (sid, reco, t0, t1))
+    monkeypatch.setenv("SGE_TASK_ID", "3")
+    feat = os.path.join(root, "feats")
+    extract_feats.main([data, "train", feat])
+    lines = open(os.path.join(data, "feats_train.scp.3")).read().splitlines()
+    assert [l.split()[0] for l in lines] == [s[0] for s in segs]
+    assert open(os.path.join(data, "utt2num_spk.3")).read().splitlines() == ["%s 2" % s[0] for s in segs]
+    for sid, reco, t0, t1 in segs:
+        z = np.load(os.path.join(feat, sid + ".npz"))
+        a = int(round(t0 * 8000))
+        n = int(round((t1 - t0) * 8000))
+        for key in ("mix", "s1", "s2"):
+            ref = so.stft_mag(_audio(root, key, reco)[a:a + n], 512, 128)
+            assert z[key].shape == ref.shape and np.abs(z[key] - ref).max() <= 1e-4 * np.abs(ref).max()
+    with open(os.path.join(data, "segments.3"), "w") as f:            # utt1 has no segment any more
+        f.write("utt0-a utt0 0.10 0.60\n")
+    with pytest.raises(KeyError):
+        extract_feats.main([data, "test", feat])

@@ -200,3 +200,75 @@ def test_stft_host_streaming_equals_single_launch(chunks):
         ops.stft_host(h_sig, rag, h_out, chunks=chunks)
         ref = ops.stft(h_sig.to(DEV), rag).cpu()
         assert torch.equal(h_out, ref)
+
+
+def test_masked_istft_int16_wraps_like_astype():
+    """`(s * 32767).astype('int16')` (steps/reconstruct_sources.py:41-42) does not clip: a mask that pushes the waveform
+    past full scale wraps modulo 2^16.  The kernel must wrap the same way (compared modulo 2^16, +-1 LSB)."""
+    n_fft, hop = 512, 128
+    lens = [9000, 6000]
+    sigs = [0.9 * s / np.abs(s).max() for s in _corpus(21, lens)]
+    rag = ops.Ragged(lens, n_fft, hop, DEV)
+    flat = torch.from_numpy(np.concatenate(sigs).astype(np.float32)).to(DEV)
+    spec = ops.stft(flat, rag, complex_out=True)
+    mask = torch.full((rag.total_frames * rag.F,), 2.5, device=DEV)           # 2.25 x full scale
+    wav, off = ops.istft_masked(spec, mask, rag, 1)
+    wav = wav.cpu().numpy()
+    wrapped = 0
+    for u, sgl in enumerate(sigs):
+        spec_u = so.stft(sgl.astype(np.float32), n_fft, hop)
+        fl = so.masked_istft_float(spec_u, np.full(spec_u.shape, 2.5, dtype=np.float32), hop)
+        ref = np.asarray(fl).astype(np.int64)                                  # trunc toward zero, then wrap to int16
+        ref = ((ref + 32768) % 65536 - 32768)
+        got = wav[off[u]:off[u] + len(ref)].astype(np.int64)
+        d = (got - ref + 32768) % 65536 - 32768
+        assert np.abs(d).max() <= 1, u
+        wrapped += int((np.abs(fl) >= 32768).sum())
+    assert wrapped > 100                                                       # the case really exercises the wrap
+
+
+@pytest.mark.parametrize("n_fft,hop", [(400, 160), (320, 80), (512, 96), (256, 33), (128, 32), (1024, 256)])
+def test_generic_sizes_stft_and_istft(n_fft, hop):
+    """Any even n_fft / any hop (the reference hands --fft-dim and --step-size to librosa unchecked): the direct-summation
+    kernels behind the same entry points, features 1e-4 and wavs +-1 LSB like the fast sizes."""
+    lens = [4000, n_fft // 2 + 1, 7 * hop + 3, 3001]
+    sigs = _corpus(31, lens)
+    rag = ops.Ragged(lens, n_fft, hop, DEV)
+    flat = torch.from_numpy(np.concatenate(sigs)).to(DEV)
+    for complex_out, layout_tf in ((False, False), (True, False), (True, True)):
+        out = ops.stft(flat, rag, complex_out=complex_out, layout_tf=layout_tf)
+        for u, v in enumerate(ops.stft_views(out, rag, layout_tf)):
+            ref = so.stft(sigs[u], n_fft, hop) if complex_out else so.stft_mag(sigs[u], n_fft, hop)
+            got = v.cpu().numpy().T if layout_tf else v.cpu().numpy()
+            assert got.shape == ref.shape
+            mx, l2 = _rel(got, ref)
+            assert mx <= 1e-4 and l2 <= 1e-4, (u, mx, l2)
+    spec = ops.stft(flat, rag, complex_out=True)
+    rng = np.random.default_rng(4)
+    masks = [rng.random((2, rag.F, int(rag.T[u])), dtype=np.float32) for u in range(len(lens))]
+    mask_flat = torch.from_numpy(np.concatenate([m.ravel() for m in masks])).to(DEV)
+    wav, off = ops.istft_masked(spec, mask_flat, rag, 2)
+    wav = wav.cpu().numpy()
+    for u in range(len(lens)):
+        spec_u = so.stft(sigs[u], n_fft, hop)
+        for s in range(2):
+            ref = so.masked_istft_int16(spec_u, masks[u][s], hop)
+            got = wav[off[u] + s * len(ref): off[u] + (s + 1) * len(ref)]
+            assert np.abs(got.astype(np.int64) - ref.astype(np.int64)).max() <= 1, (u, s)
+
+
+@pytest.mark.parametrize("layout_tf", [False, True])
+def test_log_cmvn_epilogue(layout_tf):
+    """The optional K1 epilogue of north_star: log-magnitude, then per-utterance / per-bin mean-variance normalisation."""
+    lens = [5000, 12345, 300]
+    sigs = _corpus(6, lens)
+    rag = ops.Ragged(lens, 512, 128, DEV)
+    flat = torch.from_numpy(np.concatenate(sigs)).to(DEV)
+    feat = ops.cmvn(ops.stft(flat, rag, log=True, layout_tf=layout_tf), rag, layout_tf=layout_tf)
+    for u, v in enumerate(ops.stft_views(feat, rag, layout_tf)):
+        got = v.cpu().numpy().T if layout_tf else v.cpu().numpy()
+        lg = np.log(np.maximum(so.stft_mag(sigs[u], 512, 128), 1e-8)).astype(np.float64)
+        ref = (lg - lg.mean(1, keepdims=True)) / np.sqrt(lg.var(1, keepdims=True) + 1e-8)
+        assert np.abs(got.mean(1)).max() <= 1e-4 and np.abs(got.std(1) - 1).max() <= 1e-3
+        big = so.stft_mag(sigs[u], 512, 128).min(1) > 1e-4          # rows whose log is well conditioned everywhere
+        assert np.abs(got - ref)[big].max() <= 5e-3 if big.any() else True

@@ -85,3 +85,34 @@ def test_clip_adam_kernels_unaligned_sizes():
             call("clip_adam", p, g, m, v, LL(n), norm, 1.0, 0.25, 1e-3, 0.9, 0.999, 1e-8, step, stream_ptr())
         assert abs(float(norm) - float(g.norm())) <= 1e-5 * float(g.norm())
         assert float((p - ref_p.detach()).abs().max()) <= 2e-6, n
+
+
+def test_step_accumulate_equals_mean_of_micro_batch_gradients():
+    """Trainer.step_accumulate (strong scaling: a global batch run as micro-batches) = clip + Adam on the MEAN of the
+    micro-batch gradients, each micro-batch with its own loss normaliser and BatchNorm statistics."""
+    z, case = common.load_golden("upit_s2_f129")
+    batch, _, _ = _batch(case)
+    z2, case2 = common.load_golden("upit_s2_f129")
+    case2 = dict(case2, seed=case2["seed"] + 7, lens=[n - 100 for n in case2["lens"]])
+    batch2, _, _ = _batch(case2)
+    model_a = _model(case)
+    model_b = copy.deepcopy(model_a)
+    opt = torch.optim.Adam(model_a.parameters(), lr=1e-3)
+    tr = train.Trainer(model_b, uPIT, host_rng=True)
+    torch.manual_seed(50)
+    grads = []
+    for b in (batch, batch2):
+        loss, _ = uPIT.compute_loss(model_a, 0, b)
+        loss.backward()
+        grads.append([p.grad.clone() for p in model_a.parameters()])
+    for p, g1, g2 in zip(model_a.parameters(), *grads):
+        p.grad = 0.5 * (g1 + g2)
+    torch.nn.utils.clip_grad_norm_(model_a.parameters(), 0.25)
+    opt.step()
+    torch.manual_seed(50)
+    tr.step_accumulate([batch, batch2])
+    torch.cuda.synchronize()
+    for (k, pa), (_, pb) in zip(model_a.named_parameters(), model_b.named_parameters()):
+        assert float((pa.detach() - pb.detach()).abs().max()) <= 1e-5, k
+    for k in ("running_mean", "running_var"):
+        assert torch.allclose(getattr(model_a.bn, k), getattr(model_b.bn, k), atol=1e-6)

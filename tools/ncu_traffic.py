@@ -39,7 +39,7 @@ def main():
         val = lambda m: float(r[col[m]].replace(",", "")) * UNIT.get(units[col[m]], 1.0)
         rd, wr = val("dram__bytes_read.sum"), val("dram__bytes_write.sum")
         data[key] = {"bytes": rd + wr, "read": rd, "write": wr, "kernel": r[col["Kernel Name"]][:80],
-                     "ncu_duration_us": float(r[col["gpu__time_duration.sum"]].replace(",", "")),
+                     "ncu_duration": "%s %s" % (r[col["gpu__time_duration.sum"]], units[col["gpu__time_duration.sum"]]),
                      "source": "ncu --set full, one launch, %s (tools/ncu_traffic.py)" % os.path.basename(rep)}
         print(key, data[key])
     json.dump(data, open(OUT, "w"), indent=1, sort_keys=True)
