@@ -257,6 +257,21 @@ int ss_oracle_masks(const void* spec, const float* src_mag, long long src_stride
                     int max_frames, int F, int n_src, int hard, float* masks, void* stream);
 int ss_sdr_sums(const float* ref, const long long* ref_off, const float* est, const long long* est_off, const int* n_ref,
                 const int* n_est, int n_items, int max_ref, double* sums, void* stream);
+/* BSS Eval (SDR / SIR / SAR with a flen-tap time-invariant distortion filter: what mir_eval.separation.bss_eval_sources
+ * computes at steps/evaluate_oracle.py:144 and steps/evaluate_sources.py:57; restated in oracle/eval_oracle.py, parity
+ * unpinned -- mir_eval is absent).  The O(N * flen) parts run on the device, the (n_src*flen)^2 solves on the host:
+ * ss_xcorr: out[p][l] = sum_m a_p[m + lag0 + l] * b_p[m], l < nlag, fp64 (the Toeplitz Gram blocks of the delayed
+ *   references and the right-hand sides <estimate, reference delayed by l>); pair p reads a + a_off[p] (a_len[p] samples)
+ *   and b + b_off[p]; signals are zero outside their lengths.
+ * ss_bss_proj_sums: item = (recording, estimate j), n_src consecutive items per recording; ref_off[rec*n_src + s] locates
+ *   reference s of the recording; c1[item][flen] = filter on reference j, c2[item][n_src][flen] = filters on all
+ *   references; with p1, p2 the two projections over n < N + flen - 1,
+ *   sums[item] = { sum p1^2, sum (e-p1)^2, sum (p2-p1)^2, sum p2^2, sum (e-p2)^2 }: SDR = [0]/[1], SIR = [0]/[2], SAR = [3]/[4]. */
+int ss_xcorr(const float* a, const long long* a_off, const int* a_len, const float* b, const long long* b_off,
+             const int* b_len, int n_pairs, int max_b_len, int lag0, int nlag, double* out, void* stream);
+int ss_bss_proj_sums(const float* ref, const long long* ref_off, const float* est, const long long* est_off, const int* n_ref,
+                     const int* n_est, const double* c1, const double* c2, int n_items, int n_src, int flen, int max_ref,
+                     double* sums, void* stream);
 
 /* ---- f1: global-norm clip + Adam over one flat fp32 bucket.  Replaces torch.nn.utils.clip_grad_norm_(params,
  * 0.25) and torch.optim.Adam(lr=1e-3).step() at steps/train_qsub.py:95,121-122 ----

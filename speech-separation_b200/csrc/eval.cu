@@ -74,6 +74,97 @@ sdr_sums_kernel(const float* __restrict__ ref, const long long* __restrict__ ref
   }
 }
 
+// ---- BSS Eval inner products (steps/evaluate_oracle.py:144: mir_eval bss_eval_sources; restated in oracle/eval_oracle.py).
+// xcorr: out[p][l] = sum_m a_p[m + lag0 + l] * b_p[m] (signals zero outside their lengths), fp64 accumulation.
+// These are the entries of the Toeplitz Gram blocks <s_i(.-a), s_j(.-b)> and of the right-hand sides <est, s_i(.-l)>.
+constexpr int XC_CHUNK = 2048, XC_LAGS = 256;
+
+__global__ void __launch_bounds__(XC_LAGS)
+xcorr_kernel(const float* __restrict__ a, const long long* __restrict__ a_off, const int* __restrict__ a_len,
+             const float* __restrict__ b, const long long* __restrict__ b_off, const int* __restrict__ b_len, int lag0,
+             int nlag, double* __restrict__ out) {
+  __shared__ float sa[XC_CHUNK + XC_LAGS], sb[XC_CHUNK];
+  const int p = blockIdx.z, l0 = blockIdx.x * XC_LAGS, m0 = blockIdx.y * XC_CHUNK;
+  const int na = a_len[p], nb = b_len[p];
+  if (m0 >= nb) return;
+  const float* ap = a + a_off[p];
+  const float* bp = b + b_off[p];
+  for (int i = threadIdx.x; i < XC_CHUNK; i += XC_LAGS) sb[i] = m0 + i < nb ? bp[m0 + i] : 0.0f;
+  const int abase = m0 + lag0 + l0;                       // a index of sa[0]
+  for (int i = threadIdx.x; i < XC_CHUNK + XC_LAGS; i += XC_LAGS) {
+    const int j = abase + i;
+    sa[i] = (j >= 0 && j < na) ? ap[j] : 0.0f;
+  }
+  __syncthreads();
+  const int l = l0 + threadIdx.x;
+  if (l >= nlag) return;
+  double acc = 0.0;
+  const float* x = sa + threadIdx.x;
+#pragma unroll 8
+  for (int i = 0; i < XC_CHUNK; ++i) acc = fma((double)x[i], (double)sb[i], acc);
+  atomicAdd(out + (long long)p * nlag + l, acc);
+}
+
+// Item = (recording, estimate j).  With the distortion filters solved on the host (c1: flen taps on reference j; c2:
+// S x flen taps on all references of the recording), forms for every n in [0, N + flen - 1)
+//   p1[n] = sum_l c1[l] s_j[n-l]        (s_target + e_spat)        p2[n] = sum_s sum_l c2[s][l] s_s[n-l]
+// and accumulates sums[item] = { sum p1^2, sum (e - p1)^2, sum (p2 - p1)^2, sum p2^2, sum (e - p2)^2 } in fp64 without ever
+// storing the projections: SDR = [0]/[1], SIR = [0]/[2], SAR = [3]/[4].
+constexpr int BP_OUT = 256, BP_MAXSRC = 4;
+
+__global__ void __launch_bounds__(BP_OUT)
+bss_proj_sums_kernel(const float* __restrict__ ref, const long long* __restrict__ ref_off, const float* __restrict__ est,
+                     const long long* __restrict__ est_off, const int* __restrict__ n_ref, const int* __restrict__ n_est,
+                     const double* __restrict__ c1, const double* __restrict__ c2, int S, int flen,
+                     double* __restrict__ sums) {
+  extern __shared__ unsigned char bsm[];
+  double* f2 = reinterpret_cast<double*>(bsm);            // [S][flen]
+  double* f1 = f2 + S * flen;                             // [flen]
+  float* sig = reinterpret_cast<float*>(f1 + flen);       // [S][BP_OUT + flen - 1]
+  const int item = blockIdx.y, rec = item / S, j = item - rec * S;
+  const int N = n_ref[item], L = n_est[item];
+  const int n0 = blockIdx.x * BP_OUT;
+  if (n0 >= N + flen - 1) return;
+  const int span = BP_OUT + flen - 1;
+  for (int i = threadIdx.x; i < S * flen; i += BP_OUT) f2[i] = c2[(long long)item * S * flen + i];
+  for (int i = threadIdx.x; i < flen; i += BP_OUT) f1[i] = c1[(long long)item * flen + i];
+  for (int s = 0; s < S; ++s) {
+    const float* rp = ref + ref_off[rec * S + s];
+    for (int i = threadIdx.x; i < span; i += BP_OUT) {
+      const int k = n0 - (flen - 1) + i;                  // sig[s][i] = s_s[n0 - flen + 1 + i]
+      sig[s * span + i] = (k >= 0 && k < N) ? rp[k] : 0.0f;
+    }
+  }
+  __syncthreads();
+  const int n = n0 + threadIdx.x;
+  double v[5] = {0.0, 0.0, 0.0, 0.0, 0.0};
+  if (n < N + flen - 1) {
+    double p1 = 0.0, p2 = 0.0;
+    const float* xj = sig + j * span + threadIdx.x + flen - 1;       // s_j[n]
+    for (int l = 0; l < flen; ++l) p1 = fma(f1[l], (double)xj[-l], p1);
+    for (int s = 0; s < S; ++s) {
+      const float* xs = sig + s * span + threadIdx.x + flen - 1;
+      const double* f = f2 + s * flen;
+      for (int l = 0; l < flen; ++l) p2 = fma(f[l], (double)xs[-l], p2);
+    }
+    const double e = n < L ? (double)est[est_off[item] + n] : 0.0;
+    v[0] = p1 * p1; v[1] = (e - p1) * (e - p1); v[2] = (p2 - p1) * (p2 - p1); v[3] = p2 * p2; v[4] = (e - p2) * (e - p2);
+  }
+  __shared__ double red[BP_OUT / 32][5];
+#pragma unroll
+  for (int k = 0; k < 5; ++k)
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v[k] += __shfl_xor_sync(0xffffffffu, v[k], o);
+  if ((threadIdx.x & 31) == 0)
+    for (int k = 0; k < 5; ++k) red[threadIdx.x >> 5][k] = v[k];
+  __syncthreads();
+  if (threadIdx.x < 5) {
+    double t = 0.0;
+    for (int w = 0; w < BP_OUT / 32; ++w) t += red[w][threadIdx.x];
+    atomicAdd(&sums[(long long)item * 5 + threadIdx.x], t);
+  }
+}
+
 }  // namespace ssb
 
 extern "C" int ss_oracle_masks(const void* spec, const float* src_mag, long long src_stride, const long long* frame_off,
@@ -97,4 +188,32 @@ extern "C" int ss_sdr_sums(const float* ref, const long long* ref_off, const flo
   cudaMemsetAsync(sums, 0, sizeof(double) * 5 * (size_t)n_items, st);
   sdr_sums_kernel<<<dim3(cdiv(max_ref, SDR_CHUNK), n_items), 256, 0, st>>>(ref, ref_off, est, est_off, n_ref, n_est, sums);
   return check_launch("ss_sdr_sums");
+}
+
+extern "C" int ss_xcorr(const float* a, const long long* a_off, const int* a_len, const float* b, const long long* b_off,
+                        const int* b_len, int n_pairs, int max_b_len, int lag0, int nlag, double* out, void* stream) {
+  using namespace ssb;
+  if (n_pairs <= 0 || nlag <= 0) return 0;
+  SS_REQUIRE(max_b_len > 0, "ss_xcorr: max_b_len must be positive");
+  cudaStream_t st = (cudaStream_t)stream;
+  cudaMemsetAsync(out, 0, sizeof(double) * (size_t)n_pairs * nlag, st);
+  xcorr_kernel<<<dim3(cdiv(nlag, XC_LAGS), cdiv(max_b_len, XC_CHUNK), n_pairs), XC_LAGS, 0, st>>>(a, a_off, a_len, b, b_off,
+                                                                                                b_len, lag0, nlag, out);
+  return check_launch("ss_xcorr");
+}
+
+extern "C" int ss_bss_proj_sums(const float* ref, const long long* ref_off, const float* est, const long long* est_off,
+                                const int* n_ref, const int* n_est, const double* c1, const double* c2, int n_items,
+                                int n_src, int flen, int max_ref, double* sums, void* stream) {
+  using namespace ssb;
+  if (n_items <= 0) return 0;
+  SS_REQUIRE(n_src >= 1 && n_src <= BP_MAXSRC && flen >= 1 && max_ref > 0, "ss_bss_proj_sums: bad shape");
+  const size_t smem = (size_t)(n_src + 1) * flen * 8 + (size_t)n_src * (BP_OUT + flen - 1) * 4;
+  SS_REQUIRE(smem <= 200 * 1024, "ss_bss_proj_sums: filter length %d too large", flen);
+  cudaStream_t st = (cudaStream_t)stream;
+  cudaFuncSetAttribute(bss_proj_sums_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  cudaMemsetAsync(sums, 0, sizeof(double) * 5 * (size_t)n_items, st);
+  bss_proj_sums_kernel<<<dim3(cdiv(max_ref + flen - 1, BP_OUT), n_items), BP_OUT, smem, st>>>(
+      ref, ref_off, est, est_off, n_ref, n_est, c1, c2, n_src, flen, sums);
+  return check_launch("ss_bss_proj_sums");
 }

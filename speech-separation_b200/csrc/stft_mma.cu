@@ -363,7 +363,7 @@ extern "C" int ss_stft_dft256(const float* sig, const long long* utts, int n_utt
   if (n_tiles <= 0 || n_utts <= 0) return 0;
   SS_REQUIRE(sig && utts && tile_u0 && out, "ss_stft_dft256: null pointer");
   SS_REQUIRE((reinterpret_cast<uintptr_t>(utts) & 15) == 0, "ss_stft_dft256: utterance table must be 16-byte aligned");
-  // (flag bits 8..10: timing experiments of tools/_diag_dft.py -- no MMAs / no producer work / no epilogue stores; wrong results)
+  // (flag bits 8..10: timing experiments of tools/diag_dft.py -- no MMAs / no producer work / no epilogue stores; wrong results)
   SS_REQUIRE((flags & ~(SS_STFT_LOG | 0x700)) == 0, "ss_stft_dft256: magnitude (optionally log) in the (F, T) layout only");
   cudaStream_t st = (cudaStream_t)stream;
   static unsigned char* basis[64] = {nullptr};                          // per device, built on first use

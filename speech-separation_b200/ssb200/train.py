@@ -20,10 +20,10 @@ from ._lib import LL, call, lib, stream_ptr
 
 def bucket_of(name):
     """Gradient bucket a parameter belongs to, by the reference's state_dict names."""
-    if name.startswith("blstm.") and "_l0" in name:
-        return "l0"
-    if name.startswith("blstm.") and "_l1" in name:
-        return "l1"
+    if name.startswith("blstm."):
+        import re
+        k = int(re.search(r"_l(\d+)", name).group(1))
+        return "l0" if k == 0 else "l1"        # layers >= 1 share a bucket: it is complete when layer 1's backward is
     return "head"
 
 
@@ -147,7 +147,7 @@ class Trainer:
 
     # -- gradient exchange: called by the engine as each bucket's last kernel has been enqueued --
     def _bucket_ready(self, tag):
-        if self.world == 1:
+        if self.world == 1 or tag not in self.buckets:         # (a 3-layer net reports 'l2' before 'l1': same bucket)
             return
         import torch.distributed as dist
         ev = torch.cuda.Event()

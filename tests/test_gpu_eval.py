@@ -45,10 +45,35 @@ def test_evaluate_oracle_cli_files(tmp_path):
     (tmp_path / "data").mkdir()
     (tmp_path / "data" / "wav.scp").write_text("\n".join(lines) + "\n")
     os.environ.pop("SGE_TASK_ID", None)
-    evaluate_oracle.main([str(tmp_path / "data"), "--batch", "2"])
+    evaluate_oracle.main([str(tmp_path / "data"), "--batch", "2", "--bss-filter", "32"])
     out = tmp_path / "data" / "oracle_soft_mask_eval"
+    for k in ("SDR", "SIR", "SAR"):                                    # the reference's six files, its line format
+        ses = [l.split() for l in (out / ("session_%ss.txt" % k)).read_text().splitlines()]
+        sou = [l.split() for l in (out / ("source_%ss.txt" % k)).read_text().splitlines()]
+        assert [x[0] for x in ses] == ["u0", "u1", "u2"] and all(len(x) == 3 for x in sou)
+        for a, b in zip(ses, sou):
+            assert abs(float(a[1]) - (float(b[1]) + float(b[2])) / 2) < 1e-9 and np.isfinite(float(a[1]))
     sess = [l.split() for l in (out / "session_SISDRs.txt").read_text().splitlines()]
     src = [l.split() for l in (out / "source_SISDRs.txt").read_text().splitlines()]
     assert [s[0] for s in sess] == ["u0", "u1", "u2"] and all(len(s) == 3 for s in src)
     for a, b in zip(sess, src):
         assert abs(float(a[1]) - (float(b[1]) + float(b[2])) / 2) < 1e-9 and np.isfinite(float(a[1]))
+
+
+@pytest.mark.parametrize("flen", [16, 64])
+def test_bss_eval_on_device_matches_restatement(flen):
+    """SDR / SIR / SAR with the correlations and projection energies on the device (ss_xcorr, ss_bss_proj_sums) against
+    the numpy restatement of BSS Eval (oracle/eval_oracle.py; mir_eval itself is absent: parity unpinned)."""
+    lens = [5000, 7000, 4100]
+    waves = [synth.mixture(800 + i, n, 2) for i, n in enumerate(lens)]
+    est, si, (sdr, sir, sar) = evaluate_oracle.oracle_separate([w[0] for w in waves], [w[1] for w in waves], 256, 64, False,
+                                                               bss_flen=flen)
+    for i, (mix, srcs) in enumerate(waves):
+        full = np.zeros((2, len(mix)))
+        for s in range(2):
+            full[s, :len(est[i][s])] = est[i][s]                 # zero beyond hop*(T-1), evaluate_oracle.py:142-143
+        o_sdr, o_sir, o_sar = eval_oracle.bss_eval_sources(np.stack(srcs), full, flen=flen)
+        for s in range(2):
+            assert abs(sdr[i, s] - o_sdr[s]) <= 0.02, (i, s, sdr[i, s], o_sdr[s])
+            assert abs(sir[i, s] - o_sir[s]) <= 0.05, (i, s, sir[i, s], o_sir[s])
+            assert abs(sar[i, s] - o_sar[s]) <= 0.02, (i, s, sar[i, s], o_sar[s])

@@ -96,3 +96,39 @@ def test_cfg5_masks_batch_invariance(tmp_path):
         for k in ("s1", "s2"):
             assert a[k].shape == (F, lens[i])
             assert np.abs(a[k] - b[k]).max() <= 2e-5, (i, k)
+
+
+def test_three_layer_net_matches_oracle():
+    """`num_layers=3` (BASELINE configs[0] names a 3-layer BLSTM; the reference hard-codes 2, archs/uPIT.py:115): the
+    engine's layer loops, the ping-pong of the streamed dX buffers and the Trainer's buckets, against the fp64 oracle."""
+    from ssb200 import train
+    F, S, B = 129, 2, 5
+    lens = [70, 66, 61, 55, 49]                              # T >= 48: the GEMMs stream under the recurrences
+    samples = _rand_batch(12, lens, F, S)
+    batch = uPIT.Collator("mix")(samples)
+    torch.manual_seed(4)
+    model = uPIT.SepDNN(0, feat_dim=str(F), num_spk=str(S), num_layers="3").cuda()
+    assert "blstm.weight_hh_l2_reverse" in model.state_dict()
+    sd = {k: (v.detach().double().cpu().clone() if v.is_floating_point() else v.cpu().clone())
+          for k, v in model.state_dict().items()}
+    torch.manual_seed(33)
+    loss, norm = uPIT.compute_loss(model, 0, batch)
+    loss.backward()
+    torch.cuda.synchronize()
+    torch.manual_seed(33)
+    h0, c0 = torch.randn(6, B, 600).double(), torch.randn(6, B, 600).double()
+    mix, tl = common.pad_time_major([s["mix"] for s in samples])
+    sources = [common.pad_time_major([s["source%d" % (i + 1)] for s in samples])[0] for i in range(S)]
+    params = {k: v.requires_grad_(True) for k, v in sd.items() if v.is_floating_point() and "running" not in k}
+    sd.update(params)
+    oloss, onorm, _, oidx, _, _ = uo.upit_compute_loss(sd, mix, sources, tl, h0, c0, num_layers=3)
+    oloss.backward()
+    assert abs(float(loss.detach()) - float(oloss)) <= 1e-3 * float(oloss)
+    assert np.array_equal(model.last["indices"].cpu().numpy(), oidx.numpy())
+    for k, p in model.named_parameters():
+        assert common.rel(p.grad.cpu().numpy(), params[k].grad.numpy()) <= 1e-3, k
+    tr = train.Trainer(model, uPIT)                          # flat buckets with the third layer, one fused step
+    before = tr.flat_p.clone()
+    tr.step(batch)
+    torch.cuda.synchronize()
+    assert set(tr.buckets) == {"l0", "l1", "head"} and float((tr.flat_p - before).abs().max()) > 0
