@@ -285,6 +285,19 @@ int ss_grad_norm(const float* g, long long n, float gscale, float* partial, floa
 int ss_clip_adam(float* p, const float* g, float* m, float* v, long long n, const float* norm, float gscale,
                  float max_norm, float lr, float beta1, float beta2, float eps, int step, void* stream);
 
+/* ---- ss_grad_norm for callers that cannot allocate (CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * Same result as ss_grad_norm (norm_out[0] = gscale * ||g||_2), but the per-block partial sums live in a static
+ * __device__ array inside the library (32 KB, held by every GPU that loads the library until exit) instead of a
+ * caller workspace; the call performs no cudaMalloc / cudaFree / allocating library routine.
+ * Limit: n <= ss_grad_norm_noalloc_max_n() = SS_GRAD_NORM_NOALLOC_MAX_N elements; larger n returns -1 with a message
+ * in ss_last_error() (use ss_grad_norm).  -3: the scratch symbol could not be resolved on the current device.
+ * Every call on a device shares the array (it keeps the previous call's partials; each call overwrites all it reads,
+ * nothing needs clearing): calls that OVERLAP on the GPU -- different streams without ordering -- race. */
+#define SS_GRAD_NORM_NOALLOC_MAX_N (64LL << 20)
+long long ss_grad_norm_noalloc_max_n(void);
+int ss_grad_norm_noalloc(const float* g, long long n, float gscale, float* norm_out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -85,6 +85,37 @@ __global__ void __launch_bounds__(OPT_THREADS) clip_adam_kernel(float* __restric
     adam_one(p[e], g[e], m[e], v[e], coef, a);
 }
 
+// ---- scratch of ss_grad_norm_noalloc: per-block partial sums of squares in a file-scope device array, so that the
+// entry point needs no caller workspace and allocates nothing.  Every GPU that loads the library holds these 32 KB
+// until exit.  In HOST code the name `g_norm_scratch` is only a stand-in for the symbol, not a device address:
+// noalloc_scratch() resolves the address with cudaGetSymbolAddress once per device, with that device current.
+constexpr long long NOALLOC_MAX_N = SS_GRAD_NORM_NOALLOC_MAX_N;
+constexpr int NOALLOC_MAX_PARTS = (int)((NOALLOC_MAX_N + OPT_PER_BLOCK - 1) / OPT_PER_BLOCK);   // 8192 floats
+static __device__ __align__(256) float g_norm_scratch[NOALLOC_MAX_PARTS];
+
+static float* noalloc_scratch() {
+  static float* addr[64] = {nullptr};   // per device; a racing first call resolves the same address twice
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess || dev < 0 || dev >= 64) {
+    set_error("ss_grad_norm_noalloc: cudaGetDevice: %s (device %d)", cudaGetErrorString(e), dev);
+    return nullptr;
+  }
+  float* p = __atomic_load_n(&addr[dev], __ATOMIC_ACQUIRE);
+  if (!p) {
+    void* sym = nullptr;
+    e = cudaGetSymbolAddress(&sym, g_norm_scratch);
+    if (e != cudaSuccess || !sym) {
+      set_error("ss_grad_norm_noalloc: cudaGetSymbolAddress on device %d: %s", dev, cudaGetErrorString(e));
+      (void)cudaGetLastError();
+      return nullptr;
+    }
+    p = static_cast<float*>(sym);
+    __atomic_store_n(&addr[dev], p, __ATOMIC_RELEASE);
+  }
+  return p;
+}
+
 }  // namespace ssb
 
 extern "C" int ss_optim_parts(long long n) { return ssb::cdiv(n, ssb::OPT_PER_BLOCK); }
@@ -97,6 +128,27 @@ extern "C" int ss_grad_norm(const float* g, long long n, float gscale, float* pa
   if (parts > 0) sumsq_partial_kernel<<<parts, OPT_THREADS, 0, st>>>(g, n, partial);
   sumsq_final_kernel<<<1, 256, 0, st>>>(partial, parts, gscale, norm_out);
   return check_launch("ss_grad_norm");
+}
+
+extern "C" long long ss_grad_norm_noalloc_max_n(void) { return ssb::NOALLOC_MAX_N; }
+
+// ss_grad_norm without a caller workspace and without any allocation: the same two kernels, the partial sums in the
+// library's static device array.  All calls on a device share that array: every call overwrites the `parts` entries
+// it reads (nothing has to start at zero, so nothing is cleared), and calls that overlap on the GPU (different
+// streams, no ordering between them) race.
+extern "C" int ss_grad_norm_noalloc(const float* g, long long n, float gscale, float* norm_out, void* stream) {
+  using namespace ssb;
+  SS_REQUIRE(n >= 0 && norm_out && (g || n == 0), "ss_grad_norm_noalloc: bad arguments");
+  SS_REQUIRE(n <= NOALLOC_MAX_N,
+             "ss_grad_norm_noalloc: n = %lld exceeds the static scratch (max %lld elements); use ss_grad_norm with a "
+             "caller workspace of ss_optim_parts(n) floats", n, (long long)NOALLOC_MAX_N);
+  float* partial = noalloc_scratch();
+  if (!partial) return -3;
+  const int parts = cdiv(n, OPT_PER_BLOCK);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (parts > 0) sumsq_partial_kernel<<<parts, OPT_THREADS, 0, st>>>(g, n, partial);
+  sumsq_final_kernel<<<1, 256, 0, st>>>(partial, parts, gscale, norm_out);
+  return check_launch("ss_grad_norm_noalloc");
 }
 
 extern "C" int ss_clip_adam(float* p, const float* g, float* m, float* v, long long n, const float* norm, float gscale,
