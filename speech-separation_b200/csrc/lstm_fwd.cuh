@@ -7,11 +7,13 @@ namespace ssb {
 constexpr int LF_U = 12;                    // hidden units per CTA
 constexpr int LF_N = 4 * LF_U;              // gate columns per CTA
 constexpr int LF_EPI_WARPS = 12;            // 4 TMEM lane quadrants x 3 column groups of 4 units
-constexpr int LF_THREADS = 32 * LF_EPI_WARPS + 64;
+constexpr int LF_LOAD_WARPS = 8;            // epilogue warps 0..7 also check the landed h_prev chunks
+constexpr int LF_THREADS = 32 * (LF_EPI_WARPS + 3);   // + warp 12 (gate + copies) + warp 13 (MMA issuer) + warp 14 (progress)
 constexpr int LF_WCHUNK = 2 * LF_N * 128;   // one 64-wide K chunk of the W slice: [hi 48 rows][lo 48 rows] x 128 B
 constexpr int LF_MAXKC = 10;                // H <= 640
 constexpr int LF_XPITCH = 52;               // floats per row of the lo-row exchange buffer
 constexpr int LF_TMEM = 128;
+constexpr int LF_STAGE_TILES = 2 * 128 * 32 + 64 * 12 * 4 + 64 * 4;   // staging tiles of the coalesced stores
 
 struct LstmFwdParams {
   float* gx;                 // [T*B][8H] in: x-projection + biases (interleaved gate columns); out: activated gates
@@ -23,8 +25,8 @@ struct LstmFwdParams {
   float* cs;                 // [T*B][2H] or null
   float* hn;                 // [2][B][H]
   float* cn;
-  __nv_bfloat16* hbuf;       // [slot 2][dir 2][kc][plane 2][R][64], rows pre-swizzled (SWIZZLE_128B)
-  unsigned int* sync;        // [2]
+  __nv_bfloat16* hbuf;       // exchange buffer [slot 3][dir 2][kc][2R operand rows][64], rows pre-swizzled (SWIZZLE_128B)
+  unsigned int* done;        // [2][64] per direction and CTA: reporting periods (4 steps) whose `out` rows it has made visible
   unsigned int* progress;    // [2] or null: prog_base + number of steps whose `out` rows are globally visible, per direction
   unsigned int prog_base;
   int T, B, H, R, NC, KC, NS;

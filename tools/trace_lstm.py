@@ -19,22 +19,26 @@ with torch.no_grad():
     uPIT.compute_loss(model, 0, batch)
 torch.cuda.synchronize()
 _lib.call("lstm_debug", None)
-d = dbg.cpu().numpy().reshape(T, 32)   # holds layer 1 (last launch)
-names = ["poll_start", "poll_done", "tma_issued", "mma_first_full", "mma_committed", "epi_accum", "epi_math_done", "epi_published"]
+d = dbg.cpu().numpy()[:T * 32].reshape(T, 32)   # holds layer 1 (last launch)
+# stamps (csrc/lstm_fwd.cu): thread 0 = fetch + epilogue thread, M = the MMA-issuing thread
+names = {0: "gate_start", 1: "gate_open", 2: "copies_issued", 3: "M_first_full", 4: "M_committed", 5: "epi_accum",
+         8: "epi_sums", 6: "epi_math", 7: "epi_published", 9: "epi_stores"}
 s0 = 100
-base = d[s0, 1]
-for s in range(s0, s0 + 4):
-    print("step", s, " ".join("%s=%d" % (n, d[s, i] - base) for i, n in enumerate(names)))
-per = np.diff(d[50:350, 1]).mean()
-print("cycles/step %.0f" % per)
+base = d[s0, 0]
+for s in range(s0, s0 + 3):
+    print("step", s, " ".join("%s=%d" % (n, d[s, i] - base) for i, n in sorted(names.items(), key=lambda kv: d[s, kv[0]])))
 seg = d[50:350]
-print("poll_done->tma_issued %.0f" % (seg[:, 2] - seg[:, 1]).mean())
-print("poll_done->mma_first_full %.0f" % (seg[:, 3] - seg[:, 1]).mean())
-print("mma_first_full->mma_committed %.0f" % (seg[:, 4] - seg[:, 3]).mean())
-print("mma_committed->epi_accum %.0f" % (seg[:, 5] - seg[:, 4]).mean())
-print("epi_accum->epi_math_done %.0f" % (seg[:, 6] - seg[:, 5]).mean())
-print("epi_math_done->published %.0f" % (seg[:, 7] - seg[:, 6]).mean())
-print("epi_accum->tmem_ld_done %.0f" % (seg[:, 8] - seg[:, 5]).mean())
-print("chunk arrivals rel poll_done", [int((seg[:, 10 + k] - seg[:, 1]).mean()) for k in range(1, 10)])
-print("publish: stores %.0f bar %.0f fence.proxy %.0f red.release %.0f" % ((seg[:,20]-seg[:,6]).mean(), (seg[:,21]-seg[:,20]).mean(), (seg[:,22]-seg[:,21]).mean(), (seg[:,23]-seg[:,22]).mean()))
-print("published->next poll_done %.0f" % (seg[1:, 1] - seg[:-1, 7]).mean())
+print("cycles/step %.0f" % np.diff(d[50:350, 5]).mean())
+def dt(a, b, shift=0):
+    return (seg[shift:, a] - seg[:len(seg) - shift, b]).mean()
+print("gate_open->copies_issued (10 bulk copies)          %.0f" % dt(2, 1))
+print("gate_open->M_first_full (chunk 0 landed + checked) %.0f" % dt(3, 1))
+print("M_first_full->M_committed                          %.0f" % dt(4, 3))
+print("M_committed->epi_accum                             %.0f" % dt(5, 4))
+print("epi_accum->epi_sums (tmem ld + lo-row exchange)    %.0f" % dt(8, 5))
+print("epi_sums->epi_math                                 %.0f" % dt(6, 8))
+print("epi_math->epi_published                            %.0f" % dt(7, 6))
+print("epi_published->epi_stores                          %.0f" % dt(9, 7))
+print("epi_published->next gate_open                      %.0f" % dt(1, 7, 1))
+print("chunk valid seen by M rel gate_open", [int((seg[:, 10 + k] - seg[:, 1]).mean()) for k in range(1, 10)])
+print("copy i issued rel gate_open", [int((seg[:, 20 + k] - seg[:, 1]).mean()) for k in range(10)])
