@@ -448,6 +448,9 @@ extern "C" int ss_lstm_fwd(float* gx, const void* whh_r, long long whh_ld, long 
   p.done = (unsigned int*)((char*)ws + hbuf_bytes);
   cudaMemsetAsync(ws, 0, hbuf_bytes + 1024, st);            // the tail of the last K chunk is never published and must be finite
 
+  if (H == 600 && p.R == 64 && whh_ld % 8 == 0 && whh_plane % 8 == 0)
+    return launch_lstm_fwd_tw(p, whh_r, whh_ld, whh_plane, st);
+
   CUtensorMap tmW;
   {
     uint64_t dims[3] = {(uint64_t)H, (uint64_t)8 * H, 2};

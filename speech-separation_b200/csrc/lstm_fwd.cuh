@@ -33,4 +33,7 @@ struct LstmFwdParams {
   long long* dbg;            // optional clock64 trace of CTA 0: [step][32]
 };
 
+// lstm_fwd_tw.cu: H = 600, B <= 64 with W_hh resident in tensor memory
+int launch_lstm_fwd_tw(const LstmFwdParams& p, const void* whh_r, long long whh_ld, long long whh_plane, cudaStream_t st);
+
 }  // namespace ssb
