@@ -4,13 +4,16 @@
 //   dh_rec[b][j] = sum_{n < 4H} dG_prev[b][n] * W_hh[n][j]            (n = 4u+gate, interleaved)
 //
 // has K = 4H = 2400: an output-stationary CTA must stream all of dG_prev (614 KB split-bf16) through shared memory
-// every step, at ~260 cycles per 16 KB copy (tools/microbench/bulk_size.cu) -> >= 10k cycles per step.  Here a
-// cluster of 4 CTAs owns 64 hidden units; CTA r streams only K-quarter r of dG_prev (154 KB), multiplies it with
-// its resident [K-quarter x 64 units] slice of W_hh^T (one stacked tcgen05.mma per 16-wide k-step: A = dG rows with
-// hi/lo planes interleaved, B = [W_hi; W_lo], D = 128 x 128 in TMEM), and the four partial products are reduced over
-// distributed shared memory: every CTA adds the hi/lo row pairs with a warp shuffle and sends each peer the
-// 64 x 16 block of the 16 units that peer finalises (st.async, completion counted on the peer's mbarrier).
-// Each CTA then runs the cell backward for its 16 units, writes dG[t] and publishes it (gpu-scope release counter).
+// every step -> >= 10k cycles per step.  Here a cluster of 4 CTAs owns 64 hidden units; CTA r streams only K-quarter r
+// of dG_prev (154 KB) and multiplies it with its [K-quarter x 64 units] slice of W_hh^T, which is RESIDENT IN TENSOR
+// MEMORY: A = [W^T rows: lane 2 * unit + plane] written once with tcgen05.st (up to 320 columns), B = the dG chunk as
+// the TMA box lands it (rows 2 * b + plane), D^T = 128 x 128 in TMEM columns 320..447.  Shared memory then holds all
+// ten chunks of a step (the 160 KB W slice used to leave room for a 3-deep ring: 480 cycles per chunk), and the
+// copies are issued back to back.  The four partial products are reduced over distributed shared memory: a thread
+// owns one W^T row (unit, plane) and 32 columns, adds the planes (a shuffle between neighbouring lanes, an add between
+// neighbouring columns) and sends the peer that finalises its unit eight consecutive batch rows (st.async, completion
+// counted on the peer's mbarrier).  Each CTA then runs the cell backward for its 16 units, writes dG[t] and publishes
+// it (gpu-scope release counter).
 #include <stdlib.h>
 
 #include "../../include/ssb200.h"
@@ -27,12 +30,14 @@ constexpr int KS_NCL = (KS_H + KS_UC - 1) / KS_UC;      // clusters per directio
 constexpr int KS_NCTA = KS_NCL * KS_CL;                 // CTAs per direction (40)
 constexpr int KS_KCH = (4 * KS_H + 63) / 64;            // 64-wide K chunks in total (38; the last holds 32 columns)
 constexpr int KS_MAXCH = 10;                            // chunks per CTA: 10, 10, 9, 9
-constexpr int KS_NS = 3;                                // dG ring stages
+constexpr int KS_NS = KS_MAXCH;                         // dG stages: one per chunk of the step
 constexpr int KS_CHUNK = 16384;                         // one chunk of either operand: 128 rows x 128 B
 constexpr int KS_EPI_WARPS = 16;
 constexpr int KS_THREADS = 64 + 32 * KS_EPI_WARPS;
-constexpr int KS_RBUF = KS_CL * 64 * KS_U * 4;          // [src][b][16 floats]
-constexpr int KS_SMEM = KS_MAXCH * KS_CHUNK + KS_NS * KS_CHUNK + KS_RBUF + 1024 + 256;
+constexpr int KS_RBUF = KS_CL * 64 * KS_U * 4;          // [src][16 units][64 batch rows] floats
+constexpr int KS_SMEM = KS_NS * KS_CHUNK + KS_RBUF + 1024 + 256;
+constexpr int KS_TMEM = 512;                            // W^T slice in columns [0, 320), accumulator in [320, 448)
+constexpr int KS_DCOL = 320;
 
 __device__ __forceinline__ int ks_chunk_begin(int r) { return r < 2 ? 10 * r : 20 + 9 * (r - 2); }
 
@@ -67,6 +72,19 @@ __device__ __forceinline__ bool mbar_try_wait_cluster(uint64_t* bar, uint32_t pa
   return ok != 0;
 }
 
+__device__ __forceinline__ void ks_umma_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc, uint32_t accum) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}" ::"r"(tmem_d),
+      "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(accum)
+      : "memory");
+}
+__device__ __forceinline__ void ks_tmem_st8(uint32_t taddr, uint4 a, uint4 b) {
+  asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"r"(taddr), "r"(a.x), "r"(a.y), "r"(a.z),
+               "r"(a.w), "r"(b.x), "r"(b.y), "r"(b.z), "r"(b.w)
+               : "memory");
+}
+
 // all-CTA skew probe (DBG only): globaltimer of 4 events for steps 100..115 behind the per-step rows of CTA 0
 #define KS_GSTAMP(ev)                                                                                              \
   do {                                                                                                             \
@@ -84,12 +102,12 @@ __device__ __forceinline__ bool mbar_try_wait_cluster(uint64_t* bar, uint32_t pa
 
 template <bool DBG>
 __global__ void __launch_bounds__(KS_THREADS, 1)
-lstm_bwd_ks_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUtensorMap tmG, LstmBwdParams p) {
+lstm_bwd_ks_kernel(const __grid_constant__ CUtensorMap tmG, LstmBwdParams p, const __nv_bfloat16* __restrict__ whhT,
+                   long long whhT_ld, long long whhT_plane) {
   extern __shared__ unsigned char smem_raw[];
   unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-  unsigned char* wsm = smem;                                   // KS_MAXCH chunks of [W_hi 64 units; W_lo 64 units]
-  unsigned char* ring = smem + KS_MAXCH * KS_CHUNK;            // KS_NS chunks of dG_prev, rows = 2*b + plane
-  float* rbuf = reinterpret_cast<float*>(ring + KS_NS * KS_CHUNK);   // [src][b][16], 16-byte pieces XOR-swizzled
+  unsigned char* ring = smem;                                  // KS_NS chunks of dG_prev (stage i = chunk i of the step), rows = 2*b + plane
+  float* rbuf = reinterpret_cast<float*>(ring + KS_NS * KS_CHUNK);   // [src][unit 16][b 64]
   uint64_t* full = reinterpret_cast<uint64_t*>(reinterpret_cast<unsigned char*>(rbuf) + KS_RBUF);
   uint64_t* empty = full + KS_NS;
   uint64_t* accum_full = empty + KS_NS;
@@ -108,7 +126,6 @@ lstm_bwd_ks_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
   unsigned int* counter = p.sync + dir;
 
   if (threadIdx.x == 0) {
-    tma_prefetch_desc(&tmW);
     tma_prefetch_desc(&tmG);
     for (int s = 0; s < KS_NS; ++s) {
       mbar_init(&full[s], 1);
@@ -119,18 +136,34 @@ lstm_bwd_ks_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
     mbar_init(rfull, 1);
     fence_barrier_init();
   }
-  if (warp == 1) tmem_alloc<128>(tmem_slot);
+  if (warp == 1) tmem_alloc<KS_TMEM>(tmem_slot);
   tc_fence_before();
   __syncthreads();
   cluster_sync_all();                                          // peers' mbarriers exist before anyone sends
   tc_fence_after();
   const uint32_t tmem_d = *tmem_slot;
 
+  // ---- W_hh^T slice -> tensor memory (once): lane m = 2 * unit + plane of the cluster's 64 units, 8 columns per 16-wide
+  // k-step of this CTA's K range; units >= H (last cluster) and the k-steps past 4H (last chunk) are never multiplied / zero
+  if (warp >= 2 && warp < 6) {
+    const int m = 32 * (warp & 3) + lane, unit = c * KS_UC + (m >> 1);
+    const __nv_bfloat16* wr = whhT + (long long)(m & 1) * whhT_plane + (long long)(dir * H + unit) * whhT_ld + (long long)ch0 * 64;
+    const uint32_t tl = tmem_d + ((uint32_t)(32 * (warp & 3)) << 16);
+    const uint4 z4 = make_uint4(0, 0, 0, 0);
+    for (int ks = 0; ks < 4 * nch; ++ks) {
+      const bool ok = unit < H && ch0 * 64 + 16 * ks + 16 <= 4 * H;
+      const uint4 a = ok ? __ldg(reinterpret_cast<const uint4*>(wr + 16 * ks)) : z4;
+      const uint4 b = ok ? __ldg(reinterpret_cast<const uint4*>(wr + 16 * ks + 8)) : z4;
+      ks_tmem_st8(tl + 8 * ks, a, b);
+    }
+    asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+
   if (warp == 0) {
     if (lane == 0) {
-      mbar_arrive_expect_tx(wfull, nch * KS_CHUNK);
-      for (int i = 0; i < nch; ++i) tma_load_3d(wsm + i * KS_CHUNK, &tmW, wfull, (ch0 + i) * 64, dir * H + c * KS_UC, 0);
-      uint32_t phase = 0;                                      // bit st = parity of the next wait on empty[st]
       for (int s = 1; s < nsteps; ++s) {
         const int tp = dir ? (s - 1) : (T - s);                // frame whose dG this step consumes
         const unsigned int need = (unsigned int)KS_NCTA * (unsigned int)s;
@@ -138,14 +171,13 @@ lstm_bwd_ks_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
         while (ld_acquire(counter) < need) {
         }
         KS_STAMP(1);                                           // (proxy fence: writer side, before the CTA barrier)
+        // every chunk has a stage of its own: the copies go out back to back (the stage was consumed a step ago)
 #pragma unroll
         for (int i = 0; i < KS_MAXCH; ++i) {
           if (i < nch) {
-            const int st = i % KS_NS;
-            mbar_wait(&empty[st], ((phase >> st) & 1) ^ 1);
-            phase ^= 1u << st;
-            mbar_arrive_expect_tx(&full[st], KS_CHUNK);
-            tma_load_3d(ring + st * KS_CHUNK, &tmG, &full[st], dir * 4 * H + (ch0 + i) * 64, 0, tp * Bp);
+            mbar_wait(&empty[i], (s & 1));                     // = ((s - 1) & 1) ^ 1
+            mbar_arrive_expect_tx(&full[i], KS_CHUNK);
+            tma_load_3d(ring + i * KS_CHUNK, &tmG, &full[i], dir * 4 * H + (ch0 + i) * 64, 0, tp * Bp);
           }
         }
         // progress for stream-ordered consumers (ss_stream_wait_value32): the counter just observed covers the dG rows of
@@ -160,25 +192,20 @@ lstm_bwd_ks_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
   } else if (warp == 1) {
     if (lane == 0) {
       constexpr uint32_t idesc = umma_idesc_bf16(128, 128);
-      const uint64_t a_base = umma_desc_sw128(smem_u32(ring)), b_base = umma_desc_sw128(smem_u32(wsm));
-      mbar_wait(wfull, 0);
-      uint32_t phase = 0;
+      const uint64_t b_base = umma_desc_sw128(smem_u32(ring));
       for (int s = 1; s < nsteps; ++s) {
 #pragma unroll
         for (int i = 0; i < KS_MAXCH; ++i) {
           if (i < nch) {
-            const int st = i % KS_NS;
-            mbar_wait(&full[st], (phase >> st) & 1);
-            phase ^= 1u << st;
+            mbar_wait(&full[i], (s - 1) & 1);
             KS_STAMP(10 + i);
             tc_fence_after();
-            const uint64_t da = a_base + (uint32_t)(st * (KS_CHUNK >> 4));
             const uint64_t db = b_base + (uint32_t)(i * (KS_CHUNK >> 4));
             const bool last = ch0 + i == KS_KCH - 1;           // 32 valid columns: 2 k-steps
 #pragma unroll
             for (int k = 0; k < 4; ++k)
-              if (k < 2 || !last) umma_bf16(tmem_d, da + 2 * k, db + 2 * k, idesc, (i | k) ? 1u : 0u);
-            umma_commit(&empty[st]);
+              if (k < 2 || !last) ks_umma_ts(tmem_d + KS_DCOL, tmem_d + 8 * (4 * i + k), db + 2 * k, idesc, (i | k) ? 1u : 0u);
+            umma_commit(&empty[i]);
           }
         }
         umma_commit(accum_full);
@@ -187,17 +214,16 @@ lstm_bwd_ks_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
     }
   } else {
     const int ew = warp - 2;
-    const int q = warp & 3, dst = ew >> 2;                     // TMEM lane quadrant; peer this warp's columns go to
-    const int sb = 16 * q + (lane >> 1), half = lane & 1;      // sender role: batch row, which 8 of the 16 floats
+    const int q = warp & 3, cgp = ew >> 2;                     // TMEM lane quadrant = peer that finalises its 16 units; batch rows 16 cgp .. +15
+    const int pw = lane & 1;                                   // sender role: plane of this lane's W^T row (unit 16 q + lane / 2)
     const int fb = (ew & 1) * 32 + lane, u2 = ew >> 1;         // final role: batch row, unit pair
     const int ul = 2 * u2;                                     // unit within this CTA's 16
     const int ug = c * KS_UC + rank * KS_U + ul;               // unit within the direction
     const bool row_ok = fb < B && ug < H;
     const int len = row_ok ? p.lens[fb] : 0;
-    const uint32_t trow = tmem_d + ((uint32_t)(q * 32) << 16);
-    const uint32_t rbar = map_to_rank(smem_u32(rfull), (uint32_t)dst);
-    const uint32_t rdst = map_to_rank(smem_u32(rbuf), (uint32_t)dst) + (uint32_t)((rank * 64 + sb) * 64);
-    const int ssw = (sb >> 1) & 3, fsw = (fb >> 1) & 3;
+    const uint32_t trow = tmem_d + ((uint32_t)(q * 32) << 16) + KS_DCOL;
+    const uint32_t rbar = map_to_rank(smem_u32(rfull), (uint32_t)q);
+    const uint32_t rdst = map_to_rank(smem_u32(rbuf), (uint32_t)q) + (uint32_t)(((rank * KS_U + (lane >> 1)) * 64 + 16 * cgp + 8 * pw) * 4);
     float dc[2] = {0.0f, 0.0f};
     float dh0[2] = {0.0f, 0.0f};
     // running pointers of this thread's (row, unit pair): one add per step instead of 64-bit multiplies
@@ -234,33 +260,28 @@ lstm_bwd_ks_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
         if (threadIdx.x == 64) KS_STAMP(4);
         if (threadIdx.x == 64) KS_GSTAMP(0);
         tc_fence_after();
-        float v[16], e[16];
-        tmem_ld16(trow + 16 * dst, v);                         // x W_hi columns of the 16 units peer `dst` finalises
-        tmem_ld16(trow + 64 + 16 * dst, e);                    // x W_lo columns
+        float v[32];
+        tmem_ld32(trow + 32 * cgp, v);                         // this W^T row x dG rows (b = 16 cgp + i, plane): v[2 i + plane]
         tc_fence_before();
+        // W_hi . (dG_hi + dG_lo) in the even lane, W_lo . dG_hi in the odd one; their sum is the unit's partial dh
+        float sm[16];
 #pragma unroll
         for (int i = 0; i < 16; ++i) {
-          v[i] += e[i];
-          v[i] += __shfl_xor_sync(0xffffffffu, v[i], 1);       // lanes 2b, 2b+1 hold the hi / lo plane rows of b
+          const float a = pw ? v[2 * i] : v[2 * i] + v[2 * i + 1];
+          sm[i] = a + __shfl_xor_sync(0xffffffffu, a, 1);
         }
-        {
-          const float* w = v + 8 * half;
-          const uint32_t a0 = rdst + (uint32_t)(((2 * half) ^ ssw) * 16), a1 = rdst + (uint32_t)(((2 * half + 1) ^ ssw) * 16);
-          st_async_v4(a0, half ? v[8] : v[0], half ? v[9] : v[1], half ? v[10] : v[2], half ? v[11] : v[3], rbar);
-          st_async_v4(a1, half ? v[12] : v[4], half ? v[13] : v[5], half ? v[14] : v[6], half ? v[15] : v[7], rbar);
-          (void)w;
-        }
+        // each lane of the pair sends eight consecutive batch rows to the peer that finalises the unit
+        st_async_v4(rdst, pw ? sm[8] : sm[0], pw ? sm[9] : sm[1], pw ? sm[10] : sm[2], pw ? sm[11] : sm[3], rbar);
+        st_async_v4(rdst + 16, pw ? sm[12] : sm[4], pw ? sm[13] : sm[5], pw ? sm[14] : sm[6], pw ? sm[15] : sm[7], rbar);
         if (threadIdx.x == 64) KS_STAMP(5);
         while (!mbar_try_wait_cluster(rfull, (s - 1) & 1)) {
         }
         if (threadIdx.x == 64) KS_STAMP(6);
         if (threadIdx.x == 64) KS_GSTAMP(1);
-        const float* rb = rbuf + fb * 16 + (((u2 >> 1) ^ fsw) * 4) + (u2 & 1) * 2;
 #pragma unroll
         for (int r = 0; r < KS_CL; ++r) {
-          const float2 x = *reinterpret_cast<const float2*>(rb + r * 64 * 16);
-          dhr[0] += x.x;
-          dhr[1] += x.y;
+          dhr[0] += rbuf[(r * KS_U + ul) * 64 + fb];
+          dhr[1] += rbuf[(r * KS_U + ul + 1) * 64 + fb];
         }
       }
       // the row's forward pass started at frame 0 (dir 0) / len-1 (dir 1): one step later dh_rec is d(h0)
@@ -326,20 +347,13 @@ lstm_bwd_ks_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constan
   cluster_sync_all();                                          // nobody leaves while a peer may still address it
   if (warp == 1) {
     tc_fence_after();
-    tmem_free<128>(tmem_d);
+    tmem_free<KS_TMEM>(tmem_d);
   }
 }
 
 int launch_lstm_bwd_ks(const LstmBwdParams& p, const void* whhT, long long whhT_ld, long long whhT_plane, cudaStream_t st) {
   const int H = KS_H;
-  CUtensorMap tmW, tmG;
-  {
-    uint64_t dims[3] = {(uint64_t)4 * H, (uint64_t)2 * H, 2};
-    uint64_t str[2] = {(uint64_t)whhT_ld * 2, (uint64_t)whhT_plane * 2};
-    uint32_t box[3] = {64, KS_UC, 2};
-    int rc = make_tmap_bf16(&tmW, whhT, 3, dims, str, box);
-    if (rc) return rc;
-  }
+  CUtensorMap tmG;
   {  // (columns, plane, row): a box lands in shared memory as rows 2*b + plane
     uint64_t dims[3] = {(uint64_t)8 * H, 2, (uint64_t)p.T * p.Bp - (uint64_t)(p.Bp - p.B)};   // rows of THIS sub-batch's view
     uint64_t str[2] = {(uint64_t)p.dG_plane * 2, (uint64_t)8 * H * 2};
@@ -376,7 +390,7 @@ int launch_lstm_bwd_ks(const LstmBwdParams& p, const void* whhT, long long whhT_
               max_clusters[p.dbg ? 1 : 0], 2 * KS_NCL);
     return -2;
   }
-  cudaError_t e = cudaLaunchKernelEx(&cfg, kern, tmW, tmG, p);
+  cudaError_t e = cudaLaunchKernelEx(&cfg, kern, tmG, p, (const __nv_bfloat16*)whhT, whhT_ld, whhT_plane);
   if (e != cudaSuccess) {
     set_error("ss_lstm_bwd (K-split clusters): launch failed: %s", cudaGetErrorString(e));
     return -2;
