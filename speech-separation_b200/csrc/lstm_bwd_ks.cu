@@ -34,7 +34,9 @@ constexpr int KS_NS = KS_MAXCH;                         // dG stages: one per ch
 constexpr int KS_CHUNK = 16384;                         // one chunk of either operand: 128 rows x 128 B
 constexpr int KS_EPI_WARPS = 16;
 constexpr int KS_THREADS = 64 + 32 * KS_EPI_WARPS;
-constexpr int KS_RBUF = KS_CL * 64 * KS_U * 4;          // [src][16 units][64 batch rows] floats
+constexpr int KS_RP = 68;                               // floats per unit row of the reduction buffer (64 batch rows + bank skew)
+constexpr int KS_RBUF = KS_CL * KS_U * KS_RP * 4;       // [src][16 units][KS_RP] floats
+constexpr int KS_RTX = KS_CL * KS_U * 64 * 4;           // bytes a step's partial sums add up to
 constexpr int KS_SMEM = KS_NS * KS_CHUNK + KS_RBUF + 1024 + 256;
 constexpr int KS_TMEM = 512;                            // W^T slice in columns [0, 320), accumulator in [320, 448)
 constexpr int KS_DCOL = 320;
@@ -107,7 +109,7 @@ lstm_bwd_ks_kernel(const __grid_constant__ CUtensorMap tmG, LstmBwdParams p, con
   extern __shared__ unsigned char smem_raw[];
   unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   unsigned char* ring = smem;                                  // KS_NS chunks of dG_prev (stage i = chunk i of the step), rows = 2*b + plane
-  float* rbuf = reinterpret_cast<float*>(ring + KS_NS * KS_CHUNK);   // [src][unit 16][b 64]
+  float* rbuf = reinterpret_cast<float*>(ring + KS_NS * KS_CHUNK);   // [src][unit 16][KS_RP]
   uint64_t* full = reinterpret_cast<uint64_t*>(reinterpret_cast<unsigned char*>(rbuf) + KS_RBUF);
   uint64_t* empty = full + KS_NS;
   uint64_t* accum_full = empty + KS_NS;
@@ -216,14 +218,16 @@ lstm_bwd_ks_kernel(const __grid_constant__ CUtensorMap tmG, LstmBwdParams p, con
     const int ew = warp - 2;
     const int q = warp & 3, cgp = ew >> 2;                     // TMEM lane quadrant = peer that finalises its 16 units; batch rows 16 cgp .. +15
     const int pw = lane & 1;                                   // sender role: plane of this lane's W^T row (unit 16 q + lane / 2)
-    const int fb = (ew & 1) * 32 + lane, u2 = ew >> 1;         // final role: batch row, unit pair
+    // final role: lanes run along the 8 unit pairs of a batch row (4 rows per warp), so a warp's loads and stores cover
+    // whole sectors: 64 / 128 contiguous bytes per row instead of 32 scattered 8 / 16-byte transactions
+    const int fb = 4 * ew + (lane >> 3), u2 = lane & 7;        // batch row, unit pair
     const int ul = 2 * u2;                                     // unit within this CTA's 16
     const int ug = c * KS_UC + rank * KS_U + ul;               // unit within the direction
     const bool row_ok = fb < B && ug < H;
     const int len = row_ok ? p.lens[fb] : 0;
     const uint32_t trow = tmem_d + ((uint32_t)(q * 32) << 16) + KS_DCOL;
     const uint32_t rbar = map_to_rank(smem_u32(rfull), (uint32_t)q);
-    const uint32_t rdst = map_to_rank(smem_u32(rbuf), (uint32_t)q) + (uint32_t)(((rank * KS_U + (lane >> 1)) * 64 + 16 * cgp + 8 * pw) * 4);
+    const uint32_t rdst = map_to_rank(smem_u32(rbuf), (uint32_t)q) + (uint32_t)(((rank * KS_U + (lane >> 1)) * KS_RP + 16 * cgp + 8 * pw) * 4);
     float dc[2] = {0.0f, 0.0f};
     float dh0[2] = {0.0f, 0.0f};
     // running pointers of this thread's (row, unit pair): one add per step instead of 64-bit multiplies
@@ -240,7 +244,7 @@ lstm_bwd_ks_kernel(const __grid_constant__ CUtensorMap tmG, LstmBwdParams p, con
       const bool active = row_ok && in_range && t < len;
       float4 g4[2];
       float2 ct = make_float2(0.f, 0.f), cp = ct, dov = ct;
-      if (s > 0 && ew == 0 && lane == 0) mbar_arrive_expect_tx(rfull, KS_RBUF);
+      if (s > 0 && ew == 0 && lane == 0) mbar_arrive_expect_tx(rfull, KS_RTX);
       if (active) {
         const float4* gp = reinterpret_cast<const float4*>(gptr);
         g4[0] = gp[0];
@@ -280,8 +284,8 @@ lstm_bwd_ks_kernel(const __grid_constant__ CUtensorMap tmG, LstmBwdParams p, con
         if (threadIdx.x == 64) KS_GSTAMP(1);
 #pragma unroll
         for (int r = 0; r < KS_CL; ++r) {
-          dhr[0] += rbuf[(r * KS_U + ul) * 64 + fb];
-          dhr[1] += rbuf[(r * KS_U + ul + 1) * 64 + fb];
+          dhr[0] += rbuf[(r * KS_U + ul) * KS_RP + fb];
+          dhr[1] += rbuf[(r * KS_U + ul + 1) * KS_RP + fb];
         }
       }
       // the row's forward pass started at frame 0 (dir 0) / len-1 (dir 1): one step later dh_rec is d(h0)
