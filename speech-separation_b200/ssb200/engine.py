@@ -34,6 +34,12 @@ UNIT4 = 1
 STREAM = os.environ.get("SSB_STREAM", "1") != "0"
 N_CHUNKS = 8     # time chunks of a streamed GEMM
 FWD_STREAM_FRACTION = 0.64   # forward: stream the x-projection halves that are ready within this fraction of the recurrence
+# backward: a gated job whose inputs are only ready after this fraction of the recurrence runs AFTER it, on the main stream
+# at full width, instead of finishing late on the 68 idle SMs (first entry: layer 0, whose side stream starts with the
+# whole dW_ih of the layer above; second: the other layers)
+# Measured (configs[2], 3.1 ms recurrences): layer 0 cut at 1.0 / 0.6 / 0.45 / 0.3 -> 15.58 / 15.25 / 15.28 / 15.48 ms per step;
+# other layers 1.0 / 0.85 / 0.7 -> 15.28 / 15.35 / 15.61; forward 0.55 / 0.64 / 0.75 -> 15.38 / 15.28 / 15.60.
+BWD_STREAM_FRACTION = (0.6, 1.0)
 MIN_STREAM_T = 48
 SPLIT_WIDE_BATCH = True      # backward recurrence of 64 < B <= 128 as two half-batch launches of the K-split kernel
 GRAPH_REFRESH = os.environ.get("SSB_GRAPH_REFRESH", "1") != "0"
@@ -236,8 +242,9 @@ def _chunks(T, n):
 class _Streamer:
     """Side-stream jobs gated on the progress counters of the recurrence kernel that is running on the main stream."""
 
-    def __init__(self, ws, device, backward, nsteps, kernel_batch=None):
+    def __init__(self, ws, device, backward, nsteps, kernel_batch=None, cut=None):
         self.ws, self.device = ws, device
+        self.cut = cut
         self.side = _side_stream(device)
         self.flag0 = 2 if backward else 0
         # largest value the kernel is certain to report (include/ssb200.h: every 4th step, never the last ones)
@@ -259,7 +266,7 @@ class _Streamer:
         kernel (run_late)."""
         waits = tuple(waits) or ((0, 1),)
         ready = max(r for _, r in waits)
-        if ready <= self.max_reported:
+        if ready <= self.max_reported and (self.cut is None or ready <= self.cut):
             self.jobs.append((ready, order, waits, fn))
         else:
             self.late.append((ready, order, fn))
@@ -471,7 +478,7 @@ def backward(ws, wt, p, grads, mix, src, lens_dev, h0, c0, F, n_out, gout, dmask
         sj = None
         for hi_, (b0, b1) in enumerate(halves):
             if hi_ == len(halves) - 1 and stream:
-                sj = _Streamer(ws, dev, True, nsteps, b1 - b0)
+                sj = _Streamer(ws, dev, True, nsteps, b1 - b0, cut=int(BWD_STREAM_FRACTION[0 if l == 0 else 1] * nsteps))
             sub = lambda t: None if t is None else t[2 * l:2 * l + 2][:, b0:]      # [2][B][H] state tensors: entry b0
             call("lstm_bwd", ws.gx[l][b0:], ws.cs[l][b0:], sub(c0), dout[b0:], sub(dhn), sub(dcn), lens_dev[b0:],
                  wt.whhT[l].buf, LL(wt.whhT[l].ld), LL(wt.whhT[l].plane), _sb_view(ws.dG[l], b0).buf, LL(ws.dG[l].plane),
