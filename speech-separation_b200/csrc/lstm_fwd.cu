@@ -44,15 +44,13 @@ __device__ __forceinline__ uint32_t lf_pack(__nv_bfloat16 a, __nv_bfloat16 b) {
   return (uint32_t)__bfloat16_as_ushort(a) | ((uint32_t)__bfloat16_as_ushort(b) << 16);
 }
 
-// FAST: H = 600, B <= 64 (R = 64) -- the reference's shape; every loop bound is a constant so the single
-// MMA-issuing thread runs a fully unrolled instruction stream (its scalar overhead, not the tensor pipe, paced the
-// generic loop: tools/microbench/bulk_rate.cu).
-template <bool FAST, bool TRACE>
+// (The reference's shape, H = 600 and B <= 64, runs lstm_fwd_tw.cu; this kernel serves every other shape.)
+template <bool TRACE>
 __global__ void __launch_bounds__(LF_THREADS, 1)
 lstm_fwd_kernel(const __grid_constant__ CUtensorMap tmW, LstmFwdParams p) {
   extern __shared__ unsigned char smem_raw[];
   unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-  const int PR = FAST ? 64 : p.R, PKC = FAST ? 10 : p.KC, PNS = FAST ? 5 : p.NS;
+  const int PR = p.R, PKC = p.KC, PNS = p.NS;
   const int stage_bytes = 2 * PR * 128;
   // B <= 64: the A operand is ONE 128-row tile, rows [h_hi 0..31 | h_lo 0..31 | h_hi 32..63 | h_lo 32..63]: TMEM lane
   // quadrant 2 g + plane of D then belongs to batch rows 32 g .. 32 g + 31, and the two warps of a pair (hi / lo plane of
@@ -77,7 +75,7 @@ lstm_fwd_kernel(const __grid_constant__ CUtensorMap tmW, LstmFwdParams p) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int dir = blockIdx.x / p.NC, cta = blockIdx.x % p.NC;
   const int u0 = cta * LF_U;
-  const int T = p.T, B = p.B, H = FAST ? 600 : p.H;
+  const int T = p.T, B = p.B, H = p.H;
   const long long slot_elems = 2LL * PKC * stage_bytes / 2;   // bf16 elements of one slot (both directions)
   const long long dir_elems = (long long)PKC * stage_bytes / 2;
   // operand row of (plane, batch row) inside a chunk
@@ -120,7 +118,7 @@ lstm_fwd_kernel(const __grid_constant__ CUtensorMap tmW, LstmFwdParams p) {
 #pragma unroll
         for (int i = 0; i < PKC; ++i, ++it) {
           const int kc = i;
-          const int st = FAST ? i % 5 : it % PNS, ph = FAST ? (i / 5) & 1 : (it / PNS) & 1;
+          const int st = it % PNS, ph = (it / PNS) & 1;
           mbar_wait(&full[st], ph);
           LF_STAMP(i == 0 ? 3 : 10 + i);
           tc_fence_after();
@@ -167,7 +165,7 @@ lstm_fwd_kernel(const __grid_constant__ CUtensorMap tmW, LstmFwdParams p) {
       if (lane == 0) {
 #pragma unroll
         for (int i = 0; i < PKC; ++i, ++it) {
-          const int st = FAST ? i % 5 : it % PNS, ph = FAST ? (i / 5) & 1 : (it / PNS) & 1;
+          const int st = it % PNS, ph = (it / PNS) & 1;
           mbar_wait(&empty[st], ph ^ 1);
           mbar_arrive_expect_tx(&full[st], stage_bytes);
           bulk_load(ring + st * stage_bytes, src + (long long)i * (stage_bytes / 2), stage_bytes, &full[st]);
@@ -460,10 +458,7 @@ extern "C" int ss_lstm_fwd(float* gx, const void* whh_r, long long whh_ld, long 
     if (rc) return rc;
   }
   const int smem = p.NS * 2 * p.R * 128 + p.KC * LF_WCHUNK + 64 * LF_XPITCH * 4 + 1024 + 256 + LF_STAGE_TILES;
-  const bool fast = H == 600 && p.R == 64;
-  const bool trace = p.dbg != nullptr;
-  void* kern = fast ? (trace ? (void*)lstm_fwd_kernel<true, true> : (void*)lstm_fwd_kernel<true, false>)
-                    : (trace ? (void*)lstm_fwd_kernel<false, true> : (void*)lstm_fwd_kernel<false, false>);
+  void* kern = p.dbg ? (void*)lstm_fwd_kernel<true> : (void*)lstm_fwd_kernel<false>;
   cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
   void* args[] = {(void*)&tmW, (void*)&p};
   cudaError_t e = cudaLaunchCooperativeKernel(kern, dim3(2 * p.NC), dim3(LF_THREADS), args, smem, st);
