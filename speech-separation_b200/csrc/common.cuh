@@ -23,10 +23,10 @@ int sm_count();                                // SMs of the current device (cac
 
 static inline int cdiv(long long a, long long b) { return (int)((a + b - 1) / b); }
 
-// Host helper (api.cu): encode a tiled tensor map over bf16 data with 128B swizzle.
+// Host helper (api.cu): encode a tiled tensor map over bf16 data with 128B swizzle (or none).
 // dims/strides innermost first; strides in bytes for dims 1..rank-1.
 int make_tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t* dims,
-                   const uint64_t* strides_bytes, const uint32_t* box);
+                   const uint64_t* strides_bytes, const uint32_t* box, bool swizzle128 = true);
 
 // stft_generic.cu: direct-summation STFT / masked iSTFT for the sizes the packed-FFT kernels do not cover
 int launch_stft_generic(const float* sig, const long long* sig_off, const long long* frame_off, const int* tile_off,

@@ -37,7 +37,8 @@ constexpr int KS_THREADS = 64 + 32 * KS_EPI_WARPS;
 constexpr int KS_RP = 68;                               // floats per unit row of the reduction buffer (64 batch rows + bank skew)
 constexpr int KS_RBUF = KS_CL * KS_U * KS_RP * 4;       // [src][16 units][KS_RP] floats
 constexpr int KS_RTX = KS_CL * KS_U * 64 * 4;           // bytes a step's partial sums add up to
-constexpr int KS_SMEM = KS_NS * KS_CHUNK + KS_RBUF + 1024 + 256;
+constexpr int KS_DGT = 64 * 2 * 128;                    // staging tile of this CTA's dG block: [row 2 b + plane][64 columns] bf16
+constexpr int KS_SMEM = KS_NS * KS_CHUNK + KS_DGT + KS_RBUF + 1024 + 256;
 constexpr int KS_TMEM = 512;                            // W^T slice in columns [0, 320), accumulator in [320, 448)
 constexpr int KS_DCOL = 320;
 
@@ -87,6 +88,15 @@ __device__ __forceinline__ void ks_tmem_st8(uint32_t taddr, uint4 a, uint4 b) {
                : "memory");
 }
 
+// tile in shared memory -> a box of the dG tensor (async proxy), as one bulk group
+__device__ __forceinline__ void ks_tma_store_3d(const CUtensorMap* m, const void* src, int c0, int c1, int c2) {
+  asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];" ::"l"((uint64_t)m),
+               "r"(smem_u32(src)), "r"(c0), "r"(c1), "r"(c2)
+               : "memory");
+  asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+}
+__device__ __forceinline__ void ks_tma_store_wait() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+
 // all-CTA skew probe (DBG only): globaltimer of 4 events for steps 100..115 behind the per-step rows of CTA 0
 #define KS_GSTAMP(ev)                                                                                              \
   do {                                                                                                             \
@@ -104,12 +114,14 @@ __device__ __forceinline__ void ks_tmem_st8(uint32_t taddr, uint4 a, uint4 b) {
 
 template <bool DBG>
 __global__ void __launch_bounds__(KS_THREADS, 1)
-lstm_bwd_ks_kernel(const __grid_constant__ CUtensorMap tmG, LstmBwdParams p, const __nv_bfloat16* __restrict__ whhT,
+lstm_bwd_ks_kernel(const __grid_constant__ CUtensorMap tmG, const __grid_constant__ CUtensorMap tmS64,
+                   const __grid_constant__ CUtensorMap tmS32, LstmBwdParams p, const __nv_bfloat16* __restrict__ whhT,
                    long long whhT_ld, long long whhT_plane) {
   extern __shared__ unsigned char smem_raw[];
   unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   unsigned char* ring = smem;                                  // KS_NS chunks of dG_prev (stage i = chunk i of the step), rows = 2*b + plane
-  float* rbuf = reinterpret_cast<float*>(ring + KS_NS * KS_CHUNK);   // [src][unit 16][KS_RP]
+  unsigned char* dgt = ring + KS_NS * KS_CHUNK;                // this step's dG block, staged for ONE tensor store
+  float* rbuf = reinterpret_cast<float*>(dgt + KS_DGT);        // [src][unit 16][KS_RP]
   uint64_t* full = reinterpret_cast<uint64_t*>(reinterpret_cast<unsigned char*>(rbuf) + KS_RBUF);
   uint64_t* empty = full + KS_NS;
   uint64_t* accum_full = empty + KS_NS;
@@ -129,6 +141,8 @@ lstm_bwd_ks_kernel(const __grid_constant__ CUtensorMap tmG, LstmBwdParams p, con
 
   if (threadIdx.x == 0) {
     tma_prefetch_desc(&tmG);
+    tma_prefetch_desc(&tmS64);
+    tma_prefetch_desc(&tmS32);
     for (int s = 0; s < KS_NS; ++s) {
       mbar_init(&full[s], 1);
       mbar_init(&empty[s], 1);
@@ -228,6 +242,9 @@ lstm_bwd_ks_kernel(const __grid_constant__ CUtensorMap tmG, LstmBwdParams p, con
     const uint32_t trow = tmem_d + ((uint32_t)(q * 32) << 16) + KS_DCOL;
     const uint32_t rbar = map_to_rank(smem_u32(rfull), (uint32_t)q);
     const uint32_t rdst = map_to_rank(smem_u32(rbuf), (uint32_t)q) + (uint32_t)(((rank * KS_U + (lane >> 1)) * KS_RP + 16 * cgp + 8 * pw) * 4);
+    const int nvalid = max(0, min(KS_U, H - (c * KS_UC + rank * KS_U)));   // units of this CTA that exist: 16, 8 (last cluster, rank 1) or 0
+    const uint32_t tile_pitch = nvalid == KS_U ? 128u : 64u;                // bytes per (row, plane) of the staged block
+    const uint32_t dgt_u32 = smem_u32(dgt);
     float dc[2] = {0.0f, 0.0f};
     float dh0[2] = {0.0f, 0.0f};
     // running pointers of this thread's (row, unit pair): one add per step instead of 64-bit multiplies
@@ -236,7 +253,6 @@ lstm_bwd_ks_kernel(const __grid_constant__ CUtensorMap tmG, LstmBwdParams p, con
     const float* gptr = p.gates + row0 * (8LL * H) + (long long)dir * 4 * H + 4 * ug;
     const float* cptr = p.cs + row0 * (2LL * H) + dir * H + ug;
     const float* dptr = p.dout + row0 * (2LL * H) + dir * H + ug;
-    __nv_bfloat16* optr = p.dG + row0 * (8LL * H) + (long long)dir * 4 * H + 4 * ug;
     const float* c0ptr = p.c0 + ((long long)dir * Bp + (row_ok ? fb : 0)) * H + ug;
     for (int s = 0; s < nsteps; ++s) {
       const int t = dir ? s : (T - 1 - s);                     // t == -1 / T on the extra step
@@ -320,21 +336,33 @@ lstm_bwd_ks_kernel(const __grid_constant__ CUtensorMap tmG, LstmBwdParams p, con
       __nv_bfloat16 hi[8], lo[8];
 #pragma unroll
       for (int i = 0; i < 8; ++i) split_bf16(dgv[i], hi[i], lo[i]);
-      if (row_ok && in_range) {
-        *reinterpret_cast<uint4*>(optr) = *reinterpret_cast<uint4*>(hi);
-        *reinterpret_cast<uint4*>(optr + p.dG_plane) = *reinterpret_cast<uint4*>(lo);
+      // The CTA's dG block of the step (B rows x 2 planes x 64 columns) is staged in shared memory and leaves as ONE tensor
+      // store: written by the async proxy it needs no proxy fence before the consumers' TMA loads, and the 512 threads
+      // wait for no store acknowledgement (their stores + fence were 1.3k cycles of the step).  Units >= H (last cluster)
+      // have no columns: that CTA stores a 32-column box or nothing.
+      if (fb < B && in_range && 2 * u2 < nvalid) {
+        const uint32_t a = dgt_u32 + (uint32_t)(2 * fb) * tile_pitch + (uint32_t)u2 * 16u;
+        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(reinterpret_cast<uint32_t*>(hi)[0]),
+                     "r"(reinterpret_cast<uint32_t*>(hi)[1]), "r"(reinterpret_cast<uint32_t*>(hi)[2]), "r"(reinterpret_cast<uint32_t*>(hi)[3])
+                     : "memory");
+        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a + tile_pitch), "r"(reinterpret_cast<uint32_t*>(lo)[0]),
+                     "r"(reinterpret_cast<uint32_t*>(lo)[1]), "r"(reinterpret_cast<uint32_t*>(lo)[2]), "r"(reinterpret_cast<uint32_t*>(lo)[3])
+                     : "memory");
       }
       gptr += rstep * (8LL * H);
       cptr += rstep * (2LL * H);
       dptr += rstep * (2LL * H);
-      optr += rstep * (8LL * H);
-      fence_proxy_async();                                     // this thread's dG stores -> the consumers' TMA reads
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // this thread's tile stores -> the tensor store below
       if (threadIdx.x == 64) KS_STAMP(7);
       if (threadIdx.x == 64) KS_GSTAMP(2);
       asm volatile("bar.sync 1, %0;" ::"n"(32 * KS_EPI_WARPS) : "memory");
       if (threadIdx.x == 64) {
         KS_STAMP(8);
-        red_release_add(counter, 1u);     // cumulative over the CTA's stores ordered before the bar.sync
+        if (in_range && nvalid > 0) {
+          ks_tma_store_3d(nvalid == KS_U ? &tmS64 : &tmS32, dgt, dir * 4 * H + 4 * (c * KS_UC + rank * KS_U), 0, t * Bp);
+          ks_tma_store_wait();                                 // the block is in global memory (and the tile reusable)
+        }
+        red_release_add(counter, 1u);
         KS_STAMP(9);
         KS_GSTAMP(3);
       }
@@ -363,6 +391,14 @@ int launch_lstm_bwd_ks(const LstmBwdParams& p, const void* whhT, long long whhT_
     uint64_t str[2] = {(uint64_t)p.dG_plane * 2, (uint64_t)8 * H * 2};
     uint32_t box[3] = {64, 2, 64};
     int rc = make_tmap_bf16(&tmG, p.dG, 3, dims, str, box);
+    if (rc) return rc;
+  }
+  CUtensorMap tmS64, tmS32;   // the same tensor, boxes of B rows x 2 planes x (64 | 32) columns, no swizzle: the CTAs' stores
+  for (int v = 0; v < 2; ++v) {
+    uint64_t dims[3] = {(uint64_t)8 * H, 2, (uint64_t)p.T * p.Bp - (uint64_t)(p.Bp - p.B)};
+    uint64_t str[2] = {(uint64_t)p.dG_plane * 2, (uint64_t)8 * H * 2};
+    uint32_t box[3] = {v ? 32u : 64u, 2, (uint32_t)p.B};
+    int rc = make_tmap_bf16(v ? &tmS32 : &tmS64, p.dG, 3, dims, str, box, false);
     if (rc) return rc;
   }
   auto kern = p.dbg ? lstm_bwd_ks_kernel<true> : lstm_bwd_ks_kernel<false>;
@@ -394,7 +430,7 @@ int launch_lstm_bwd_ks(const LstmBwdParams& p, const void* whhT, long long whhT_
               max_clusters[p.dbg ? 1 : 0], 2 * KS_NCL);
     return -2;
   }
-  cudaError_t e = cudaLaunchKernelEx(&cfg, kern, tmG, p, (const __nv_bfloat16*)whhT, whhT_ld, whhT_plane);
+  cudaError_t e = cudaLaunchKernelEx(&cfg, kern, tmG, tmS64, tmS32, p, (const __nv_bfloat16*)whhT, whhT_ld, whhT_plane);
   if (e != cudaSuccess) {
     set_error("ss_lstm_bwd (K-split clusters): launch failed: %s", cudaGetErrorString(e));
     return -2;
