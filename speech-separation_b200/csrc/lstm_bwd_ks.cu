@@ -36,7 +36,6 @@ constexpr int KS_EPI_WARPS = 16;
 constexpr int KS_THREADS = 64 + 32 * KS_EPI_WARPS;
 constexpr int KS_RP = 68;                               // floats per unit row of the reduction buffer (64 batch rows + bank skew)
 constexpr int KS_RBUF = KS_CL * KS_U * KS_RP * 4;       // [src][16 units][KS_RP] floats
-constexpr int KS_RTX = KS_CL * KS_U * 64 * 4;           // bytes a step's partial sums add up to
 constexpr int KS_DGT = 64 * 2 * 128;                    // staging tile of this CTA's dG block: [row 2 b + plane][64 columns] bf16
 constexpr int KS_SMEM = KS_NS * KS_CHUNK + KS_DGT + KS_RBUF + 1024 + 256;
 constexpr int KS_TMEM = 512;                            // W^T slice in columns [0, 320), accumulator in [320, 448)
@@ -112,7 +111,9 @@ __device__ __forceinline__ void ks_tma_store_wait() { asm volatile("cp.async.bul
     if (DBG && blockIdx.x == 0) p.dbg[s * 32 + (slot)] = clock64();    \
   } while (0)
 
-template <bool DBG>
+// RB = batch rows of the dG boxes (16, 32 or 64 >= B): small batches of long utterances (configs[4]) move a quarter of
+// the operand per step and multiply N = 32 instead of 128 columns.
+template <int RB, bool DBG>
 __global__ void __launch_bounds__(KS_THREADS, 1)
 lstm_bwd_ks_kernel(const __grid_constant__ CUtensorMap tmG, const __grid_constant__ CUtensorMap tmS64,
                    const __grid_constant__ CUtensorMap tmS32, LstmBwdParams p, const __nv_bfloat16* __restrict__ whhT,
@@ -120,6 +121,7 @@ lstm_bwd_ks_kernel(const __grid_constant__ CUtensorMap tmG, const __grid_constan
   extern __shared__ unsigned char smem_raw[];
   unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   unsigned char* ring = smem;                                  // KS_NS chunks of dG_prev (stage i = chunk i of the step), rows = 2*b + plane
+  constexpr int STAGE = 2 * RB * 128;                          // one dG box: rows 2 * b + plane, 64 columns
   unsigned char* dgt = ring + KS_NS * KS_CHUNK;                // this step's dG block, staged for ONE tensor store
   float* rbuf = reinterpret_cast<float*>(dgt + KS_DGT);        // [src][unit 16][KS_RP]
   uint64_t* full = reinterpret_cast<uint64_t*>(reinterpret_cast<unsigned char*>(rbuf) + KS_RBUF);
@@ -192,8 +194,8 @@ lstm_bwd_ks_kernel(const __grid_constant__ CUtensorMap tmG, const __grid_constan
         for (int i = 0; i < KS_MAXCH; ++i) {
           if (i < nch) {
             mbar_wait(&empty[i], (s & 1));                     // = ((s - 1) & 1) ^ 1
-            mbar_arrive_expect_tx(&full[i], KS_CHUNK);
-            tma_load_3d(ring + i * KS_CHUNK, &tmG, &full[i], dir * 4 * H + (ch0 + i) * 64, 0, tp * Bp);
+            mbar_arrive_expect_tx(&full[i], STAGE);
+            tma_load_3d(ring + i * STAGE, &tmG, &full[i], dir * 4 * H + (ch0 + i) * 64, 0, tp * Bp);
           }
         }
         // progress for stream-ordered consumers (ss_stream_wait_value32): the counter just observed covers the dG rows of
@@ -207,7 +209,7 @@ lstm_bwd_ks_kernel(const __grid_constant__ CUtensorMap tmG, const __grid_constan
     }
   } else if (warp == 1) {
     if (lane == 0) {
-      constexpr uint32_t idesc = umma_idesc_bf16(128, 128);
+      constexpr uint32_t idesc = umma_idesc_bf16(128, 2 * RB);
       const uint64_t b_base = umma_desc_sw128(smem_u32(ring));
       for (int s = 1; s < nsteps; ++s) {
 #pragma unroll
@@ -216,7 +218,7 @@ lstm_bwd_ks_kernel(const __grid_constant__ CUtensorMap tmG, const __grid_constan
             mbar_wait(&full[i], (s - 1) & 1);
             KS_STAMP(10 + i);
             tc_fence_after();
-            const uint64_t db = b_base + (uint32_t)(i * (KS_CHUNK >> 4));
+            const uint64_t db = b_base + (uint32_t)(i * (STAGE >> 4));
             const bool last = ch0 + i == KS_KCH - 1;           // 32 valid columns: 2 k-steps
 #pragma unroll
             for (int k = 0; k < 4; ++k)
@@ -260,7 +262,7 @@ lstm_bwd_ks_kernel(const __grid_constant__ CUtensorMap tmG, const __grid_constan
       const bool active = row_ok && in_range && t < len;
       float4 g4[2];
       float2 ct = make_float2(0.f, 0.f), cp = ct, dov = ct;
-      if (s > 0 && ew == 0 && lane == 0) mbar_arrive_expect_tx(rfull, KS_RTX);
+      if (s > 0 && ew == 0 && lane == 0) mbar_arrive_expect_tx(rfull, KS_CL * KS_U * RB * 4);
       if (active) {
         const float4* gp = reinterpret_cast<const float4*>(gptr);
         g4[0] = gp[0];
@@ -280,6 +282,7 @@ lstm_bwd_ks_kernel(const __grid_constant__ CUtensorMap tmG, const __grid_constan
         if (threadIdx.x == 64) KS_STAMP(4);
         if (threadIdx.x == 64) KS_GSTAMP(0);
         tc_fence_after();
+        if (16 * cgp < RB) {                                   // (warp-uniform) column groups past the padded batch have no columns
         float v[32];
         tmem_ld32(trow + 32 * cgp, v);                         // this W^T row x dG rows (b = 16 cgp + i, plane): v[2 i + plane]
         tc_fence_before();
@@ -293,6 +296,7 @@ lstm_bwd_ks_kernel(const __grid_constant__ CUtensorMap tmG, const __grid_constan
         // each lane of the pair sends eight consecutive batch rows to the peer that finalises the unit
         st_async_v4(rdst, pw ? sm[8] : sm[0], pw ? sm[9] : sm[1], pw ? sm[10] : sm[2], pw ? sm[11] : sm[3], rbar);
         st_async_v4(rdst + 16, pw ? sm[12] : sm[4], pw ? sm[13] : sm[5], pw ? sm[14] : sm[6], pw ? sm[15] : sm[7], rbar);
+        }
         if (threadIdx.x == 64) KS_STAMP(5);
         while (!mbar_try_wait_cluster(rfull, (s - 1) & 1)) {
         }
@@ -385,11 +389,12 @@ lstm_bwd_ks_kernel(const __grid_constant__ CUtensorMap tmG, const __grid_constan
 
 int launch_lstm_bwd_ks(const LstmBwdParams& p, const void* whhT, long long whhT_ld, long long whhT_plane, cudaStream_t st) {
   const int H = KS_H;
+  const int rb = p.B <= 16 ? 16 : p.B <= 32 ? 32 : 64;
   CUtensorMap tmG;
   {  // (columns, plane, row): a box lands in shared memory as rows 2*b + plane
     uint64_t dims[3] = {(uint64_t)8 * H, 2, (uint64_t)p.T * p.Bp - (uint64_t)(p.Bp - p.B)};   // rows of THIS sub-batch's view
     uint64_t str[2] = {(uint64_t)p.dG_plane * 2, (uint64_t)8 * H * 2};
-    uint32_t box[3] = {64, 2, 64};
+    uint32_t box[3] = {64, 2, (uint32_t)rb};
     int rc = make_tmap_bf16(&tmG, p.dG, 3, dims, str, box);
     if (rc) return rc;
   }
@@ -401,7 +406,9 @@ int launch_lstm_bwd_ks(const LstmBwdParams& p, const void* whhT, long long whhT_
     int rc = make_tmap_bf16(v ? &tmS32 : &tmS64, p.dG, 3, dims, str, box, false);
     if (rc) return rc;
   }
-  auto kern = p.dbg ? lstm_bwd_ks_kernel<true> : lstm_bwd_ks_kernel<false>;
+  auto kern = rb == 16 ? (p.dbg ? lstm_bwd_ks_kernel<16, true> : lstm_bwd_ks_kernel<16, false>)
+            : rb == 32 ? (p.dbg ? lstm_bwd_ks_kernel<32, true> : lstm_bwd_ks_kernel<32, false>)
+                       : (p.dbg ? lstm_bwd_ks_kernel<64, true> : lstm_bwd_ks_kernel<64, false>);
   cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, KS_SMEM);
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(2 * KS_NCTA);
@@ -419,7 +426,7 @@ int launch_lstm_bwd_ks(const LstmBwdParams& p, const void* whhT, long long whhT_
   // here instead of asking for a cooperative launch: Nsight Compute cannot replay a launch that is both cooperative
   // and clustered, and work that already occupies SMs (the flag-gated GEMMs of the side stream) always finishes on
   // its own, so late CTAs only wait.
-  static int max_clusters[2] = {-1, -1};
+  static int max_clusters[2] = {-1, -1};   // (the three row variants use the same resources)
   if (max_clusters[p.dbg ? 1 : 0] < 0) {
     int n = 0;
     if (cudaOccupancyMaxActiveClusters(&n, kern, &cfg) != cudaSuccess) n = 0;

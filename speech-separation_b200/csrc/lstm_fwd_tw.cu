@@ -24,7 +24,7 @@ namespace ssb {
 constexpr int TW_THREADS = 512;             // 16 warps: warp % 4 < 3 epilogue (TMEM lane quadrants 0..2), warp % 4 == 3 roles
 constexpr int TW_EPI = 384;
 constexpr int TW_KC = 10, TW_KSTEPS = 38;   // 64-wide chunks / 16-wide k-steps of K = 600
-constexpr int TW_STAGE = 16384;             // one chunk: 128 operand rows x 128 B
+constexpr int TW_STAGE = 16384;             // one chunk at RB = 64: 128 operand rows x 128 B (RB = 16 / 32: a quarter / half)
 constexpr int TW_CPC = 2;                   // chunks per bulk copy: a copy costs the engine ~280 cycles whether it moves 16 or 32 KB
 constexpr int TW_NCOPY = TW_KC / TW_CPC;
 constexpr int TW_TMEM = 512;
@@ -59,14 +59,17 @@ struct LstmFwdTwParams {
   long long whh_ld, whh_plane;
 };
 
-template <bool TRACE>
+// RB = padded batch rows of the exchanged operand (16, 32 or 64 >= B): a batch of 8 twenty-second utterances (configs[4])
+// moves 40 KB instead of 160 KB of h per step and multiplies N = 32 instead of 128 columns.
+template <int RB, bool TRACE>
 __global__ void __launch_bounds__(TW_THREADS, 1) lstm_fwd_tw_kernel(LstmFwdTwParams pp) {
+  constexpr int STAGE = 2 * RB * 128;                          // one K chunk of the operand: rows [h_hi 0..RB) | h_lo 0..RB)]
   const LstmFwdParams& p = pp.p;
   extern __shared__ unsigned char smem_raw[];
   unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   constexpr int H = 600;
   unsigned char* ring = smem;                                  // stage i = K chunk i of the step
-  float* xbuf = reinterpret_cast<float*>(ring + TW_KC * TW_STAGE);         // [64][LF_XPITCH] activated gates of the step
+  float* xbuf = reinterpret_cast<float*>(ring + TW_KC * STAGE);         // [64][LF_XPITCH] activated gates of the step
   uint64_t* full = reinterpret_cast<uint64_t*>(xbuf + 64 * LF_XPITCH);     // [10] chunk landed
   uint64_t* empty = full + 10;                                 // [10] chunk consumed (MMA commit)
   uint64_t* accum_full = empty + 10;
@@ -81,7 +84,7 @@ __global__ void __launch_bounds__(TW_THREADS, 1) lstm_fwd_tw_kernel(LstmFwdTwPar
   const int dir = blockIdx.x / p.NC, cta = blockIdx.x % p.NC;
   const int u0 = cta * LF_U;
   const int T = p.T, B = p.B;
-  const long long slot_elems = 2LL * TW_KC * (TW_STAGE / 2), dir_elems = (long long)TW_KC * (TW_STAGE / 2);
+  const long long slot_elems = 2LL * TW_KC * (STAGE / 2), dir_elems = (long long)TW_KC * (STAGE / 2);
   unsigned int* counter = p.done + 128 + dir;
 
   if (threadIdx.x == 0) {
@@ -121,7 +124,7 @@ __global__ void __launch_bounds__(TW_THREADS, 1) lstm_fwd_tw_kernel(LstmFwdTwPar
 
   if (warp == W_MMA) {
     if (lane == 0) {
-      constexpr uint32_t idesc = umma_idesc_bf16(128, 128);
+      constexpr uint32_t idesc = umma_idesc_bf16(128, 2 * RB);
       const uint64_t b_base = umma_desc_sw128(smem_u32(ring));
       for (int s = 0; s < T; ++s) {
 #pragma unroll
@@ -131,7 +134,7 @@ __global__ void __launch_bounds__(TW_THREADS, 1) lstm_fwd_tw_kernel(LstmFwdTwPar
             TW_STAMP(i == 0 ? 3 : 10 + i);
             tc_fence_after();
           }
-          const uint64_t db = b_base + (uint32_t)i * (TW_STAGE >> 4);
+          const uint64_t db = b_base + (uint32_t)i * (STAGE >> 4);
 #pragma unroll
           for (int k = 0; k < 4; ++k)
             if (4 * i + k < TW_KSTEPS) umma_bf16_ts(tmem + TW_DCOL, tmem + 8 * (4 * i + k), db + 2 * k, idesc, (i | k) ? 1u : 0u);
@@ -163,8 +166,8 @@ __global__ void __launch_bounds__(TW_THREADS, 1) lstm_fwd_tw_kernel(LstmFwdTwPar
 #pragma unroll
         for (int i = 0; i < TW_NCOPY; ++i) {
           mbar_wait(&empty[i], (s & 1) ^ 1);
-          mbar_arrive_expect_tx(&full[i], TW_CPC * TW_STAGE);
-          bulk_load(ring + i * TW_CPC * TW_STAGE, src + (long long)i * TW_CPC * (TW_STAGE / 2), TW_CPC * TW_STAGE, &full[i]);
+          mbar_arrive_expect_tx(&full[i], TW_CPC * STAGE);
+          bulk_load(ring + i * TW_CPC * STAGE, src + (long long)i * TW_CPC * (STAGE / 2), TW_CPC * STAGE, &full[i]);
           if (TRACE) TW_STAMP(20 + i);
         }
         TW_STAMP(2);
@@ -203,11 +206,13 @@ __global__ void __launch_bounds__(TW_THREADS, 1) lstm_fwd_tw_kernel(LstmFwdTwPar
     c[0] = ok0 ? p.c0[((long long)dir * B + b0) * H + u] : 0.0f;
     c[1] = ok1 ? p.c0[((long long)dir * B + b0 + 1) * H + u] : 0.0f;
     // coalesced stores: epilogue thread -> (operand row, 8-byte part) of the 128 x 24-byte tile this CTA publishes
-    const int st_row = eidx / 3, st_part = eidx % 3;
+    const int st_row = eidx / 3, st_part = eidx % 3;            // (tile row plane * 64 + b, 8-byte part) of the staged tiles
+    const int pub_row = (st_row >> 6) * RB + (st_row & 63);    // its operand row; published if b < RB
+    const bool pub = (st_row & 63) < RB;
     long long st_off;
     {
       const int uu = u0 + st_part * 4, k = uu & 63;
-      st_off = dir * dir_elems + (long long)(uu >> 6) * (TW_STAGE / 2) + st_row * 64 + ((((k >> 3) ^ (st_row & 7)) << 3) | (k & 7));
+      st_off = dir * dir_elems + (long long)(uu >> 6) * (STAGE / 2) + pub_row * 64 + ((((k >> 3) ^ (pub_row & 7)) << 3) | (k & 7));
     }
     auto stage_h = [&](uint16_t* tile, const float* hv) {      // rows: hi plane 0..63, lo plane 64..127
       __nv_bfloat16 hi, lo;
@@ -220,8 +225,10 @@ __global__ void __launch_bounds__(TW_THREADS, 1) lstm_fwd_tw_kernel(LstmFwdTwPar
     };
     auto publish = [&](int slot) {                             // hst -> exchange buffer, one release per CTA
       asm volatile("bar.sync 6, %0;" ::"n"(TW_EPI) : "memory");
-      const uint2 v = reinterpret_cast<const uint2*>(hst)[st_row * 4 + st_part];
-      tw_st_strong64(p.hbuf + slot * slot_elems + st_off, v.x, v.y);
+      if (pub) {
+        const uint2 v = reinterpret_cast<const uint2*>(hst)[st_row * 4 + st_part];
+        tw_st_strong64(p.hbuf + slot * slot_elems + st_off, v.x, v.y);
+      }
       asm volatile("bar.sync 9, %0;" ::"n"(TW_EPI) : "memory");
       if (eidx == 0) red_release_add(counter, 1u);             // cumulative over the CTA's stores ordered before the bar.sync
     };
@@ -246,8 +253,13 @@ __global__ void __launch_bounds__(TW_THREADS, 1) lstm_fwd_tw_kernel(LstmFwdTwPar
       }
       tc_fence_after();
       float d[16], e[16];
-      tmem_ld16(trow + 16 * cgp, d);                           // W row x h_hi of batch rows 16 cgp ..
-      tmem_ld16(trow + 64 + 16 * cgp, e);                      // W row x h_lo
+      if (16 * cgp < RB) {                                     // (warp-uniform) column groups past the padded batch have no columns
+        tmem_ld16(trow + 16 * cgp, d);                         // W row x h_hi of batch rows 16 cgp ..
+        tmem_ld16(trow + RB + 16 * cgp, e);                    // W row x h_lo
+      } else {
+#pragma unroll
+        for (int i = 0; i < 16; ++i) d[i] = e[i] = 0.0f;
+      }
       tc_fence_before();
       // hi / lo planes of W are neighbouring lanes: W_hi.(h_hi + h_lo) + W_lo.h_hi
 #pragma unroll
@@ -347,6 +359,8 @@ __global__ void __launch_bounds__(TW_THREADS, 1) lstm_fwd_tw_kernel(LstmFwdTwPar
   }
 }
 
+int tw_rows(int B) { return B <= 16 ? 16 : B <= 32 ? 32 : 64; }
+
 // called by ss_lstm_fwd (lstm_fwd.cu) for H = 600, B <= 64
 int launch_lstm_fwd_tw(const LstmFwdParams& p, const void* whh_r, long long whh_ld, long long whh_plane, cudaStream_t st) {
   LstmFwdTwParams pp;
@@ -354,10 +368,15 @@ int launch_lstm_fwd_tw(const LstmFwdParams& p, const void* whh_r, long long whh_
   pp.whh = (const __nv_bfloat16*)whh_r;
   pp.whh_ld = whh_ld;
   pp.whh_plane = whh_plane;
-  void* kern = p.dbg ? (void*)lstm_fwd_tw_kernel<true> : (void*)lstm_fwd_tw_kernel<false>;
-  cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, TW_SMEM);
+  const int rb = tw_rows(p.B);
+  void* kern;
+  if (rb == 16) kern = p.dbg ? (void*)lstm_fwd_tw_kernel<16, true> : (void*)lstm_fwd_tw_kernel<16, false>;
+  else if (rb == 32) kern = p.dbg ? (void*)lstm_fwd_tw_kernel<32, true> : (void*)lstm_fwd_tw_kernel<32, false>;
+  else kern = p.dbg ? (void*)lstm_fwd_tw_kernel<64, true> : (void*)lstm_fwd_tw_kernel<64, false>;
+  const int smem = TW_KC * 2 * rb * 128 + 64 * LF_XPITCH * 4 + 256 + LF_STAGE_TILES + 1024;
+  cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
   void* args[] = {(void*)&pp};
-  cudaError_t e = cudaLaunchCooperativeKernel(kern, dim3(2 * p.NC), dim3(TW_THREADS), args, TW_SMEM, st);
+  cudaError_t e = cudaLaunchCooperativeKernel(kern, dim3(2 * p.NC), dim3(TW_THREADS), args, smem, st);
   if (e != cudaSuccess) {
     set_error("ss_lstm_fwd: cooperative launch failed: %s", cudaGetErrorString(e));
     return -2;
