@@ -20,7 +20,7 @@
 extern "C" {
 #endif
 
-#define SSB200_VERSION 2
+#define SSB200_VERSION 3
 
 /* ---- library ---- */
 const char* ss_last_error(void);
@@ -177,10 +177,10 @@ int ss_masks_to_ragged(const float* z, long long ldz, const long long* frame_off
  * bwd: dout [T*B][2H] gradient wrt out; whhT sb16 [2H][4H] (row dir*H+j, column 4u+gate);
  *      dG sb16 [T*B][8H] gate pre-activation gradients (zero at t>=len_b);
  *      dhn,dcn (optional) gradient wrt (hn,cn); dh0,dc0 (optional) gradient wrt (h0,c0).
- *      batch_pitch (0 = B): the pointers may address a SUB-BATCH of a wider padded batch -- rows b0..b0+B of every frame,
+ *      batch_pitch (0 = B; fwd with H = 600 and bwd): the pointers may address a SUB-BATCH of a wider padded batch -- rows b0..b0+B of every frame,
  *      every pointer advanced to its row / entry b0 by the caller, batch_pitch = rows per frame of the whole batch (and
  *      entries per direction of c0 / dhn / dcn / dh0 / dc0).  Batch rows are independent chains, so a batch of
- *      64 < B <= 128 is run as two halves through the K-split kernel (H = 600) instead of the slower generic one.
+ *      64 < B <= 128 is run as two halves through the tensor-memory kernels (H = 600) instead of the slower generic ones.
  * progress (optional, both): two counters, one per direction; while it runs the kernel stores
  *      progress[d] = prog_base + (number of steps of direction d whose out / dG rows are globally visible), every few
  *      steps (never the last ones: kernel completion covers those).  Direction 0 forward and direction 1 backward walk
@@ -190,7 +190,7 @@ int ss_masks_to_ragged(const float* z, long long ldz, const long long* frame_off
 long long ss_lstm_ws_bytes(int B, int H);
 int ss_lstm_fwd(float* gx, const void* whh_r, long long whh_ld, long long whh_plane, const float* h0, const float* c0,
                 const int* lens, void* out, long long out_plane, float* cs, float* hn, float* cn, void* ws,
-                unsigned int* progress, unsigned int prog_base, int T, int B, int H, void* stream);
+                unsigned int* progress, unsigned int prog_base, int T, int B, int batch_pitch, int H, void* stream);
 int ss_lstm_bwd(const float* gates, const float* cs, const float* c0, const float* dout, const float* dhn,
                 const float* dcn, const int* lens, const void* whhT, long long whhT_ld, long long whhT_plane, void* dG,
                 long long dG_plane, float* dh0, float* dc0, void* ws, unsigned int* progress, unsigned int prog_base,

@@ -423,8 +423,8 @@ extern "C" long long ss_lstm_ws_bytes(int B, int H) {
 
 extern "C" int ss_lstm_fwd(float* gx, const void* whh_r, long long whh_ld, long long whh_plane, const float* h0,
                            const float* c0, const int* lens, void* out, long long out_plane, float* cs, float* hn,
-                           float* cn, void* ws, unsigned int* progress, unsigned int prog_base, int T, int B, int H,
-                           void* stream) {
+                           float* cn, void* ws, unsigned int* progress, unsigned int prog_base, int T, int B,
+                           int batch_pitch, int H, void* stream) {
   using namespace ssb;
   SS_REQUIRE(T > 0 && B > 0 && B <= 128, "ss_lstm_fwd: need 1 <= B <= 128 (got %d) and T > 0", B);
   SS_REQUIRE(H % LF_U == 0 && H % 8 == 0 && H <= 64 * LF_MAXKC, "ss_lstm_fwd: unsupported hidden size %d", H);
@@ -446,8 +446,11 @@ extern "C" int ss_lstm_fwd(float* gx, const void* whh_r, long long whh_ld, long 
   p.done = (unsigned int*)((char*)ws + hbuf_bytes);
   cudaMemsetAsync(ws, 0, hbuf_bytes + 1024, st);            // the tail of the last K chunk is never published and must be finite
 
+  p.Bp = batch_pitch > 0 ? batch_pitch : B;
+  SS_REQUIRE(p.Bp >= B, "ss_lstm_fwd: batch_pitch %d < B %d", batch_pitch, B);
   if (H == 600 && p.R == 64 && whh_ld % 8 == 0 && whh_plane % 8 == 0)
     return launch_lstm_fwd_tw(p, whh_r, whh_ld, whh_plane, st);
+  SS_REQUIRE(p.Bp == B, "ss_lstm_fwd: a sub-batch view (batch_pitch %d != B %d) needs H = 600 and B <= 64", batch_pitch, B);
 
   CUtensorMap tmW;
   {

@@ -30,6 +30,7 @@ struct LstmFwdParams {
   unsigned int* progress;    // [2] or null: prog_base + number of steps whose `out` rows are globally visible, per direction
   unsigned int prog_base;
   int T, B, H, R, NC, KC, NS;
+  int Bp;                    // rows per frame of the padded batch the pointers walk (lstm_fwd_tw.cu; >= B)
   long long* dbg;            // optional clock64 trace of CTA 0: [step][32]
 };
 

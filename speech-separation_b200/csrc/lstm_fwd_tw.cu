@@ -83,7 +83,7 @@ __global__ void __launch_bounds__(TW_THREADS, 1) lstm_fwd_tw_kernel(LstmFwdTwPar
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int dir = blockIdx.x / p.NC, cta = blockIdx.x % p.NC;
   const int u0 = cta * LF_U;
-  const int T = p.T, B = p.B;
+  const int T = p.T, B = p.B, Bp = p.Bp;                      // Bp: rows per frame of the padded batch (>= B)
   const long long slot_elems = 2LL * TW_KC * (STAGE / 2), dir_elems = (long long)TW_KC * (STAGE / 2);
   unsigned int* counter = p.done + 128 + dir;
 
@@ -201,10 +201,10 @@ __global__ void __launch_bounds__(TW_THREADS, 1) lstm_fwd_tw_kernel(LstmFwdTwPar
     const bool ok0 = b0 < B, ok1 = b0 + 1 < B;
     const int len0 = lens_s[b0], len1 = lens_s[b0 + 1];
     float h[2], c[2];
-    h[0] = ok0 ? p.h0[((long long)dir * B + b0) * H + u] : 0.0f;
-    h[1] = ok1 ? p.h0[((long long)dir * B + b0 + 1) * H + u] : 0.0f;
-    c[0] = ok0 ? p.c0[((long long)dir * B + b0) * H + u] : 0.0f;
-    c[1] = ok1 ? p.c0[((long long)dir * B + b0 + 1) * H + u] : 0.0f;
+    h[0] = ok0 ? p.h0[((long long)dir * Bp + b0) * H + u] : 0.0f;
+    h[1] = ok1 ? p.h0[((long long)dir * Bp + b0 + 1) * H + u] : 0.0f;
+    c[0] = ok0 ? p.c0[((long long)dir * Bp + b0) * H + u] : 0.0f;
+    c[1] = ok1 ? p.c0[((long long)dir * Bp + b0 + 1) * H + u] : 0.0f;
     // coalesced stores: epilogue thread -> (operand row, 8-byte part) of the 128 x 24-byte tile this CTA publishes
     const int st_row = eidx / 3, st_part = eidx % 3;            // (tile row plane * 64 + b, 8-byte part) of the staged tiles
     const int pub_row = (st_row >> 6) * RB + (st_row & 63);    // its operand row; published if b < RB
@@ -239,8 +239,8 @@ __global__ void __launch_bounds__(TW_THREADS, 1) lstm_fwd_tw_kernel(LstmFwdTwPar
       const int t = dir ? (T - 1 - s) : s;
       const bool act0 = ok0 && t < len0, act1 = ok1 && t < len1;
       float4 gx0 = make_float4(0.f, 0.f, 0.f, 0.f), gx1 = gx0;
-      if (act0) gx0 = *reinterpret_cast<const float4*>(p.gx + ((long long)t * B + b0) * (8LL * H) + (long long)dir * 4 * H + 4 * u);
-      if (act1) gx1 = *reinterpret_cast<const float4*>(p.gx + ((long long)t * B + b0 + 1) * (8LL * H) + (long long)dir * 4 * H + 4 * u);
+      if (act0) gx0 = *reinterpret_cast<const float4*>(p.gx + ((long long)t * Bp + b0) * (8LL * H) + (long long)dir * 4 * H + 4 * u);
+      if (act1) gx1 = *reinterpret_cast<const float4*>(p.gx + ((long long)t * Bp + b0 + 1) * (8LL * H) + (long long)dir * 4 * H + 4 * u);
       // one warp polls the mbarrier; the others sleep on a hardware barrier
       if (warp == 0) mbar_wait(accum_full, s & 1);
       asm volatile("bar.sync 2, %0;" ::"n"(TW_EPI) : "memory");
@@ -325,31 +325,31 @@ __global__ void __launch_bounds__(TW_THREADS, 1) lstm_fwd_tw_kernel(LstmFwdTwPar
         const int plo = st_row >> 6, bb = st_row & 63;
         if (bb < B) {
           const uint2 v = reinterpret_cast<const uint2*>(ost)[st_row * 4 + st_part];
-          __stcs(reinterpret_cast<uint2*>(p.out + plo * p.out_plane + ((long long)t * B + bb) * (2LL * H) + dir * H + u0 + st_part * 4), v);
+          __stcs(reinterpret_cast<uint2*>(p.out + plo * p.out_plane + ((long long)t * Bp + bb) * (2LL * H) + dir * H + u0 + st_part * 4), v);
         }
 #pragma unroll
         for (int j = 0; j < 2; ++j) {
           const int f = eidx + TW_EPI * j, rr = f / 12, c4 = f % 12;
           if (rr < B && t < lens_s[rr])
-            __stcs(reinterpret_cast<float4*>(p.gx + ((long long)t * B + rr) * (8LL * H) + (long long)dir * 4 * H + 4 * u0) + c4,
+            __stcs(reinterpret_cast<float4*>(p.gx + ((long long)t * Bp + rr) * (8LL * H) + (long long)dir * 4 * H + 4 * u0) + c4,
                    reinterpret_cast<const float4*>(xbuf + rr * LF_XPITCH)[c4]);
         }
         if (p.cs && eidx < 192) {
           const int rr = eidx / 3, c4 = eidx % 3;
           if (rr < B && t < lens_s[rr])
-            __stcs(reinterpret_cast<float4*>(p.cs + ((long long)t * B + rr) * (2LL * H) + dir * H + u0) + c4,
+            __stcs(reinterpret_cast<float4*>(p.cs + ((long long)t * Bp + rr) * (2LL * H) + dir * H + u0) + c4,
                    reinterpret_cast<const float4*>(cst + rr * 12)[c4]);
         }
       }
       if (eidx == 0) TW_STAMP(9);
     }
     if (ok0) {
-      p.hn[((long long)dir * B + b0) * H + u] = h[0];
-      p.cn[((long long)dir * B + b0) * H + u] = c[0];
+      p.hn[((long long)dir * Bp + b0) * H + u] = h[0];
+      p.cn[((long long)dir * Bp + b0) * H + u] = c[0];
     }
     if (ok1) {
-      p.hn[((long long)dir * B + b0 + 1) * H + u] = h[1];
-      p.cn[((long long)dir * B + b0 + 1) * H + u] = c[1];
+      p.hn[((long long)dir * Bp + b0 + 1) * H + u] = h[1];
+      p.cn[((long long)dir * Bp + b0 + 1) * H + u] = c[1];
     }
   }
   __syncthreads();

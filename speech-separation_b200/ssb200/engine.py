@@ -42,6 +42,9 @@ FWD_STREAM_FRACTION = 0.64   # forward: stream the x-projection halves that are 
 BWD_STREAM_FRACTION = (0.6, 1.0)
 MIN_STREAM_T = 48
 SPLIT_WIDE_BATCH = True      # backward recurrence of 64 < B <= 128 as two half-batch launches of the K-split kernel
+# The same for the forward recurrence (ss_lstm_fwd takes a sub-batch view too) does NOT pay: two launches at 5.2 us per
+# time step against ~9.5 for one pass of the generic 128-row kernel (batch 100: 32.2 instead of 31.3 ms per step).
+SPLIT_WIDE_BATCH_FWD = False
 GRAPH_REFRESH = os.environ.get("SSB_GRAPH_REFRESH", "1") != "0"
 
 
@@ -291,12 +294,15 @@ class _Streamer:
             fn(0)
 
 
-def _lstm_fwd(ws, wt, l, h0, c0, lens_dev, training, sj):
-    o = ws.out[l]
-    call("lstm_fwd", ws.gx[l], wt.whh_r[l].buf, LL(wt.whh_r[l].ld), LL(wt.whh_r[l].plane),
-         h0[2 * l:2 * l + 2], c0[2 * l:2 * l + 2], lens_dev, o.buf, LL(o.plane), ws.cs[l] if training else None,
-         ws.hn[2 * l:2 * l + 2], ws.cn[2 * l:2 * l + 2], ws.lstm_ws, ws.progress if sj else None,
-         ctypes.c_uint(sj.base if sj else 0), ws.T, ws.B, H, stream_ptr())
+def _lstm_fwd(ws, wt, l, h0, c0, lens_dev, training, sj, b0=0, b1=None):
+    """Rows b0..b1 of the batch (a sub-batch view: every pointer advanced to row / entry b0, batch_pitch = ws.B)."""
+    o, B = ws.out[l], ws.B
+    b1 = B if b1 is None else b1
+    sub = lambda t: t[2 * l:2 * l + 2][:, b0:]                 # [2][B][H] state tensors: entry b0
+    call("lstm_fwd", ws.gx[l][b0:], wt.whh_r[l].buf, LL(wt.whh_r[l].ld), LL(wt.whh_r[l].plane),
+         sub(h0), sub(c0), lens_dev[b0:], _sb_view(o, b0).buf, LL(o.plane), ws.cs[l][b0:] if training else None,
+         sub(ws.hn), sub(ws.cn), ws.lstm_ws, ws.progress if sj else None,
+         ctypes.c_uint(sj.base if sj else 0), ws.T, b1 - b0, B, H, stream_ptr())
 
 
 def forward(ws, wt, p, x, lens_dev, h0, c0, bn_train, save=True, bn_momentum=0.1, bn_eps=1e-5, dp=None):
@@ -311,8 +317,13 @@ def forward(ws, wt, p, x, lens_dev, h0, c0, bn_train, save=True, bn_momentum=0.1
     stream = STREAM and T >= MIN_STREAM_T
     for l in range(ws.L):
         nxt = l + 1 < ws.L
-        sj = _Streamer(ws, x.device, False, T) if (stream and nxt) else None
-        _lstm_fwd(ws, wt, l, h0, c0, lens_dev, training, sj)
+        # (optionally two half-batch launches for 64 < B <= 128: see SPLIT_WIDE_BATCH_FWD)
+        halves = [(0, B)] if (B <= 64 or not SPLIT_WIDE_BATCH_FWD) else [(0, (B + 1) // 2), ((B + 1) // 2, B)]
+        sj = None
+        for hi_, (b0, b1) in enumerate(halves):
+            if hi_ == len(halves) - 1 and stream and nxt:
+                sj = _Streamer(ws, x.device, False, T)
+            _lstm_fwd(ws, wt, l, h0, c0, lens_dev, training, sj, b0, b1)
         if not nxt:
             break
         if sj is None:
