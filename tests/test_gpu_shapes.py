@@ -132,3 +132,59 @@ def test_three_layer_net_matches_oracle():
     tr.step(batch)
     torch.cuda.synchronize()
     assert set(tr.buckets) == {"l0", "l1", "head"} and float((tr.flat_p - before).abs().max()) > 0
+
+
+@pytest.mark.parametrize("B", [24, 40])
+def test_padded_row_variants_match_oracle(B):
+    """Batches of 17..32 utterances run the 32-row variants of the tensor-memory recurrence kernels, 33..64 the 64-row ones
+    (B <= 16: the 16-row ones, covered by every small golden): loss, permutations and gradients against the fp64 oracle."""
+    F, S = 129, 2
+    lens = sorted(np.random.default_rng(B).integers(5, 40, size=B).tolist(), reverse=True)
+    samples = _rand_batch(B + 1, lens, F, S)
+    batch = uPIT.Collator("mix")(samples)
+    torch.manual_seed(3)
+    model = uPIT.SepDNN(0, feat_dim=str(F), num_spk=str(S)).cuda()
+    sd = {k: (v.detach().double().cpu().clone() if v.is_floating_point() else v.cpu().clone())
+          for k, v in model.state_dict().items()}
+    torch.manual_seed(22)
+    loss, norm = uPIT.compute_loss(model, 0, batch)
+    loss.backward()
+    torch.cuda.synchronize()
+    torch.manual_seed(22)
+    h0, c0 = torch.randn(4, B, 600).double(), torch.randn(4, B, 600).double()
+    order = np.argsort(np.array(lens))[::-1]
+    srt = [samples[i] for i in order]
+    mix, tl = common.pad_time_major([s["mix"] for s in srt])
+    sources = [common.pad_time_major([s["source%d" % (i + 1)] for s in srt])[0] for i in range(S)]
+    params = {k: v.requires_grad_(True) for k, v in sd.items() if v.is_floating_point() and "running" not in k}
+    sd.update(params)
+    oloss, onorm, _, oidx, _, _ = uo.upit_compute_loss(sd, mix, sources, tl, h0, c0)
+    oloss.backward()
+    assert abs(float(loss.detach()) - float(oloss)) <= 1e-3 * float(oloss)
+    assert np.array_equal(model.last["indices"].cpu().numpy(), oidx.numpy())
+    for k, p in model.named_parameters():
+        assert common.rel(p.grad.cpu().numpy(), params[k].grad.numpy()) <= 1e-3, k
+
+
+def test_forward_sub_batch_view_equals_one_launch():
+    """ss_lstm_fwd with batch_pitch: two half-batch launches (rows 0..49 and 50..99 of a 100-row padded batch, tensor-memory
+    kernel) give the same masks as one pass of the generic 128-row kernel (batch rows are independent chains)."""
+    from ssb200 import engine
+    F, B = 129, 100
+    lens = sorted(np.random.default_rng(5).integers(6, 30, size=B).tolist(), reverse=True)
+    samples = [{"mix": s["mix"]} for s in _rand_batch(6, lens, F, 0)]
+    batch = uPIT.Collator("mix")(samples)
+    torch.manual_seed(4)
+    model = uPIT.SepDNN(0, feat_dim=str(F), num_spk="2").cuda().eval()
+    outs = []
+    try:
+        for split in (False, True):
+            engine.SPLIT_WIDE_BATCH_FWD = split
+            torch.manual_seed(30)
+            model.hidden = (torch.randn(4, B, 600, device="cuda"), torch.randn(4, B, 600, device="cuda"))
+            with torch.no_grad():
+                outs.append(model(batch["mix"]).float().cpu().numpy())
+    finally:
+        engine.SPLIT_WIDE_BATCH_FWD = False
+    assert outs[0].shape == outs[1].shape
+    assert np.abs(outs[0] - outs[1]).max() <= 2e-5
