@@ -71,6 +71,8 @@ def allreduce_buckets(flat, buckets, group=None, tags=BUCKET_ORDER):
     return works
 
 
+EAGER_REFRESH = True
+
 class ExactDP:
     """Data-parallel mode B: the small collectives that make N ranks reproduce the reference's arithmetic
     on the concatenated batch -- sum of (BatchNorm sums, batch size), max of T, sum of (loss numerator, normaliser), sum
@@ -257,4 +259,8 @@ class Trainer:
         call("grad_norm", self.flat_g, LL(self.n), gscale, self.partial, self.norm, st)
         call("clip_adam", self.flat_p, self.flat_g, self.flat_m, self.flat_v, LL(self.n), self.norm, gscale,
              self.clip, self.lr, float(self.betas[0]), float(self.betas[1]), self.eps, self.steps, st)
-        self.model._wt_versions = None     # parameters changed behind autograd's back: refresh the operand copies
+        self.model._wt_versions = None     # parameters changed behind autograd's back: refresh the operand copies ...
+        # ... right away (one CUDA-graph replay behind the update): it then runs while the host prepares the next batch
+        # instead of in front of the next step's first GEMM
+        if EAGER_REFRESH and hasattr(self.model, "weights") and hasattr(self.model, "param_dict"):
+            self.model.weights(self.model.param_dict(), need_grad_copies=True)
