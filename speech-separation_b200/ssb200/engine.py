@@ -32,7 +32,12 @@ H = 600          # archs/uPIT.py:115, archs/RSH.py:155 (hard-coded in the refere
 UNIT4 = 1
 # stream GEMMs under the recurrences (module switch for A/B tests and profiling; results agree either way)
 STREAM = os.environ.get("SSB_STREAM", "1") != "0"
-N_CHUNKS = 8     # time chunks of a streamed GEMM
+# Time chunks of the streamed GEMMs.  Measured at configs[2] with the 2.7 / 3.1 ms recurrences of this round (ms per train
+# step): all three at 16 / 12 / 10 / 8 / 6 / 4 / 3 -> 17.15 / 16.23 / 15.54 / 15.22 / 15.00 / 14.90 / 15.43; around (4, 4, 4):
+# forward 4 / 6 / 8 -> 14.85 / 14.88 / 14.81, dX 3 / 4 / 6 -> 14.88 / 14.85 / 14.83, dW 3 / 4 / 6 -> 15.06 / 14.85 / 15.01.
+N_CHUNKS = 4         # backward: dX of a layer
+N_CHUNKS_FWD = 8     # forward: x-projection of the next layer
+N_CHUNKS_DW = 4      # backward: dW_hh (and dW_ih of layer 0), accumulated over row blocks
 FWD_STREAM_FRACTION = 0.64   # forward: stream the x-projection halves that are ready within this fraction of the recurrence
 # backward: a gated job whose inputs are only ready after this fraction of the recurrence runs AFTER it, on the main stream
 # at full width, instead of finishing late on the 68 idle SMs (first entry: layer 0, whose side stream starts with the
@@ -336,7 +341,7 @@ def forward(ws, wt, p, x, lens_dev, h0, c0, bn_train, save=True, bn_momentum=0.1
         # the others follow on the main stream at full width, as ONE full-K GEMM where both halves of a chunk are late.
         o, w, gx, bias = ws.out[l], wt.wih[l + 1], ws.gx[l + 1], wt.bias[l + 1]
         cut = min(sj.max_reported, int(FWD_STREAM_FRACTION * T))
-        for (a, b) in _chunks(T, N_CHUNKS):
+        for (a, b) in _chunks(T, N_CHUNKS_FWD):
             r0, rows = a * B, (b - a) * B
             halves = sorted(((b, 0), (T - a, 1)))              # (ready, direction), earliest first
             if halves[0][0] > cut:
@@ -530,7 +535,7 @@ def backward(ws, wt, p, grads, mix, src, lens_dev, h0, c0, F, n_out, gout, dmask
                         sj.add(((d, ready[d]),), job, order=0)
             # (3) weight gradients that only need this layer's gate gradients, accumulated over row blocks in the order
             # the two directions produce them (direction 0 from the last block down, direction 1 from the first up)
-            sizes = _block_chunks(nblk, N_CHUNKS)
+            sizes = _block_chunks(nblk, N_CHUNKS_DW)
             done = 0
             for ci, n in enumerate(sizes):
                 blk0 = (nblk - done - n, done)
