@@ -188,3 +188,35 @@ def test_forward_sub_batch_view_equals_one_launch():
         engine.SPLIT_WIDE_BATCH_FWD = False
     assert outs[0].shape == outs[1].shape
     assert np.abs(outs[0] - outs[1]).max() <= 2e-5
+
+
+@pytest.mark.parametrize("lens", [[2], [2, 1, 1], [3, 3], [5, 1]])   # (one frame in total: torch's BatchNorm1d refuses it)
+def test_tiny_sequences_match_oracle(lens):
+    """One- to five-frame utterances, batch 1..3: the recurrence kernels' first / only steps (no streaming below 48 frames,
+    reverse rows that start at the very first step, the extra d(h0) step of the backward kernel)."""
+    F, S, B = 129, 2, len(lens)
+    samples = _rand_batch(77 + sum(lens), lens, F, S)
+    batch = uPIT.Collator("mix")(samples)
+    torch.manual_seed(5)
+    model = uPIT.SepDNN(0, feat_dim=str(F), num_spk=str(S)).cuda()
+    sd = {k: (v.detach().double().cpu().clone() if v.is_floating_point() else v.cpu().clone())
+          for k, v in model.state_dict().items()}
+    torch.manual_seed(23)
+    loss, norm = uPIT.compute_loss(model, 0, batch)
+    loss.backward()
+    torch.cuda.synchronize()
+    torch.manual_seed(23)
+    h0, c0 = torch.randn(4, B, 600).double(), torch.randn(4, B, 600).double()
+    order = np.argsort(np.array(lens), kind="stable")[::-1]
+    srt = [samples[i] for i in order]
+    mix, tl = common.pad_time_major([s["mix"] for s in srt])
+    sources = [common.pad_time_major([s["source%d" % (i + 1)] for s in srt])[0] for i in range(S)]
+    params = {k: v.requires_grad_(True) for k, v in sd.items() if v.is_floating_point() and "running" not in k}
+    sd.update(params)
+    oloss, onorm, _, oidx, _, _ = uo.upit_compute_loss(sd, mix, sources, tl, h0, c0)
+    oloss.backward()
+    assert abs(float(loss.detach()) - float(oloss)) <= 1e-3 * float(oloss)
+    assert np.array_equal(model.last["indices"].cpu().numpy(), oidx.numpy())
+    for k, p in model.named_parameters():
+        ref = params[k].grad.numpy()
+        assert np.abs(p.grad.cpu().numpy() - ref).max() <= 1e-3 * max(np.abs(ref).max(), 1e-12), k
