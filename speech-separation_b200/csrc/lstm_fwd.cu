@@ -1,4 +1,5 @@
-// K2b: persistent bidirectional LSTM recurrence (forward pass), one cooperative launch per layer.
+// K2b (generic path: any H <= 640 divisible by 12, B <= 128; the reference's shape H = 600, B <= 64 runs lstm_fwd_tw.cu):
+// persistent bidirectional LSTM recurrence (forward pass), one cooperative launch per layer.
 // Replaces the sequential part of cudnnRNNForward behind `self.blstm(x, self.hidden)` (archs/uPIT.py:115,132;
 // archs/RSH.py:155,172) for a length-sorted padded batch with PackedSequence semantics:
 //   * the reverse direction starts at each utterance's own last frame, from (h0, c0);
@@ -13,8 +14,8 @@
 // a few units of ONE batch row, so direct stores are 32 scattered 4..16-byte transactions per instruction, the SM
 // retires about one transaction per cycle (1.7k per step), and the release and the next step's polls queue behind them.
 // So (1) everything is staged in shared memory and stored row-wise (whole sectors), (2) only the carried state is
-// stored before the release -- each warp releases for itself as soon as its own 8-byte stores are out, no CTA barrier,
-// no proxy fence on the writer side -- and (3) the activated gates, cell states, `out` rows leave only after the next
+// stored before the release (ONE per CTA: twelve per-warp releases made 600 adds per step on one address, which queue up
+// in L2), no proxy fence on the writer side -- and (3) the activated gates, cell states, `out` rows leave only after the next
 // step's gate has opened.  On the reader side one otherwise idle thread polls the counter, crosses to the async proxy
 // (fence.proxy.async is cheap in a thread with nothing outstanding) and issues the ten copies.
 //
