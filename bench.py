@@ -644,7 +644,8 @@ def run_separate(args, rank, local, world, which="train"):
         # two slots: batch i+1 is prepared and enqueued while the device works on batch i; every step still ends with
         # one batch's int16 audio on the host
         h = pipeline.submit(model, batches[(i + 1) % N_BATCHES], N_FFT, HOP, slot=(i + 1) & 1)
-        if "pending" in sink:
+        torch.cuda.current_stream().wait_event(h["done"])      # the slots run on streams of their own: the timing events
+        if "pending" in sink:                                  # of this stream must wait for every submitted batch
             sink["wav"] = pipeline.collect(sink["pending"])
         sink["pending"] = h
 

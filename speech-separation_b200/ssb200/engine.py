@@ -226,7 +226,9 @@ def _dev_index(device):
 def _side_stream(device):
     key = _dev_index(device)
     if key not in _SIDE:
-        _SIDE[key] = torch.cuda.Stream(device=device)
+        # high priority: its gated GEMMs are on the step's critical path, while other streams (the second slot of
+        # ssb200.pipeline) only fill what is left of the idle SMs
+        _SIDE[key] = torch.cuda.Stream(device=device, priority=-1)
     return _SIDE[key]
 
 

@@ -74,32 +74,51 @@ def train_batch(mix_wavs, src_wavs, n_fft=512, hop=128, device="cuda"):
 _PENDING = {}
 
 
+_SLOT_STREAMS = {}
+
+
+def _slot_stream(device, slot):
+    """Every slot has a stream (and, in the model, a workspace) of its own: batch i+1's STFT / first GEMM and batch i-1's
+    masks / iSTFT / copy-out then run on the SMs batch i's recurrence leaves idle instead of queueing behind it."""
+    dev = torch.device(device)
+    key = (dev.index if dev.index is not None else torch.cuda.current_device(), slot)
+    if key not in _SLOT_STREAMS:
+        _SLOT_STREAMS[key] = torch.cuda.Stream(device=dev)
+    return _SLOT_STREAMS[key]
+
+
 def submit(model, wavs, n_fft=512, hop=128, device=None, slot=0):
     """First half of `separate`: uploads the waveforms and enqueues STFT, model, masks, iSTFT and the copy of the int16
-    audio into pinned memory on the current stream, without waiting.  Returns a handle for `collect`.  Two slots used
-    alternately let the host side of batch i+1 (ordering, concatenation, h0/c0 draw, launches) run while the device
-    works on batch i -- the evaluation counterpart of Trainer.prefetch."""
+    audio into pinned memory on the slot's stream, without waiting.  Returns a handle for `collect`.  Two slots used
+    alternately let the host side of batch i+1 (ordering, concatenation, h0/c0 draw, launches) AND the parts of its
+    device work that do not need 100 SMs run while the device works on batch i -- the evaluation counterpart of
+    Trainer.prefetch."""
     if slot in _PENDING:
         raise RuntimeError("pipeline.submit: slot %d still holds a batch that was not collected" % slot)
     device = model.lin.weight.device if device is None else device
     S, F = model.num_spk, n_fft // 2 + 1
     assert F == model.feat_dim and model.out_dim == S * F
     order = _order(wavs, hop)
-    rag = ops.Ragged([len(wavs[i]) for i in order], n_fft, hop, device)
-    spec = ops.stft(_upload(wavs, order, device, tag="in%d" % slot), rag, complex_out=True, layout_tf=True)
-    batch = _batch(rag, ops.ragged_to_padded(spec, rag), device)
-    model.hidden = model.init_hidden(batch["B"])
-    with torch.no_grad():
-        run_forward(model, batch, model.hidden, save=False)     # one workspace: the stream orders the batches
-        ws = batch["ws"]
-        mask = ops.masks_to_ragged(ws.z, ws.ldz, rag, batch["T"], S)
-        wav, off = ops.istft_masked(spec, mask, rag, S, layout_tf=True)
-    stage = _pinned("out%d" % slot, wav.numel(), wav.dtype)
-    stage.copy_(wav, non_blocking=True)                        # the only device->host copy
-    done = torch.cuda.Event()
-    done.record()
+    # operand copies of the parameters: rebuilt (if they changed) on the caller's stream, which every slot stream follows
+    model.weights(model.param_dict(), need_grad_copies=False)
+    stream = _slot_stream(device, slot)
+    stream.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(stream):
+        rag = ops.Ragged([len(wavs[i]) for i in order], n_fft, hop, device)
+        spec = ops.stft(_upload(wavs, order, device, tag="in%d" % slot), rag, complex_out=True, layout_tf=True)
+        batch = _batch(rag, ops.ragged_to_padded(spec, rag), device)
+        model.hidden = model.init_hidden(batch["B"])
+        with torch.no_grad():
+            run_forward(model, batch, model.hidden, save=False, slot=slot)
+            ws = batch["ws"]
+            mask = ops.masks_to_ragged(ws.z, ws.ldz, rag, batch["T"], S)
+            wav, off = ops.istft_masked(spec, mask, rag, S, layout_tf=True)
+        stage = _pinned("out%d" % slot, wav.numel(), wav.dtype)
+        stage.copy_(wav, non_blocking=True)                    # the only device->host copy
+        done = torch.cuda.Event()
+        done.record()
     h = {"slot": slot, "done": done, "stage": stage, "off": off, "order": order, "L": rag.L, "S": S, "n": len(wavs),
-         "keep": (spec, mask, wav)}                            # device buffers stay referenced until the copy is done
+         "keep": (spec, mask, wav, batch)}                     # device buffers stay referenced until the copy is done
     _PENDING[slot] = h
     return h
 
