@@ -171,7 +171,8 @@ int ss_masks_to_ragged(const float* z, long long ldz, const long long* frame_off
  * behind nn.LSTM(..., bidirectional=True) at archs/uPIT.py:115,132 / archs/RSH.py:155,172 (PackedSequence
  * semantics via lens[], descending) and of its backward (steps/train_qsub.py:120) ----
  * Gate columns are interleaved: column dir*4H + 4*u + gate (gate order i,f,g,o as torch).
- * fwd: gx [T*B][8H] = x W_ih^T + b_ih + b_hh (both directions) is overwritten with the activated gates;
+ * fwd: gx [T*B][8H] = x W_ih^T + b_ih + b_hh (both directions) is overwritten with the activated gates (training,
+ *      i.e. cs != NULL; without cs the contents of gx after the call are unspecified: evaluation keeps neither);
  *      whh_r sb16 [8H][H] (rows dir*4H+4u+gate); h0,c0,hn,cn [2][B][H]; out sb16 [T*B][2H] (zero at t>=len_b);
  *      cs [T*B][2H] cell states (training; may be NULL).  ws: ss_lstm_ws_bytes(B,H) bytes.
  * bwd: dout [T*B][2H] gradient wrt out; whhT sb16 [2H][4H] (row dir*H+j, column 4u+gate);

@@ -314,10 +314,12 @@ __global__ void __launch_bounds__(TW_THREADS, 1) lstm_fwd_tw_kernel(LstmFwdTwPar
       publish((s + 1) & 1);
       if (eidx == 0) TW_STAMP(7);
       // the rest of the step's results: staged now, stored row-wise once the next step's gate has opened
-      *reinterpret_cast<float4*>(xbuf + b0 * LF_XPITCH + 4 * ul) = ga[0];
-      *reinterpret_cast<float4*>(xbuf + (b0 + 1) * LF_XPITCH + 4 * ul) = ga[1];
-      cst[b0 * 12 + ul] = c[0];
-      cst[(b0 + 1) * 12 + ul] = c[1];
+      if (p.cs) {                                              // (evaluation keeps neither the gates nor the cell states)
+        *reinterpret_cast<float4*>(xbuf + b0 * LF_XPITCH + 4 * ul) = ga[0];
+        *reinterpret_cast<float4*>(xbuf + (b0 + 1) * LF_XPITCH + 4 * ul) = ga[1];
+        cst[b0 * 12 + ul] = c[0];
+        cst[(b0 + 1) * 12 + ul] = c[1];
+      }
       stage_h(ost, hout);
       asm volatile("bar.sync 7, %0;" ::"n"(TW_EPI) : "memory");
       if (s + 1 < T) asm volatile("bar.sync 8, %0;" ::"n"(32 + TW_EPI) : "memory");
@@ -330,7 +332,7 @@ __global__ void __launch_bounds__(TW_THREADS, 1) lstm_fwd_tw_kernel(LstmFwdTwPar
 #pragma unroll
         for (int j = 0; j < 2; ++j) {
           const int f = eidx + TW_EPI * j, rr = f / 12, c4 = f % 12;
-          if (rr < B && t < lens_s[rr])
+          if (p.cs && rr < B && t < lens_s[rr])
             __stcs(reinterpret_cast<float4*>(p.gx + ((long long)t * Bp + rr) * (8LL * H) + (long long)dir * 4 * H + 4 * u0) + c4,
                    reinterpret_cast<const float4*>(xbuf + rr * LF_XPITCH)[c4]);
         }
